@@ -1,0 +1,145 @@
+"""Generate the golden fixtures under tests/golden/ by running the UNMODIFIED
+reference (/root/reference/fvm_classes.py, loaded through oracle/ref_loader.py)
+in the build container.  The reference ships no tests or golden vectors of its
+own, so these files are what pins the oracle -- and,
+through it, the CUDA path -- to the reference's behaviour.
+
+    python tests/golden/make_golden.py        # needs /root/reference; ~5 min
+
+Every array below comes from the reference's own classes and the literal loop
+of fvm_classes.py:373-377,408-411 (scipy spsolve); nothing is computed by the
+oracle restatement or by the product.
+"""
+import os
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from oracle import ref_loader as R            # noqa: E402
+from oracle import fvm_oracle as O            # noqa: E402  (mesh generators only)
+from fvm_b200 import workloads as W           # noqa: E402
+
+BCS = [dict(left_value=1., right_value=0.), dict(left_flux=0.3, right_flux=-0.2),
+       dict(left_value=1., right_flux=0.1), dict(left_flux=0.2, right_value=0.5),
+       dict(left_flux=0.0, right_flux=0.0)]
+
+
+def bc_arrays(bc):
+    """[left_flux, right_flux, left_value, right_value] with NaN for None."""
+    return np.array([np.nan if bc.get(key) is None else bc[key]
+                     for key in ("left_flux", "right_flux", "left_value", "right_value")])
+
+
+def assembly_cases():
+    rng = np.random.default_rng(1234)
+    out = {}
+    n = 0
+    for t in range(40):
+        J = int(rng.integers(3, 64))
+        kind = t % 3
+        if kind == 0:
+            f = np.linspace(0, 1, J + 1)
+        elif kind == 1:
+            f = W.graded_faces(J, 30.0)
+        else:
+            f = np.concatenate([[0], np.sort(rng.uniform(0, 1, J - 1)), [1]])
+        scal = t % 2 == 0
+        a = float(rng.normal()) if scal else rng.normal(size=J)
+        d = float(10 ** rng.uniform(-3, 0)) if scal else 10 ** rng.uniform(-3, 0, size=J)
+        for scheme in O.SCHEMES:
+            bc = BCS[n % len(BCS)]
+            r = R.reference_assembly(f, a, d, 0.01, scheme, bc)
+            pre = "c%03d_" % n
+            out[pre + "faces"] = f
+            out[pre + "a"] = np.asarray(a, dtype=float)
+            out[pre + "d"] = np.asarray(d, dtype=float)
+            out[pre + "scheme"] = np.array(O.SCHEMES.index(scheme))
+            out[pre + "bc"] = bc_arrays(bc)
+            for key in ("lo", "di", "up", "alpha", "beta", "kappa", "D"):
+                out[pre + key] = r[key]
+            n += 1
+    out["n_cases"] = np.array(n)
+    return out
+
+
+def cfg1_examples():
+    """fvm_examples.py flow on its three meshes (old-API shim):
+    a=1, d=1e-3, k=0.01, Dirichlet flags, w_init=sin(pi c)^100, 251 steps."""
+    out = {}
+    bc = dict(left_value=1., right_value=0.)
+    for kind in ("uniform", "random", "geometric"):
+        f = O.example_faces(kind)
+        c = 0.5 * (f[1:] + f[:-1])
+        w0 = np.sin(np.pi * c) ** 100
+        out[kind + "_faces"] = f
+        out[kind + "_w0"] = w0
+        for scheme in O.SCHEMES:
+            out["%s_%s_theta0.5" % (kind, scheme)] = R.reference_theta_run(
+                f, 1, 1e-3, 0.01, scheme, bc, 0.5, w0, 251, every=1)
+            out["%s_%s_theta1.0" % (kind, scheme)] = R.reference_theta_run(
+                f, 1, 1e-3, 0.01, scheme, bc, 1.0, w0, 251, every=50)
+    return out
+
+
+def demo_J149():
+    """The shipped demo, fvm_classes.py:346-411: J=149, exponential, theta=1, 201 steps."""
+    f = O.demo_faces()
+    c = 0.5 * (f[1:] + f[:-1])
+    w0 = np.sin(np.pi * c) ** 100
+    w0[0] = 1.0
+    bc = dict(left_value=1., right_value=0.)
+    states = R.reference_theta_run(f, 1, 1e-3, 0.01, "exponential", bc, 1.0, w0, 201, every=1)
+    asm = R.reference_assembly(f, 1, 1e-3, 0.01, "exponential", bc)
+    return dict(faces=f, w0=w0, states=states, kappa=asm["kappa"], D=asm["D"],
+                lo=asm["lo"], di=asm["di"], up=asm["up"])
+
+
+def cfg2_subset():
+    """cfg 2 on a subset of the sweep: J=4096 graded mesh, 8 Peclet numbers x 3 schemes,
+    2000 Crank-Nicolson steps; snapshots after steps 1, 100, 2000.  The
+    exponential scheme is left out where the reference's kappa is NaN (Pe >= 709.8)."""
+    wl = W.peclet_sweep(4096)
+    pick = [0, 4, 8, 12, 16, 20, 24, 28]          # Pe = 1e-3, 1e-2, ..., 1e4
+    snaps = [1, 100, 2000]
+    out = dict(pick=np.array(pick), snaps=np.array(snaps), pe=wl["pe"][pick])
+    for scheme in O.SCHEMES:
+        for j in pick:
+            if scheme == "exponential" and wl["pe"][j] > 700:
+                continue
+            t0 = time.time()
+            st = R.reference_theta_run(wl["faces"], wl["a"][j], wl["d"][j], wl["k"][j], scheme,
+                                       wl["bc"], 0.5, wl["w0"][j], 2000, every=1)
+            out["%s_%02d" % (scheme, j)] = st[[s - 1 for s in snaps]]
+            print("cfg2", scheme, j, "%.1fs" % (time.time() - t0), flush=True)
+    return out
+
+
+def cfg3_subset():
+    """cfg 3 on its first 8 problems: J=1024 graded mesh, exponential, zero-flux Robin,
+    Crank-Nicolson, 2000 steps; snapshots after 1, 10, 100, 1000, 2000."""
+    wl = W.batched_sweep(65536, 1024, first=0, count=8)
+    snaps = [1, 10, 100, 1000, 2000]
+    states = []
+    for p in range(8):
+        st = R.reference_theta_run(wl["faces"], wl["a"][p], wl["d"][p], wl["k"][p], "exponential",
+                                   wl["bc"], 0.5, wl["w0"][p], 2000, every=1)
+        states.append(st[[s - 1 for s in snaps]])
+        print("cfg3", p, flush=True)
+    return dict(snaps=np.array(snaps), states=np.array(states), a=wl["a"], d=wl["d"], k=wl["k"])
+
+
+if __name__ == "__main__":
+    only = sys.argv[1:]
+    jobs = dict(assembly_cases=assembly_cases, cfg1_examples=cfg1_examples, demo_J149=demo_J149,
+                cfg3_subset=cfg3_subset, cfg2_subset=cfg2_subset)
+    for name, fn in jobs.items():
+        if only and name not in only:
+            continue
+        t0 = time.time()
+        data = fn()
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), **data)
+        print(name, "%.1fs" % (time.time() - t0), flush=True)
