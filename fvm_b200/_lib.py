@@ -1,0 +1,110 @@
+"""ctypes binding of the C-ABI in include/fvm_b200.h.
+
+There is no CPU fallback: if the library or a CUDA device is missing, the first
+call raises.  torch is used for device memory and streams only.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfvm_b200.so")
+
+FVM_OK = 0
+FVM_ERR_INVALID_ARG = -1
+FVM_ERR_UNSUPPORTED = -2
+CENTRAL, UPWIND, EXPONENTIAL = 0, 1, 2
+SCHEMES = {"central": CENTRAL, "upwind": UPWIND, "exponential": EXPONENTIAL}
+BC_DIRICHLET, BC_ROBIN = 0, 1
+
+c_i64 = ctypes.c_int64
+c_i32 = ctypes.c_int32
+c_dbl = ctypes.c_double
+c_ptr = ctypes.c_void_p
+
+
+class FvmProblem(ctypes.Structure):
+    """struct fvm_problem (include/fvm_b200.h)."""
+    _fields_ = [
+        ("J", c_i64), ("P", c_i64),
+        ("faces", c_ptr),
+        ("a", c_ptr), ("a_ps", c_i64), ("a_cs", c_i64),
+        ("d", c_ptr), ("d_ps", c_i64), ("d_cs", c_i64),
+        ("reaction", c_ptr), ("r_ps", c_i64), ("r_cs", c_i64),
+        ("scheme", c_i32), ("left_kind", c_i32), ("right_kind", c_i32),
+        ("alpha_left", c_i32), ("alpha_right", c_i32),
+        ("left_flux", c_ptr), ("right_flux", c_ptr),
+    ]
+
+
+class FvmError(RuntimeError):
+    def __init__(self, status, where):
+        self.status = status
+        msg = lib().fvm_status_string(status).decode()
+        super().__init__("%s failed with status %d: %s" % (where, status, msg))
+
+
+_SIGNATURES = {
+    "fvm_version": (ctypes.c_int, []),
+    "fvm_status_string": (ctypes.c_char_p, [ctypes.c_int]),
+    "fvm_assemble": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                    c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
+    "fvm_theta_factor": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_dbl,
+                                        c_i32, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64,
+                                        c_ptr, c_ptr, c_ptr]),
+    "fvm_theta_step_thomas": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_dbl,
+                                             c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr]),
+    "fvm_fused_max_cells": (c_i64, []),
+    "fvm_theta_run_fused": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_dbl, c_i64, c_i64,
+                                           c_ptr, c_ptr, c_ptr]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded shared library (raises if it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "%s is missing: build it with `python -m fvm_b200.build` (needs nvcc). "
+                "fvm_b200 has no CPU fallback." % LIB_PATH)
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)          # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def exported_symbols():
+    return sorted(_SIGNATURES)
+
+
+def require_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        raise RuntimeError("fvm_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    return torch
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda or t.dtype.is_floating_point and t.element_size() != 8:
+        raise TypeError("expected a CUDA float64 tensor")
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    import torch
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def check(status, where):
+    if status != FVM_OK:
+        raise FvmError(status, where)

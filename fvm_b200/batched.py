@@ -1,0 +1,294 @@
+"""Batches of independent advection-diffusion problems on one mesh, on the GPU.
+
+This is the accelerated entry the reference's driver idiom maps to
+(fvm_classes.py:367-377,408-411): construct, set boundary conditions, then
+``run(w, theta, nsteps)`` instead of the ``spsolve`` loop.  State and coefficients
+are torch CUDA float64 tensors; all arithmetic happens in libfvm_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import _lib
+
+
+def _bc_kinds(left_flux, right_flux, left_value, right_value):
+    """Row type of each end.  A value beats a flux when both are given
+    (fvm_classes.py:277-287); an end with neither raises UnboundLocalError like the
+    reference does at :304."""
+    if left_value is not None:
+        left = _lib.BC_DIRICHLET
+    elif left_flux is not None:
+        left = _lib.BC_ROBIN
+    else:
+        raise UnboundLocalError("left boundary condition is not set (fvm_classes.py:260,304)")
+    if right_value is not None:
+        right = _lib.BC_DIRICHLET
+    elif right_flux is not None:
+        right = _lib.BC_ROBIN
+    else:
+        raise UnboundLocalError("right boundary condition is not set (fvm_classes.py:260,304)")
+    return left, right
+
+
+def _alpha_ends(left_flux, left_kind, right_kind, strict_bc):
+    """End entries of the alpha mask.  The reference keys BOTH ends off
+    ``left_flux is None`` (fvm_classes.py:237-238); strict_bc keys each end off its own row."""
+    if strict_bc:
+        return int(left_kind == _lib.BC_ROBIN), int(right_kind == _lib.BC_ROBIN)
+    a1 = 0 if left_flux is None else 1
+    return a1, a1
+
+
+class BatchedAdvectionDiffusionModel(object):
+    """P problems on one mesh.
+
+    faces : (J+1,) array-like.
+    a, d  : scalar, (P,) per-problem scalars, (J,) per-cell shared, or (P, J).
+    k     : time step (the reference's 4th positional argument, fvm_classes.py:92,351);
+            scalar or (P,).
+    reaction : optional decay rate, same shapes as a (not in the reference).
+    """
+
+    def __init__(self, faces, a, d, k, discretisation="central", P=None, reaction=None,
+                 strict_bc=False, device=None):
+        torch = _lib.require_cuda()
+        _lib.lib()
+        if discretisation not in _lib.SCHEMES:
+            raise AttributeError("discretisation must be one of `upwind`, `central` or `exponential` "
+                                 "(the reference fails on self.kappa, fvm_classes.py:128,131)")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None \
+            else torch.device(device)
+        self.discretisation = discretisation
+        self.strict_bc = strict_bc
+        self.faces = self._dev(faces).reshape(-1)
+        self.J = int(self.faces.numel()) - 1
+        if self.J < 3:
+            raise IndexError("at least 3 cells are needed (the reference fails at fvm_classes.py:292)")
+        if P is None:                      # infer the batch size: k first, then 2-D, then 1-D != J
+            shapes = [tuple(np.shape(x)) for x in (k, a, d)]
+            P = 1
+            for s in reversed(shapes[1:]):
+                if len(s) == 1 and s[0] != self.J:
+                    P = s[0]
+            for s in reversed(shapes[1:]):
+                if len(s) == 2:
+                    P = s[0]
+            if len(shapes[0]) == 1:
+                P = shapes[0][0]
+        self.P = int(P)
+        self.a, self._a_str = self._cellvar(a)
+        self.d, self._d_str = self._cellvar(d)
+        self.reaction, self._r_str = (None, (0, 0)) if reaction is None else self._cellvar(reaction)
+        kk = self._dev(k).reshape(-1)
+        self.k = kk.expand(self.P).contiguous() if kk.numel() == 1 else kk.contiguous()
+        if self.k.numel() != self.P:
+            raise ValueError("k must be a scalar or have one entry per problem")
+        self._asm = None
+        self._factors = {}
+        self._pr = None
+
+    # ------------------------------------------------------------------ helpers
+    def _dev(self, x):
+        torch = _lib.require_cuda()
+        if isinstance(x, torch.Tensor):
+            return x.to(device=self.device, dtype=torch.float64)
+        return torch.as_tensor(np.asarray(x, dtype=np.float64), device=self.device)
+
+    def _cellvar(self, x):
+        """Tensor and (problem stride, cell stride) of a coefficient."""
+        t = self._dev(x)
+        if t.ndim == 0:
+            return t.reshape(1).contiguous(), (0, 0)
+        if t.ndim == 1 and t.numel() == self.P:          # (when P == J a 1-D array is per problem)
+            return t.contiguous(), (1, 0)
+        if t.ndim == 1 and t.numel() == self.J:
+            return t.contiguous(), (0, 1)
+        if t.ndim == 2 and tuple(t.shape) == (self.P, self.J):
+            return t.contiguous(), (self.J, 1)
+        raise ValueError("coefficient must be scalar, (P,), (J,) or (P, J); got %s" % (tuple(t.shape),))
+
+    def _flux(self, x):
+        t = self._dev(x).reshape(-1)
+        t = t.expand(self.P).contiguous() if t.numel() == 1 else t.contiguous()
+        if t.numel() != self.P:
+            raise ValueError("a boundary flux must be a scalar or have one entry per problem")
+        return t
+
+    def set_boundary_conditions(self, left_flux=None, right_flux=None, left_value=None, right_value=None):
+        """Same keywords as the reference (fvm_classes.py:141-147).  Fluxes may be per
+        problem; Dirichlet values are only flags, exactly as in the reference: a Dirichlet
+        cell keeps whatever the initial state holds there."""
+        self.left_flux, self.right_flux = left_flux, right_flux
+        self.left_value, self.right_value = left_value, right_value
+        self._asm = None
+        self._factors = {}
+        self._pr = None
+
+    def _problem(self):
+        if getattr(self, "_pr", None) is not None:
+            return self._pr
+        if not hasattr(self, "left_flux"):
+            raise AttributeError("boundary conditions are not set: call set_boundary_conditions first")
+        lk, rk = _bc_kinds(self.left_flux, self.right_flux, self.left_value, self.right_value)
+        al, ar = _alpha_ends(self.left_flux, lk, rk, self.strict_bc)
+        self._lf = self._flux(self.left_flux) if lk == _lib.BC_ROBIN else None
+        self._rf = self._flux(self.right_flux) if rk == _lib.BC_ROBIN else None
+        pr = _lib.FvmProblem()
+        pr.J, pr.P = self.J, self.P
+        pr.faces = self.faces.data_ptr()
+        pr.a, (pr.a_ps, pr.a_cs) = self.a.data_ptr(), self._a_str
+        pr.d, (pr.d_ps, pr.d_cs) = self.d.data_ptr(), self._d_str
+        if self.reaction is not None:
+            pr.reaction, (pr.r_ps, pr.r_cs) = self.reaction.data_ptr(), self._r_str
+        pr.scheme = _lib.SCHEMES[self.discretisation]
+        pr.left_kind, pr.right_kind = lk, rk
+        pr.alpha_left, pr.alpha_right = al, ar
+        pr.left_flux = self._lf.data_ptr() if self._lf is not None and bool((self._lf != 0).any()) else None
+        pr.right_flux = self._rf.data_ptr() if self._rf is not None and bool((self._rf != 0).any()) else None
+        self._pr = pr
+        return pr
+
+    # ------------------------------------------------------------------ assembly
+    def assemble(self, interleaved=False):
+        """kappa, modified D, the diagonals of M and the end entries of beta, from
+        fvm_assemble.  Tensors are (P, J), or (J, P) when ``interleaved``."""
+        torch = _lib.require_cuda()
+        key = bool(interleaved)
+        if self._asm is not None and key in self._asm:
+            return self._asm[key]
+        pr = self._problem()
+        shape = (self.J, self.P) if interleaved else (self.P, self.J)
+        ps, cs = (1, self.P) if interleaved else (self.J, 1)
+        with torch.cuda.device(self.device):
+            out = {n: torch.empty(shape, dtype=torch.float64, device=self.device)
+                   for n in ("lo", "di", "up", "kappa", "D")}
+            out["beta_left"] = torch.empty(self.P, dtype=torch.float64, device=self.device)
+            out["beta_right"] = torch.empty(self.P, dtype=torch.float64, device=self.device)
+            st = _lib.lib().fvm_assemble(ctypes.byref(pr), _lib.ptr(out["lo"]), _lib.ptr(out["di"]),
+                                         _lib.ptr(out["up"]), _lib.ptr(out["kappa"]), _lib.ptr(out["D"]),
+                                         ps, cs, _lib.ptr(out["beta_left"]), _lib.ptr(out["beta_right"]),
+                                         _lib.stream_ptr())
+        _lib.check(st, "fvm_assemble")
+        out["alpha_left"], out["alpha_right"] = pr.alpha_left, pr.alpha_right
+        if self._asm is None:
+            self._asm = {}
+        self._asm[key] = out
+        return out
+
+    # ------------------------------------------------------------------ variant 1
+    def factor(self, theta):
+        """Factored theta operators in the interleaved layout (fvm_theta_factor)."""
+        torch = _lib.require_cuda()
+        theta = float(theta)
+        if theta in self._factors:
+            return self._factors[theta]
+        asm = self.assemble(interleaved=True)
+        with torch.cuda.device(self.device):
+            f = {n: torch.empty((self.J, self.P), dtype=torch.float64, device=self.device)
+                 for n in ("fp", "fq", "fb")}
+            f["bt_left"] = torch.empty(self.P, dtype=torch.float64, device=self.device)
+            f["bt_right"] = torch.empty(self.P, dtype=torch.float64, device=self.device)
+            st = _lib.lib().fvm_theta_factor(
+                self.J, self.P, _lib.ptr(asm["lo"]), _lib.ptr(asm["di"]), _lib.ptr(asm["up"]), 1, self.P,
+                _lib.ptr(self.k), theta, asm["alpha_left"], asm["alpha_right"],
+                _lib.ptr(asm["beta_left"]), _lib.ptr(asm["beta_right"]),
+                _lib.ptr(f["fp"]), _lib.ptr(f["fq"]), _lib.ptr(f["fb"]), 1, self.P,
+                _lib.ptr(f["bt_left"]), _lib.ptr(f["bt_right"]), _lib.stream_ptr())
+        _lib.check(st, "fvm_theta_factor")
+        self._factors[theta] = f
+        return f
+
+    def step_thomas_(self, w_t, theta, nsteps=1):
+        """Variant 1 on an interleaved state w_t (J, P), in place."""
+        torch = _lib.require_cuda()
+        f = self.factor(theta)
+        if tuple(w_t.shape) != (self.J, self.P) or not w_t.is_contiguous():
+            raise ValueError("interleaved state must be a contiguous (J, P) tensor")
+        with torch.cuda.device(self.device):
+            st = _lib.lib().fvm_theta_step_thomas(
+                self.J, self.P, _lib.ptr(f["fp"]), _lib.ptr(f["fq"]), _lib.ptr(f["fb"]), 1, self.P,
+                float(theta), _lib.ptr(f["bt_left"]), _lib.ptr(f["bt_right"]), _lib.ptr(w_t), 1, self.P,
+                int(nsteps), _lib.stream_ptr())
+        _lib.check(st, "fvm_theta_step_thomas")
+        return w_t
+
+    # ------------------------------------------------------------------ variant 2
+    def run_fused_(self, w, theta, nsteps, checkpoint_every=0, ckpt=None):
+        """Variant 2 on a problem-major state w (P, J), in place; optional checkpoints
+        tensor (nsteps // checkpoint_every, P, J)."""
+        torch = _lib.require_cuda()
+        if tuple(w.shape) != (self.P, self.J) or not w.is_contiguous():
+            raise ValueError("state must be a contiguous (P, J) tensor")
+        pr = self._problem()
+        with torch.cuda.device(self.device):
+            st = _lib.lib().fvm_theta_run_fused(ctypes.byref(pr), _lib.ptr(self.k), float(theta), int(nsteps),
+                                                int(checkpoint_every), _lib.ptr(w), _lib.ptr(ckpt),
+                                                _lib.stream_ptr())
+        _lib.check(st, "fvm_theta_run_fused")
+        return w
+
+    # ------------------------------------------------------------------ public driver
+    def run(self, w, theta, nsteps, checkpoint_every=0, variant="auto"):
+        """Advance w (P, J) by ``nsteps`` theta steps; returns (w_final, checkpoints or None).
+        Equivalent of the loop  d = (I + k*(1-theta)*alpha*M)*w + beta ; w = spsolve(A, d)
+        (fvm_classes.py:408-411) for every problem of the batch.
+        variant: 'fused' (on-chip, J <= fused_max_cells), 'thomas' (streaming), or 'auto'."""
+        torch = _lib.require_cuda()
+        w = self._dev(w).reshape(self.P, self.J).clone()
+        nsteps = int(nsteps)
+        ce = int(checkpoint_every or 0)
+        n_ck = nsteps // ce if ce > 0 else 0
+        ckpt = torch.empty((n_ck, self.P, self.J), dtype=torch.float64, device=self.device) if n_ck else None
+        if variant == "auto":
+            variant = "fused" if self.J <= int(_lib.lib().fvm_fused_max_cells()) else "thomas"
+        if variant == "fused":
+            self.run_fused_(w, theta, nsteps, ce, ckpt)
+        elif variant == "thomas":
+            w_t = w.t().contiguous()
+            if n_ck:
+                for i in range(n_ck):
+                    self.step_thomas_(w_t, theta, ce)
+                    ckpt[i].copy_(w_t.t())
+                rest = nsteps - n_ck * ce
+                if rest:
+                    self.step_thomas_(w_t, theta, rest)
+            else:
+                self.step_thomas_(w_t, theta, nsteps)
+            w = w_t.t().contiguous()
+        else:
+            raise ValueError("variant must be 'auto', 'fused' or 'thomas'")
+        return w, ckpt
+
+    def run_host(self, w_host, theta, nsteps, out=None, variant="auto"):
+        """Host-buffer form of :meth:`run`: ``w_host`` (P, J) lives in host memory (numpy array
+        or CPU tensor; pinned memory makes the copies asynchronous and fast).  Copies it to the
+        device, advances it ``nsteps`` theta steps, copies the result into ``out`` (allocated
+        pinned if None) and waits for it.  This is what a caller that keeps its state on the
+        host -- like every script written against the reference -- pays per call."""
+        torch = _lib.require_cuda()
+        if isinstance(w_host, np.ndarray):
+            w_host = torch.from_numpy(np.ascontiguousarray(w_host, dtype=np.float64))
+        w_host = w_host.reshape(self.P, self.J)
+        if getattr(self, "_stage", None) is None:
+            self._stage = torch.empty((self.P, self.J), dtype=torch.float64, device=self.device)
+        if out is None:
+            out = torch.empty((self.P, self.J), dtype=torch.float64).pin_memory()
+        elif isinstance(out, np.ndarray):
+            out = torch.from_numpy(out)
+        with torch.cuda.device(self.device):
+            self._stage.copy_(w_host, non_blocking=True)
+            if variant == "auto":
+                variant = "fused" if self.J <= int(_lib.lib().fvm_fused_max_cells()) else "thomas"
+            if variant == "fused":
+                self.run_fused_(self._stage, theta, nsteps)
+                res = self._stage
+            else:
+                w_t = self._stage.t().contiguous()
+                self.step_thomas_(w_t, theta, nsteps)
+                res = w_t.t()
+            out.copy_(res, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        return out

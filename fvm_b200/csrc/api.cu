@@ -1,0 +1,16 @@
+// Status strings and version of the C-ABI (include/fvm_b200.h).
+#include <cuda_runtime.h>
+#include "../../include/fvm_b200.h"
+
+extern "C" int fvm_version(void) { return 100; }  // 0.1.0
+
+extern "C" const char* fvm_status_string(int status) {
+  switch (status) {
+    case FVM_OK: return "ok";
+    case FVM_ERR_INVALID_ARG: return "invalid argument (NULL pointer, J < 3, P < 1, theta outside (0, 1] or bad enum)";
+    case FVM_ERR_UNSUPPORTED: return "size not supported by this entry point";
+    default: break;
+  }
+  if (status > 0) return cudaGetErrorString((cudaError_t)status);
+  return "unknown fvm_b200 status";
+}

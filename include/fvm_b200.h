@@ -1,0 +1,129 @@
+/* fvm_b200 -- C-ABI of the B200-native FVM theta-step hot path.
+ *
+ * The reference (danieljfarrell/FVM) is pure Python: it has no FFI of its own.
+ * Each entry point below replaces a piece of the reference's Python/scipy path
+ * (cited as fvm_classes.py:LINE) and is what a binding for that path would call;
+ * INTEGRATION.md shows the ctypes stub.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer to fp64 data unless stated otherwise;
+ *  - the caller owns every buffer; the library allocates nothing and keeps no
+ *    state between calls; all work is enqueued on `stream` (a CUstream /
+ *    cudaStream_t handle passed as void*; NULL = the legacy default stream) and
+ *    no call synchronises the host;
+ *  - strided arrays: element (problem p, cell j) of X lives at X[p*X_ps + j*X_cs]
+ *    (strides in elements).  Problem-major [P][J] is (ps=J, cs=1); interleaved
+ *    [J][P] is (ps=1, cs=P); a per-problem scalar is (ps=1, cs=0); one array
+ *    shared by all problems is (ps=0, cs=1);
+ *  - return value: 0 = FVM_OK, < 0 = FVM_ERR_* (bad argument, nothing was
+ *    launched), > 0 = a cudaError_t from the launch.  Nothing throws.
+ */
+#ifndef FVM_B200_H
+#define FVM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FVM_OK 0
+#define FVM_ERR_INVALID_ARG (-1)  /* NULL pointer, J < 3, P < 1, theta outside (0, 1], bad enum */
+#define FVM_ERR_UNSUPPORTED (-2)  /* size outside what this entry point handles               */
+
+/* discretisation of the advective flux [fvm_classes.py:116-128] */
+#define FVM_CENTRAL 0
+#define FVM_UPWIND 1
+#define FVM_EXPONENTIAL 2
+
+/* which row an end of the mesh gets [fvm_classes.py:156-177 Robin, :191-216 Dirichlet] */
+#define FVM_BC_DIRICHLET 0
+#define FVM_BC_ROBIN 1
+
+/* One batch of P advection-diffusion problems on ONE shared mesh.
+ * Mirrors the constructor + set_boundary_conditions of AdvectionDiffusionModel
+ * [fvm_classes.py:92-98,141-147].  Host struct holding device pointers. */
+typedef struct fvm_problem {
+  int64_t J;              /* cells (>= 3: the reference fails below that, fvm_classes.py:292) */
+  int64_t P;              /* independent problems                                            */
+  const double* faces;    /* [J+1] face positions, shared by all problems [:38]               */
+  const double* a;        /* advection velocity  a[p*a_ps + j*a_cs]        [:96]              */
+  int64_t a_ps, a_cs;
+  const double* d;        /* diffusion coefficient (unmodified)            [:97]              */
+  int64_t d_ps, d_cs;
+  const double* reaction; /* optional decay rate r >= 0 (dw/dt = ... - r w); NULL = none.
+                             Not in the reference: -r is added to the diagonal
+                             of M on rows that are not Dirichlet rows.                          */
+  int64_t r_ps, r_cs;
+  int32_t scheme;         /* FVM_CENTRAL | FVM_UPWIND | FVM_EXPONENTIAL                       */
+  int32_t left_kind;      /* FVM_BC_DIRICHLET | FVM_BC_ROBIN: row 0 of M                      */
+  int32_t right_kind;     /* ... row J-1 of M                                                 */
+  int32_t alpha_left;     /* end entries (0 or 1) of the alpha mask [:237-241].  The reference */
+  int32_t alpha_right;    /* sets BOTH from `left_flux is None`; the host layer reproduces that */
+  const double* left_flux;  /* [P] Robin flux at the left end  (beta[0]   =  flux/h[0],   :182); NULL = 0 */
+  const double* right_flux; /* [P] Robin flux at the right end (beta[J-1] = -flux/h[J-1], :188); NULL = 0 */
+} fvm_problem;
+
+/* Library version (major*10000 + minor*100 + patch). */
+int fvm_version(void);
+
+/* Text for a status code returned by any entry point (static storage). */
+const char* fvm_status_string(int status);
+
+/* kappa, modified diffusivity D, and the three diagonals of M = coefficient_matrix().
+ * Replaces AdvectionDiffusionModel.__init__ (kappa, D = d + a h kappa / 2,
+ * fvm_classes.py:116-131), _interior_matrix_elements (:149-154), the Robin and
+ * Dirichlet row builders (:156-231), beta_vector (:244-263) and coefficient_matrix
+ * (:265-310).  M[j][j-1] = lo, M[j][j] = di, M[j][j+1] = up (lo at j=0 and up at
+ * j=J-1 are written as 0).  central/upwind results are bit-identical to the
+ * reference's numpy arithmetic; the exponential scheme evaluates
+ * D = d (B(mu) + mu/2), B = mu/expm1(mu) (cancellation- and overflow-safe; the
+ * reference's formula, :117, returns NaN for mu >= 709.8).
+ * lo/di/up/kappa/D use strides (out_ps, out_cs); kappa and D may be NULL.
+ * beta_left/beta_right: [P], beta[0] and beta[J-1] (beta is 0 elsewhere); may be NULL. */
+int fvm_assemble(const fvm_problem* prob, double* lo, double* di, double* up, double* kappa,
+                 double* D, int64_t out_ps, int64_t out_cs, double* beta_left,
+                 double* beta_right, void* stream);
+
+/* Factor the theta-method operators once per model.  Replaces
+ *   A = I - k*theta*alpha*M ;  B = I + k*(1-theta)*alpha*M      [fvm_classes.py:373-377]
+ * and the per-step SuperLU factorisation inside spsolve (:411).
+ * In : M diagonals (strides m_ps, m_cs), dt[P] (the reference's `k`), theta in (0, 1],
+ *      alpha end entries, beta_left/right [P] (may be NULL = 0).
+ * Out: fp, fq, fb (strides f_ps, f_cs), bt_left/bt_right [P]:
+ *        inv_j = 1/(A_jj - A_j,j-1 * fq_{j-1});  fp_j = A_j,j-1 * inv_j;  fq_j = A_j,j+1 * inv_j;
+ *        fb_j  = inv_j * B_jj;   bt = beta * inv  at the two ends.
+ *      With c = (1-theta)/theta the off-diagonals of inv*B are -c*fp and -c*fq, so the
+ *      three arrays carry both operators. */
+int fvm_theta_factor(int64_t J, int64_t P, const double* lo, const double* di, const double* up,
+                     int64_t m_ps, int64_t m_cs, const double* dt, double theta,
+                     int32_t alpha_left, int32_t alpha_right, const double* beta_left,
+                     const double* beta_right, double* fp, double* fq, double* fb,
+                     int64_t f_ps, int64_t f_cs, double* bt_left, double* bt_right, void* stream);
+
+/* Variant 1: `nsteps` theta steps, one thread per system, state updated IN PLACE.
+ * Replaces the loop body  rhs = B*w + beta ; w = spsolve(A, rhs)  [fvm_classes.py:408-411].
+ * Streams fp/fq/fb and w from HBM every step; use the interleaved layout (ps=1, cs=P)
+ * for both so that a warp's accesses coalesce.  Any J >= 3. */
+int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, const double* fq,
+                          const double* fb, int64_t f_ps, int64_t f_cs, double theta,
+                          const double* bt_left, const double* bt_right, double* w, int64_t w_ps,
+                          int64_t w_cs, int64_t nsteps, void* stream);
+
+/* Largest J the fused on-chip variant accepts. */
+int64_t fvm_fused_max_cells(void);
+
+/* Variant 2: assembly + factorisation + `nsteps` theta steps in ONE launch, one warp per
+ * system, state in registers and coefficients in shared memory; HBM is touched when the
+ * state is loaded, at checkpoints, and when it is stored.  Replaces the whole of
+ * fvm_classes.py:367-377,408-411 for a batch.  J <= fvm_fused_max_cells().
+ * w: [P][J] problem-major, in/out.  dt: [P].
+ * checkpoint_every > 0: after every that many steps the state is also written to
+ * ckpt[(n-1)*P*J + p*J + j], n = 1..nsteps/checkpoint_every (ckpt may be NULL: none). */
+int fvm_theta_run_fused(const fvm_problem* prob, const double* dt, double theta, int64_t nsteps,
+                        int64_t checkpoint_every, double* w, double* ckpt, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FVM_B200_H */

@@ -1,0 +1,109 @@
+"""Host-side logic and the C-ABI surface, without a GPU."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import fvm_b200
+from fvm_b200 import _lib, workloads as W
+from fvm_b200.batched import _alpha_ends, _bc_kinds
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    """Every function include/fvm_b200.h declares is exported by the built library and
+    bound with a signature in fvm_b200/_lib.py."""
+    hdr = open(os.path.join(ROOT, "include", "fvm_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(fvm_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.exported_symbols())
+    handle = _lib.lib()                       # raises if the .so is missing
+    for name in declared:
+        assert hasattr(handle, name)
+    assert handle.fvm_version() >= 100
+    assert handle.fvm_fused_max_cells() >= 1024
+    assert b"invalid" in handle.fvm_status_string(_lib.FVM_ERR_INVALID_ARG)
+
+
+def test_argument_validation_needs_no_gpu():
+    """Bad arguments are rejected before anything is launched."""
+    handle = _lib.lib()
+    pr = _lib.FvmProblem()
+    assert handle.fvm_assemble(ctypes.byref(pr), None, None, None, None, None, 1, 1, None, None, None) \
+        == _lib.FVM_ERR_INVALID_ARG
+    assert handle.fvm_theta_run_fused(ctypes.byref(pr), None, 0.5, 1, 0, None, None, None) \
+        == _lib.FVM_ERR_INVALID_ARG
+    assert handle.fvm_theta_step_thomas(2, 1, None, None, None, 1, 1, 0.5, None, None, None, 1, 1, 1, None) \
+        == _lib.FVM_ERR_INVALID_ARG
+
+
+def test_struct_layout_matches_header():
+    # 2 + 1 + 3*3 int64/pointer fields, 5 int32 (+4 pad), 2 pointers
+    assert ctypes.sizeof(_lib.FvmProblem) == 8 * 12 + 4 * 5 + 4 + 8 * 2
+
+
+def test_mesh_and_cellvariable():
+    f = np.array([0.0, 0.1, 0.4, 0.5, 1.0])
+    m = fvm_b200.Mesh(f)
+    assert m.J == 4 and np.allclose(m.cells, [0.05, 0.25, 0.45, 0.75])
+    assert np.allclose(m.cell_widths, [0.1, 0.3, 0.1, 0.5])
+    assert m.h(1) == pytest.approx(0.3) and m.hm(1) == pytest.approx(0.2) and m.hp(1) == pytest.approx(0.2)
+    with pytest.raises(ValueError):
+        m.hm(0)                                               # fvm_classes.py:49-50
+    with pytest.raises(ValueError):
+        m.hp(3)                                               # :55-56
+    with pytest.raises(ValueError):
+        fvm_b200.Mesh([0, 0.5, 0.5, 1])                       # :36-37
+    fvm_b200.Mesh([0, 0.6, 0.3, 1])                           # unsorted faces are accepted, like the reference
+    v = fvm_b200.CellVariable(2.0, mesh=m)
+    assert v.shape == (4,) and np.all(v == 2.0) and (v * 3).mesh is m
+    u = fvm_b200.CellVariable(np.array([1.0, 2.0, 4.0, 8.0]), mesh=m)
+    i = np.array([1, 2])
+    # p(i) and m(i+1) are the same face
+    assert np.allclose(u.p(i), u.m(i + 1))
+    assert u.m(1) == pytest.approx(0.3 / 0.4 * 1.0 + 0.1 / 0.4 * 2.0)
+
+
+def test_bc_resolution_and_alpha_quirk():
+    assert _bc_kinds(None, None, 1.0, 0.0) == (_lib.BC_DIRICHLET, _lib.BC_DIRICHLET)
+    assert _bc_kinds(0.0, 0.0, None, None) == (_lib.BC_ROBIN, _lib.BC_ROBIN)
+    assert _bc_kinds(0.0, 0.0, 1.0, None) == (_lib.BC_DIRICHLET, _lib.BC_ROBIN)   # value beats flux
+    with pytest.raises(UnboundLocalError):
+        _bc_kinds(None, None, None, None)
+    # both ends follow left_flux (fvm_classes.py:237-238)
+    assert _alpha_ends(None, _lib.BC_DIRICHLET, _lib.BC_ROBIN, False) == (0, 0)
+    assert _alpha_ends(0.0, _lib.BC_ROBIN, _lib.BC_DIRICHLET, False) == (1, 1)
+    assert _alpha_ends(0.0, _lib.BC_ROBIN, _lib.BC_DIRICHLET, True) == (1, 0)
+
+
+def test_product_fails_loudly_without_cuda():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        fvm_b200.BatchedAdvectionDiffusionModel(np.linspace(0, 1, 9), 1.0, 1.0, 0.1)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        fvm_b200.AdvectionDiffusionModel(np.linspace(0, 1, 9), 1.0, 1.0, 0.1)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "fvm_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, fn)).read()
+                assert "oracle" not in text or fn == "workloads.py", fn
+
+
+def test_workloads_are_shard_invariant():
+    full = W.batched_sweep(64, 32)
+    part = W.batched_sweep(64, 32, first=16, count=8)
+    for key in ("a", "d", "k", "w0"):
+        assert np.array_equal(full[key][16:24], part[key])
+    f = W.graded_faces(1024)
+    h = np.diff(f)
+    assert f[0] == 0 and abs(f[-1] - 1) < 1e-15 and abs(h[0] / h[-1] - 100) < 1e-9
