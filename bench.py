@@ -29,8 +29,9 @@ sys.path.insert(0, ROOT)
 METRIC = "fp64 cell-updates/sec (theta-step)"
 UNIT = "cell-updates/s"
 # algorithmic work per cell-update of the fused on-chip variant
-FLOP_PER_CELL_UPDATE = 11.0          # RHS 3 FMA, forward 1 FMA, backward 1 FMA + 1 MUL
-SMEM_B_PER_CELL_UPDATE = 40.0        # five factored coefficients (p, q, b, v, u) read once per step
+FLOP_PER_CELL_UPDATE = 11.0          # RHS 3 FMA, forward 1 FMA, backward 1 FMA + 1 MUL (SURVEY.md 8(d))
+FP64_INSTR_PER_CELL_UPDATE = 7.0     # what the partitioned on-chip solver issues: + 2 spike-correction FMAs
+ONCHIP_B_PER_CELL_UPDATE = 40.0      # five factored coefficients read once per step (32 B TMEM + 8 B registers)
 HBM_B_PER_CELL_UPDATE_THOMAS = 64.0  # variant 1: w, fp, fq, fb in; g out; g, fq in; w out
 
 
@@ -281,25 +282,32 @@ def run_b200(args):
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (fused_kernel): on-chip bound
+    # ---- roofline of the dominant kernel (fused_tmem_kernel): it touches HBM only at launch
+    # boundaries, so the bound is on chip.  Coefficients come from tensor memory and registers
+    # (not shared memory), which leaves the fp64 pipe as the binding unit: 64 DFMA/clk/SM,
+    # measured on this GPU type by profiles/microbench/fp64_peak.cu (r01_fp64_peak_b200.txt).
     f_clk = (clocks.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)) * 1e6
     f_max = peaks.get("sm_max_mhz", 1965.0) * 1e6
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
     cu_s_kernel = cu_per_step_rank / (kernel_ms * 1e-3)
-    smem_peak = sms * 128.0 * f_max / 1e9                      # GB/s at max clock
     fp64_peak = sms * 64.0 * 2.0 * f_max / 1e12                # TFLOP/s at max clock
-    smem_ach = SMEM_B_PER_CELL_UPDATE * cu_s_kernel / 1e9
     fp64_ach = FLOP_PER_CELL_UPDATE * cu_s_kernel / 1e12
-    roofline = {"kernel": "fused_kernel<32,CN> (variant 2)", "bound": "smem",
-                "achieved": smem_ach, "peak": smem_peak, "unit": "GB/s", "frac": smem_ach / smem_peak,
-                "traffic": None,
-                "peak_source": "nominal: %d SMs x 128 B/clk x %.0f MHz (max SM clock, %s); HBM is not the "
-                               "bound: the kernel touches HBM only at launch boundaries" % (sms, f_max / 1e6, peak_src),
-                "algorithmic_bytes_per_cell_update": SMEM_B_PER_CELL_UPDATE,
-                "frac_at_observed_clock": smem_ach / (sms * 128.0 * f_clk / 1e9),
-                "fp64": {"achieved": fp64_ach, "peak": fp64_peak, "unit": "TFLOP/s", "frac": fp64_ach / fp64_peak,
-                         "flop_per_cell_update": FLOP_PER_CELL_UPDATE,
-                         "peak_source": "nominal: %d SMs x 64 FMA/clk x 2 x %.0f MHz" % (sms, f_max / 1e6)},
+    issue_frac = FP64_INSTR_PER_CELL_UPDATE * cu_s_kernel / (sms * 32.0 * f_clk)   # warp-DFMA slots: 64 lanes/clk = 2 cycles per warp instruction
+    smem_peak = sms * 128.0 * f_max / 1e9
+    onchip = ONCHIP_B_PER_CELL_UPDATE * cu_s_kernel / 1e9
+    roofline = {"kernel": "fused_tmem_kernel<CN> (variant 2: state in registers, coefficients in TMEM)",
+                "bound": "fp64", "achieved": fp64_ach, "peak": fp64_peak, "unit": "TFLOP/s",
+                "frac": fp64_ach / fp64_peak, "traffic": None,
+                "peak_source": "%d SMs x 64 DFMA/clk x 2 flop x %.0f MHz (max SM clock, %s); the 64 DFMA/clk/SM rate is "
+                               "measured (profiles/microbench/r01_fp64_peak_b200.txt)" % (sms, f_max / 1e6, peak_src),
+                "flop_per_cell_update": FLOP_PER_CELL_UPDATE,
+                "fp64_pipe_issue_frac": issue_frac,
+                "fp64_instr_per_cell_update": FP64_INSTR_PER_CELL_UPDATE,
+                "onchip_coefficient_traffic": {"achieved": onchip, "unit": "GB/s", "bytes_per_cell_update": ONCHIP_B_PER_CELL_UPDATE,
+                                               "shared_memory_peak": smem_peak,
+                                               "note": "coefficient reads served by TMEM (tcgen05.ld) and registers; exceeds what "
+                                                       "the 128 B/clk/SM shared-memory pipe could deliver when frac > 1",
+                                               "frac_of_shared_memory_peak": onchip / smem_peak},
                 "hbm": {"achieved": 16.0 * P * J / (kernel_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                         "note": "state read once + written once per launch of %d steps" % inner},
                 "kernel_ms_per_launch": kernel_ms, "cell_updates_per_launch": cu_per_step_rank}

@@ -8,13 +8,25 @@
 //   3. reduced system on the 32 separators  precomputed parallel cyclic reduction, 5 levels
 //                                           of 2 shuffles + 2 FMA, no divisions
 //   4. x = g - v*xs(l-1) - u*xs(l)          2 FMA / cell   (v, u = left/right spikes T^-1 e)
-// State w[C] lives in registers for the whole launch; the five per-cell coefficients
-// (p, q, b, v, u) live in shared memory as [coef][c][lane] (lane-consecutive doubles:
-// conflict-free).  HBM traffic: J doubles in, J doubles out, J per checkpoint.
+// State w[C] lives in registers for the whole launch.  Five coefficients per interior cell
+// (p, q, b, v, u) must be read every step; where they live decides the speed, because a
+// step is bound by on-chip bandwidth, not arithmetic:
+//   * fused_kernel      (any J <= 1024): q in registers, p/b/v/u in shared memory
+//                       ([coef][c][lane], lane-consecutive doubles: conflict-free).
+//   * fused_tmem_kernel (512 < J <= 1024): q in registers, p/b/v/u in TENSOR MEMORY.
+//                       TMEM (256 KB/SM) is idle in this workload -- there is no MMA -- and
+//                       its tcgen05.ld path is separate from, and wider than, the 128 B/clk
+//                       shared-memory pipe (profiles/microbench/r01_tmem_bw_b200.txt).  Each
+//                       warp owns 256 columns of its lane quadrant: columns [0,128) hold
+//                       (p_c, b_c) pairs, [128,256) hold (v_c, u_c) pairs, 4 columns per cell.
+//                       Shared memory is only a staging area during set-up.
+// HBM traffic: J doubles in, J doubles out, J per checkpoint.
 //
 // Assembly (fvm_device.cuh) and factorisation run inside the same launch, one lane per
 // owned cell, so a launch needs only the mesh, the per-problem scalars and the state.
 #include "fvm_device.cuh"
+#include "tmem.cuh"
+#include <cstdlib>
 
 namespace fvm {
 
@@ -25,10 +37,164 @@ constexpr int kFusedThreads = 256;   // upper bound used for register allocation
 __device__ __forceinline__ double shfl_up(double x, int s) { return __shfl_up_sync(kFull, x, s); }
 __device__ __forceinline__ double shfl_dn(double x, int s) { return __shfl_down_sync(kFull, x, s); }
 
-// MODE 0: any theta in (0,1];  1: Crank-Nicolson (c = (1-theta)/theta = 1);  2: implicit (c = 0).
-// RB: beta[J-1] is nonzero AND cell J-1 is an interior cell of its lane (slow path).
-// QREG: q (the one coefficient a step reads twice) is held in registers instead of shared
-//       memory: 4 instead of 6 shared-memory reads per cell-update, and 4/5 of the footprint.
+// Per-lane constants of one system, fixed for the whole launch.
+struct Reduced {
+  double al[5], ga[5];           // PCR elimination factors of the separator system, per level
+  double invD;                   // 1 / final PCR diagonal
+  double slo, sup;               // separator's row of A (off-diagonals)
+  double sblo, sbdi, sbup;       // separator's row of B
+  double bfirst, bint, bsep;     // beta entries as they enter the sweeps
+  int rb_c;                      // RB only: position of cell J-1 inside its lane
+};
+
+// Where phase 1 puts (p_c, b_c).
+struct PutSmem {
+  double* sp; double* sb;
+  __device__ __forceinline__ void operator()(int c, double p, double b) const { sp[c * 32] = p; sb[c * 32] = b; }
+};
+struct PutTmem {
+  uint32_t t_pb;
+  __device__ __forceinline__ void operator()(int c, double p, double b) const { tmem_st_2d(t_pb + 4 * c, p, b); }
+};
+
+// Phase 1: assemble this lane's rows of A, factor the interior block (p, q, b), run the
+// forward sweep of the left spike (into sv) and keep the separator's row.
+template <int C, bool RB, class Put>
+__device__ __forceinline__ void setup_rows(const fvm_problem& pr, int64_t p, int lane, double dt_p,
+                                           double theta, const Put& put, double* sq, double* sv,
+                                           Reduced& R, double& sdi) {
+  constexpr int N = C - 1;
+  const int64_t J = pr.J;
+  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
+  const double dt_theta = mul(dt_p, theta);
+  double beta_l = 0.0, beta_r = 0.0;
+  if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
+    beta_l = dvd(pr.left_flux[p], sub(pr.faces[1], pr.faces[0]));
+  if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
+    beta_r = dvd(-pr.right_flux[p], sub(pr.faces[J], pr.faces[J - 1]));
+  R.slo = 0.0; sdi = 1.0; R.sup = 0.0;
+  R.bfirst = 0.0; R.bint = 0.0; R.bsep = 0.0;
+  R.rb_c = RB ? (int)((J - 1) % C) : -1;
+  double q_prev = 0.0, gv_prev = 0.0;
+  const int64_t j0 = (int64_t)lane * C;
+  double Dm = cell_D(pr, p, j0 - 1), D0 = cell_D(pr, p, j0);     // sliding window of modified D
+#pragma unroll 1
+  for (int c = 0; c < C; ++c) {
+    const int64_t j = j0 + c;
+    const double Dp = cell_D(pr, p, j + 1);
+    Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;      // padding rows (j >= J) are identity
+    if (j < J) {
+      Row m = assemble_row_D(pr, p, j, Dm, D0, Dp);
+      a = theta_lhs_row(m, dt_theta, alpha_of(j, J, pr.alpha_left, pr.alpha_right));
+    }
+    Dm = D0; D0 = Dp;
+    if (c < N) {
+      const double inv = 1.0 / (a.di - a.lo * q_prev);
+      const double pc = a.lo * inv;
+      q_prev = a.up * inv;
+      gv_prev = (c == 0) ? pc : -pc * gv_prev;      // forward sweep of the left spike
+      put(c, pc, inv * (rth - cth * a.di));
+      sq[c * 32] = q_prev;
+      sv[c * 32] = gv_prev;
+      if (j == 0) R.bfirst = beta_l * inv;
+      if (RB && j == J - 1) R.bint = beta_r * inv;
+    } else {
+      R.slo = a.lo; sdi = a.di; R.sup = a.up;
+      if (j == 0) R.bsep += beta_l;
+      if (j == J - 1) R.bsep += beta_r;
+    }
+  }
+  R.sblo = -cth * R.slo; R.sbdi = rth - cth * sdi; R.sbup = -cth * R.sup;
+}
+
+// Parallel cyclic reduction of the 32-unknown separator system (RL, RD, RU per lane): the
+// elimination factors of each of the 5 levels and the final diagonal are kept, so that a
+// step only applies them to its right-hand side (pcr_solve).
+__device__ __forceinline__ void pcr_factor(int lane, double RL, double RD, double RU, Reduced& R) {
+#pragma unroll
+  for (int l = 0; l < 5; ++l) {
+    const int s = 1 << l;
+    const bool hm = lane >= s, hp = lane + s < 32;
+    const double Dm = shfl_up(RD, s), Dp = shfl_dn(RD, s);
+    const double Lm = shfl_up(RL, s), Um = shfl_up(RU, s);
+    const double Lp = shfl_dn(RL, s), Up = shfl_dn(RU, s);
+    const double a_ = hm ? -RL / Dm : 0.0;
+    const double g_ = hp ? -RU / Dp : 0.0;
+    R.al[l] = a_; R.ga[l] = g_;
+    RD = RD + (hm ? a_ * Um : 0.0) + (hp ? g_ * Lp : 0.0);
+    RL = hm ? a_ * Lm : 0.0;
+    RU = hp ? g_ * Up : 0.0;
+  }
+  R.invD = 1.0 / RD;
+}
+
+// Phase 2: backward sweeps of both spikes (sv: gv -> v; su <- u, reading q from sq, which
+// may alias su), the separator system and its PCR factors.
+template <int C>
+__device__ __forceinline__ void setup_reduced(int lane, const double* sq, double* sv, double* su,
+                                              double sdi, Reduced& R) {
+  constexpr int N = C - 1;
+  double RL = R.slo, RD = sdi, RU = R.sup;
+  if (N > 0) {
+    double vn = sv[(N - 1) * 32];
+    double un = sq[(N - 1) * 32];
+    su[(N - 1) * 32] = un;
+    const double vlast = vn, ulast = un;
+#pragma unroll 1
+    for (int c = N - 2; c >= 0; --c) {
+      const double qc = sq[c * 32];
+      vn = sv[c * 32] - qc * vn;
+      un = -qc * un;
+      sv[c * 32] = vn;
+      su[c * 32] = un;
+    }
+    const double v0n = shfl_dn(vn, 1), u0n = shfl_dn(un, 1);   // next lane's first interior cell
+    RL = -R.slo * vlast;
+    RD = sdi - R.slo * ulast - R.sup * v0n;         // sup == 0 on lane 31
+    RU = -R.sup * u0n;
+  }
+  pcr_factor(lane, RL, RD, RU, R);
+}
+
+template <int C>
+__device__ __forceinline__ void load_state(const double* __restrict__ src, int64_t J, int lane, double (&w)[C]) {
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int64_t j = (int64_t)lane * C + c;
+    w[c] = (j < J) ? src[j] : 0.0;
+  }
+}
+template <int C>
+__device__ __forceinline__ void store_state(double* __restrict__ dst, int64_t J, int lane, const double (&w)[C]) {
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const int64_t j = (int64_t)lane * C + c;
+    if (j < J) dst[j] = w[c];
+  }
+}
+
+// r~ of one interior cell.  MODE 0: any theta in (0,1];  1: Crank-Nicolson (c = 1);  2: implicit (c = 0).
+template <int MODE>
+__device__ __forceinline__ double rhs_cell(double pc, double qc, double bc, double wm, double wc,
+                                           double wp, double cth) {
+  if (MODE == 2) return bc * wc;
+  const double t = fma(qc, wp, pc * wm);
+  return (MODE == 1) ? fma(bc, wc, -t) : fma(-cth, t, bc * wc);
+}
+
+__device__ __forceinline__ double pcr_solve(double rr, const Reduced& R) {
+#pragma unroll
+  for (int l = 0; l < 5; ++l) {
+    const int s = 1 << l;
+    const double rm = shfl_up(rr, s), rp = shfl_dn(rr, s);
+    rr = fma(R.ga[l], rp, fma(R.al[l], rm, rr));
+  }
+  return rr * R.invD;
+}
+
+// ------------------------------------------------------------------------------------------
+// Shared-memory variant.  RB: beta[J-1] is nonzero AND cell J-1 is an interior cell of its
+// lane (slow path).  QREG: q in registers (4 instead of 6 shared-memory reads per cell-update).
 template <int C, int MODE, bool RB, bool QREG>
 __global__ void __launch_bounds__(kFusedThreads, 1)
 fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
@@ -46,104 +212,23 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
   double* su = sv + NS * 32;
   double* sq = QREG ? su : su + NS * 32;   // QREG: q is staged in u's slots during set-up only
   const int64_t J = pr.J;
-  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
+  const double cth = (1.0 - theta) / theta;
 
   for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
-    // ------------------------------------------------------------------ setup (once)
-    const double dt_theta = mul(dt[p], theta);
-    double beta_l = 0.0, beta_r = 0.0;
-    if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
-      beta_l = dvd(pr.left_flux[p], sub(pr.faces[1], pr.faces[0]));
-    if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
-      beta_r = dvd(-pr.right_flux[p], sub(pr.faces[J], pr.faces[J - 1]));
-    double slo = 0.0, sdi = 1.0, sup = 0.0;         // separator's row of A
-    double bfirst = 0.0, bint = 0.0, bsep = 0.0;    // beta entries as they enter the sweeps
-    int rb_c = -1;
-    {
-      double q_prev = 0.0, gv_prev = 0.0;
-#pragma unroll 1
-      for (int c = 0; c < C; ++c) {
-        const int64_t j = (int64_t)lane * C + c;
-        Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;  // padding rows (j >= J) are identity
-        if (j < J) {
-          double kap, Dc;
-          Row m = assemble_row(pr, p, j, kap, Dc);
-          a = theta_lhs_row(m, dt_theta, alpha_of(j, J, pr.alpha_left, pr.alpha_right));
-        }
-        if (c < N) {
-          const double inv = 1.0 / (a.di - a.lo * q_prev);
-          const double pc = a.lo * inv;
-          q_prev = a.up * inv;
-          gv_prev = (c == 0) ? pc : -pc * gv_prev;  // forward sweep of the left spike
-          sp[c * 32] = pc;
-          sq[c * 32] = q_prev;
-          sb[c * 32] = inv * (rth - cth * a.di);
-          sv[c * 32] = gv_prev;
-          if (j == 0) bfirst = beta_l * inv;
-          if (RB && j == J - 1) bint = beta_r * inv;
-        } else {
-          slo = a.lo; sdi = a.di; sup = a.up;
-          if (j == 0) bsep += beta_l;
-          if (j == J - 1) bsep += beta_r;
-        }
-      }
-      if (RB) rb_c = (int)((J - 1) % C);
-    }
-    double qr[NS];                                  // QREG: q for the whole launch
+    Reduced R;
+    double sdi;
+    setup_rows<C, RB>(pr, p, lane, dt[p], theta, PutSmem{sp, sb}, sq, sv, R, sdi);
+    double qr[NS];
     if (QREG) {
 #pragma unroll
       for (int c = 0; c < NS; ++c) qr[c] = (c < N) ? sq[c * 32] : 0.0;
     }
-    double RL = slo, RD = sdi, RU = sup;            // reduced (separator) system
-    if (N > 0) {
-      double vn = sv[(N - 1) * 32];                 // backward sweeps of both spikes
-      double un = sq[(N - 1) * 32];
-      su[(N - 1) * 32] = un;
-      const double vlast = vn, ulast = un;
-#pragma unroll 1
-      for (int c = N - 2; c >= 0; --c) {
-        const double qc = sq[c * 32];
-        vn = sv[c * 32] - qc * vn;
-        un = -qc * un;
-        sv[c * 32] = vn;
-        su[c * 32] = un;
-      }
-      const double v0n = shfl_dn(vn, 1), u0n = shfl_dn(un, 1);   // next lane's first interior cell
-      RL = -slo * vlast;
-      RD = sdi - slo * ulast - sup * v0n;           // sup == 0 on lane 31
-      RU = -sup * u0n;
-    }
-    double al[5], ga[5];                            // PCR elimination factors per level
-#pragma unroll
-    for (int l = 0; l < 5; ++l) {
-      const int s = 1 << l;
-      const bool hm = lane >= s, hp = lane + s < 32;
-      const double Dm = shfl_up(RD, s), Dp = shfl_dn(RD, s);
-      const double Lm = shfl_up(RL, s), Um = shfl_up(RU, s);
-      const double Lp = shfl_dn(RL, s), Up = shfl_dn(RU, s);
-      const double a_ = hm ? -RL / Dm : 0.0;
-      const double g_ = hp ? -RU / Dp : 0.0;
-      al[l] = a_; ga[l] = g_;
-      RD = RD + (hm ? a_ * Um : 0.0) + (hp ? g_ * Lp : 0.0);
-      RL = hm ? a_ * Lm : 0.0;
-      RU = hp ? g_ * Up : 0.0;
-    }
-    const double invD = 1.0 / RD;
-    const double sblo = -cth * slo, sbdi = rth - cth * sdi, sbup = -cth * sup;
+    setup_reduced<C>(lane, sq, sv, su, sdi, R);
     __syncwarp();
 
-    // ------------------------------------------------------------------ state in
     double w[C];
-    {
-      const double* src = w_io + p * J;
-#pragma unroll
-      for (int c = 0; c < C; ++c) {
-        const int64_t j = (int64_t)lane * C + c;
-        w[c] = (j < J) ? src[j] : 0.0;
-      }
-    }
+    load_state<C>(w_io + p * J, J, lane, w);
 
-    // ------------------------------------------------------------------ time loop
     int64_t until_ckpt = ckpt_every, n_ckpt = 0;
     for (int64_t n = 0; n < nsteps; ++n) {
       double wl = shfl_up(w[C - 1], 1);
@@ -155,36 +240,24 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
         double wm = wl, g = 0.0;
 #pragma unroll
         for (int c = 0; c < N; ++c) {
-          const double pc = sp[c * 32], bc = sb[c * 32];
+          const double pc = sp[c * 32];
           const double wc = w[c];
-          double r;
-          if (MODE == 2) {
-            r = bc * wc;
-          } else {
-            const double t = fma(QREG ? qr[c] : sq[c * 32], w[c + 1], pc * wm);
-            r = (MODE == 1) ? fma(bc, wc, -t) : fma(-cth, t, bc * wc);
-          }
-          if (c == 0) r += bfirst;
-          if (RB) { if (c == rb_c) r += bint; }
+          double r = rhs_cell<MODE>(pc, QREG ? qr[c] : sq[c * 32], sb[c * 32], wm, wc, w[c + 1], cth);
+          if (c == 0) r += R.bfirst;
+          if (RB) { if (c == R.rb_c) r += R.bint; }
           g = (c == 0) ? r : fma(-pc, g, r);
           w[c] = g;
           wm = wc;
         }
-        const double rs = fma(sbup, wr, fma(sbdi, w[C - 1], fma(sblo, wm, bsep)));
+        const double rs = fma(R.sbup, wr, fma(R.sbdi, w[C - 1], fma(R.sblo, wm, R.bsep)));
 #pragma unroll
         for (int c = N - 2; c >= 0; --c) w[c] = fma(-(QREG ? qr[c] : sq[c * 32]), w[c + 1], w[c]);
         const double g0n = shfl_dn(w[0], 1);
-        rr = fma(-sup, g0n, fma(-slo, w[N - 1], rs));
+        rr = fma(-R.sup, g0n, fma(-R.slo, w[N - 1], rs));
       } else {
-        rr = fma(sbup, wr, fma(sbdi, w[0], fma(sblo, wl, bsep)));
+        rr = fma(R.sbup, wr, fma(R.sbdi, w[0], fma(R.sblo, wl, R.bsep)));
       }
-#pragma unroll
-      for (int l = 0; l < 5; ++l) {
-        const int s = 1 << l;
-        const double rm = shfl_up(rr, s), rp = shfl_dn(rr, s);
-        rr = fma(ga[l], rp, fma(al[l], rm, rr));
-      }
-      const double xs = rr * invD;
+      const double xs = pcr_solve(rr, R);
       if (N > 0) {
         const double xsl = shfl_up(xs, 1);          // lane 0: v == 0, value unused
 #pragma unroll
@@ -194,27 +267,274 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
 
       if (ckpt != nullptr && ckpt_every > 0 && --until_ckpt == 0) {
         until_ckpt = ckpt_every;
-        double* dst = ckpt + (n_ckpt * pr.P + p) * J;
+        store_state<C>(ckpt + (n_ckpt * pr.P + p) * J, J, lane, w);
         ++n_ckpt;
-#pragma unroll
-        for (int c = 0; c < C; ++c) {
-          const int64_t j = (int64_t)lane * C + c;
-          if (j < J) dst[j] = w[c];
-        }
       }
     }
-
-    // ------------------------------------------------------------------ state out
-    {
-      double* dst = w_io + p * J;
-#pragma unroll
-      for (int c = 0; c < C; ++c) {
-        const int64_t j = (int64_t)lane * C + c;
-        if (j < J) dst[j] = w[c];
-      }
-    }
+    store_state<C>(w_io + p * J, J, lane, w);
     __syncwarp();
   }
+}
+
+// ------------------------------------------------------------------------------------------
+// Tensor-memory variant, C = 32 (512 < J <= 1024), 8 warps per CTA, one CTA per SM.
+//
+// A step of the shared-memory kernel is bound by the latency of its dependent-FMA chains
+// (31 links forward, 30 backward, ~9 cycles each; profiles/r01_fused_v3_tmem.summary.txt), not
+// by the fp64 pipe.  This kernel therefore factors each lane's interior block T with a TWISTED
+// factorisation: cells 0..15 are eliminated top-down, cells 30..16 bottom-up, the two sweeps
+// meet between cells 15 and 16, and substitution runs outwards from there.  Same flops, same
+// five coefficients per cell, but two independent chains of half the length: 16 + 1 + 16
+// dependent links per step instead of 61.  Per cell:  e = elimination coefficient (times the
+// neighbour the sweep comes from), s = substitution coefficient (times the neighbour the
+// sweep moves towards), b = diagonal of inv*B; inv*B's off-diagonals are -c*e and -c*s.
+//
+// TMEM layout per warp (256 columns of its lane quadrant), in the order the loop consumes it:
+//   columns [0,128)  : slot i = (e, b) of left cell i, then (e, b) of right cell 30-i   (8 columns)
+//   columns [128,256): slot i = (v, u) of left cell i, then (v, u) of right cell 30-i
+// s lives in registers (it is read twice per step).  IT = slots per tcgen05.ld (2 -> .x16,
+// 4 -> .x32); loads are double-buffered so the next chunk is in flight while one is consumed.
+template <int IT> struct TmemChunk;
+template <> struct TmemChunk<4> {
+  static constexpr int REGS = 32;
+  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[32]) { tmem_ld_x32(t, r); }
+  static __device__ __forceinline__ void wait(uint32_t (&r)[32]) { tmem_wait_ld_x32(r); }
+};
+template <> struct TmemChunk<2> {
+  static constexpr int REGS = 16;
+  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[16]) { tmem_ld_x16(t, r); }
+  static __device__ __forceinline__ void wait(uint32_t (&r)[16]) { tmem_wait_ld_x16(r); }
+};
+
+// k-th double of a chunk (two 32-bit columns each)
+__device__ __forceinline__ double chunk_dbl(const uint32_t* r, int k) { return __hiloint2double((int)r[2 * k + 1], (int)r[2 * k]); }
+
+template <int MODE, int IT>
+__global__ void __launch_bounds__(kFusedThreads, 1)
+fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
+                  int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
+  constexpr int C = 32, N = 31, M = 16;              // left cells 0..M-1, right cells N-1..M
+  constexpr int NCH = M / IT;                        // chunks per region
+  using TC = TmemChunk<IT>;
+  extern __shared__ double smem[];
+  __shared__ uint32_t tmem_base_slot;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int warps = blockDim.x >> 5;
+  double* sS = smem + (size_t)warp * (3 * N * 32) + lane;        // set-up staging: s, v, u
+  double* sv = sS + N * 32;
+  double* su = sv + N * 32;
+  const int64_t J = pr.J;
+  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
+
+  if (warp == 0) tmem_alloc_512(&tmem_base_slot);
+  tmem_fence_before_sync();
+  __syncthreads();
+  tmem_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t t_eb = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
+  const uint32_t t_vu = t_eb + 128;
+
+  for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
+    // ------------------------------------------------------------------ set-up (once)
+    Reduced R;
+    double sdi = 1.0, delta;
+    {
+      const double dt_theta = mul(dt[p], theta);
+      double beta_l = 0.0, beta_r = 0.0;
+      if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
+        beta_l = dvd(pr.left_flux[p], sub(pr.faces[1], pr.faces[0]));
+      if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
+        beta_r = dvd(-pr.right_flux[p], sub(pr.faces[J], pr.faces[J - 1]));
+      R.bfirst = 0.0; R.bint = 0.0; R.bsep = 0.0; R.rb_c = -1;
+      const int64_t j0 = (int64_t)lane * C;
+      auto row_of = [&](int c, double Dm, double D0, double Dp) {
+        const int64_t j = j0 + c;
+        Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;    // padding rows (j >= J) are identity
+        if (j < J) {
+          Row m = assemble_row_D(pr, p, j, Dm, D0, Dp);
+          a = theta_lhs_row(m, dt_theta, alpha_of(j, J, pr.alpha_left, pr.alpha_right));
+        }
+        return a;
+      };
+      // modified diffusivity in sliding windows: one expm1 per cell and sweep direction
+      double lDm = cell_D(pr, p, j0 - 1), lD0 = cell_D(pr, p, j0);
+      double rDp = cell_D(pr, p, j0 + C), rD0 = cell_D(pr, p, j0 + C - 1);
+      const Row asep = row_of(C - 1, cell_D(pr, p, j0 + C - 2), rD0, rDp);   // the separator's row
+      rDp = rD0; rD0 = cell_D(pr, p, j0 + C - 2);
+      double sl_prev = 0.0, sr_prev = 0.0, gv_prev = 0.0, gu_prev = 0.0;
+#pragma unroll 1
+      for (int i = 0; i < M; ++i) {
+        {                                            // left cell i: top-down elimination
+          const double lDp = cell_D(pr, p, j0 + i + 1);
+          const Row a = row_of(i, lDm, lD0, lDp);
+          lDm = lD0; lD0 = lDp;
+          const double inv = 1.0 / (a.di - a.lo * sl_prev);
+          const double e = a.lo * inv;
+          sl_prev = a.up * inv;
+          gv_prev = (i == 0) ? e : -e * gv_prev;     // elimination sweep of the left spike
+          sS[i * 32] = sl_prev; sv[i * 32] = gv_prev; su[i * 32] = 0.0;
+          tmem_st_2d(t_eb + 8 * i, e, inv * (rth - cth * a.di));
+          if ((int64_t)lane * C + i == 0) R.bfirst = beta_l * inv;
+        }
+        if (i < N - M) {                             // right cell 30-i: bottom-up elimination
+          const int c = N - 1 - i;
+          const double rDm = cell_D(pr, p, j0 + c - 1);
+          const Row a = row_of(c, rDm, rD0, rDp);
+          rDp = rD0; rD0 = rDm;
+          const double inv = 1.0 / (a.di - a.up * sr_prev);
+          const double e = a.up * inv;
+          sr_prev = a.lo * inv;
+          gu_prev = (i == 0) ? e : -e * gu_prev;     // elimination sweep of the right spike
+          sS[c * 32] = sr_prev; su[c * 32] = gu_prev; sv[c * 32] = 0.0;
+          tmem_st_2d(t_eb + 8 * i + 4, e, inv * (rth - cth * a.di));
+        }
+      }
+      R.slo = asep.lo; sdi = asep.di; R.sup = asep.up;
+      const int64_t js = (int64_t)lane * C + C - 1;
+      if (js == J - 1) R.bsep += beta_r;
+      R.sblo = -cth * R.slo; R.sbdi = rth - cth * sdi; R.sbup = -cth * R.sup;
+    }
+    double sr[N];                                    // s for the whole launch
+#pragma unroll
+    for (int c = 0; c < N; ++c) sr[c] = sS[c * 32];
+    delta = 1.0 / (1.0 - sr[M] * sr[M - 1]);
+    {
+      // substitution sweeps of both spikes, outwards from the meeting point
+      double xv = (sv[M * 32] - sr[M] * sv[(M - 1) * 32]) * delta;
+      double xu = (su[M * 32] - sr[M] * su[(M - 1) * 32]) * delta;
+      sv[M * 32] = xv; su[M * 32] = xu;
+      double lv = xv, lu = xu;
+#pragma unroll 1
+      for (int c = M - 1; c >= 0; --c) {
+        const double sc = sS[c * 32];
+        lv = sv[c * 32] - sc * lv; lu = su[c * 32] - sc * lu;
+        sv[c * 32] = lv; su[c * 32] = lu;
+      }
+      double rv = xv, ru = xu;
+#pragma unroll 1
+      for (int c = M + 1; c < N; ++c) {
+        const double sc = sS[c * 32];
+        rv = sv[c * 32] - sc * rv; ru = su[c * 32] - sc * ru;
+        sv[c * 32] = rv; su[c * 32] = ru;
+      }
+      // lv, lu = spikes at cell 0; rv, ru = spikes at cell N-1
+      const double v0n = shfl_dn(lv, 1), u0n = shfl_dn(lu, 1);
+      const double RL = -R.slo * rv;
+      const double RD = sdi - R.slo * ru - R.sup * v0n;          // sup == 0 on lane 31
+      const double RU = -R.sup * u0n;
+      pcr_factor(lane, RL, RD, RU, R);
+#pragma unroll 1
+      for (int i = 0; i < M; ++i) {
+        tmem_st_2d(t_vu + 8 * i, sv[i * 32], su[i * 32]);
+        if (i < N - M) tmem_st_2d(t_vu + 8 * i + 4, sv[(N - 1 - i) * 32], su[(N - 1 - i) * 32]);
+      }
+    }
+    tmem_wait_st();
+    __syncwarp();
+
+    double w[C];
+    load_state<C>(w_io + p * J, J, lane, w);
+
+    // ------------------------------------------------------------------ time loop
+    uint32_t ra[TC::REGS], rb[TC::REGS];
+    int64_t until_ckpt = ckpt_every, n_ckpt = 0;
+    TC::ld(t_eb, ra);                               // first (e, b) chunk of the first step
+    for (int64_t n = 0; n < nsteps; ++n) {
+      double wl = shfl_up(w[C - 1], 1);
+      double wr = shfl_dn(w[0], 1);
+      if (lane == 0) wl = 0.0;
+      if (lane == 31) wr = 0.0;
+      const double w_m_old = w[M], w_last_old = w[N - 1], w_sep = w[C - 1];
+      double oldL = wl, gL = 0.0;                   // left sweep comes from cell -1 (previous separator)
+      double oldR = w_sep, gR = 0.0;                // right sweep comes from cell 31 (own separator)
+      // elimination: chunk k is consumed from one buffer while chunk k+1 (or the first (v, u)
+      // chunk of the correction) is already on its way into the other
+#pragma unroll
+      for (int k = 0; k < NCH; ++k) {
+        uint32_t* cur = (k & 1) ? rb : ra;
+        if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : t_vu, ra); }
+        else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : t_vu, rb); }
+#pragma unroll
+        for (int ii = 0; ii < IT; ++ii) {
+          const int i = k * IT + ii;
+          {
+            const int c = i;
+            const double e = chunk_dbl(cur, 4 * ii), b = chunk_dbl(cur, 4 * ii + 1);
+            const double wc = w[c];
+            const double wn = (c == M - 1) ? w_m_old : w[c + 1];
+            double r = rhs_cell<MODE>(e, sr[c], b, oldL, wc, wn, cth);
+            if (c == 0) r += R.bfirst;
+            gL = (i == 0) ? r : fma(-e, gL, r);
+            w[c] = gL;
+            oldL = wc;
+          }
+          if (i < N - M) {
+            const int c = N - 1 - i;
+            const double e = chunk_dbl(cur, 4 * ii + 2), b = chunk_dbl(cur, 4 * ii + 3);
+            const double wc = w[c];
+            double r = rhs_cell<MODE>(e, sr[c], b, oldR, wc, w[c - 1], cth);
+            gR = (i == 0) ? r : fma(-e, gR, r);
+            w[c] = gR;
+            oldR = wc;
+          }
+        }
+      }
+      const double rs = fma(R.sbup, wr, fma(R.sbdi, w_sep, fma(R.sblo, w_last_old, R.bsep)));
+      // the sweeps meet between cells M-1 and M; substitute outwards
+      w[M] = fma(-sr[M], w[M - 1], w[M]) * delta;
+#pragma unroll
+      for (int j = 0; j < M; ++j) {
+        const int cl = M - 1 - j, cr = M + 1 + j;
+        w[cl] = fma(-sr[cl], w[cl + 1], w[cl]);
+        if (cr < N) w[cr] = fma(-sr[cr], w[cr - 1], w[cr]);
+      }
+      const double g0n = shfl_dn(w[0], 1);
+      const double rr = fma(-R.sup, g0n, fma(-R.slo, w[N - 1], rs));
+      const double xs = pcr_solve(rr, R);
+      const double xsl = shfl_up(xs, 1);            // lane 0: v == 0, value unused
+      // correction; NCH is even, so the first (v, u) chunk sits in ra again
+#pragma unroll
+      for (int k = 0; k < NCH; ++k) {
+        uint32_t* cur = (k & 1) ? rb : ra;
+        if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_vu + 8 * IT * (k + 1) : t_eb, ra); }
+        else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_vu + 8 * IT * (k + 1) : t_eb, rb); }
+#pragma unroll
+        for (int ii = 0; ii < IT; ++ii) {
+          const int i = k * IT + ii;
+          w[i] = fma(-chunk_dbl(cur, 4 * ii + 1), xs, fma(-chunk_dbl(cur, 4 * ii), xsl, w[i]));
+          if (i < N - M) {
+            const int c = N - 1 - i;
+            w[c] = fma(-chunk_dbl(cur, 4 * ii + 3), xs, fma(-chunk_dbl(cur, 4 * ii + 2), xsl, w[c]));
+          }
+        }
+      }
+      w[C - 1] = xs;
+
+      if (ckpt != nullptr && ckpt_every > 0 && --until_ckpt == 0) {
+        until_ckpt = ckpt_every;
+        store_state<C>(ckpt + (n_ckpt * pr.P + p) * J, J, lane, w);
+        ++n_ckpt;
+      }
+    }
+    TC::wait(ra);                                   // drain the prefetch of the step that never comes
+    store_state<C>(w_io + p * J, J, lane, w);
+    __syncwarp();
+  }
+
+  tmem_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc_512(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------
+static int device_limits(int& sms, int& max_smem) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  return 0;
 }
 
 template <int C, int MODE, bool RB, bool QREG>
@@ -222,18 +542,16 @@ static int launch_fused(const fvm_problem& pr, const double* dt, double theta, i
                         int64_t ckpt_every, double* w, double* ckpt, cudaStream_t stream) {
   constexpr int NS = (C > 1 ? C - 1 : 1);
   constexpr size_t per_warp = (size_t)(QREG ? 4 : 5) * NS * 32 * sizeof(double);
-  int dev = 0, sms = 0, max_smem = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return (int)e;
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  int sms = 0, max_smem = 0;
+  int st = device_limits(sms, max_smem);
+  if (st) return st;
   int warps = (int)((size_t)max_smem / per_warp);
   if (warps > kFusedThreads / 32) warps = kFusedThreads / 32;
   if (warps < 1) return FVM_ERR_UNSUPPORTED;
   if ((int64_t)warps > pr.P) warps = (int)pr.P;
   const size_t smem = per_warp * warps;
   auto kern = fused_kernel<C, MODE, RB, QREG>;
-  e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   int per_sm = 1;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, warps * 32, smem);
@@ -246,6 +564,29 @@ static int launch_fused(const fvm_problem& pr, const double* dt, double theta, i
   return (int)cudaGetLastError();
 }
 
+template <int MODE, int IT>
+static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
+                             int64_t ckpt_every, double* w, double* ckpt, cudaStream_t stream) {
+  constexpr int warps = kFusedThreads / 32;
+  constexpr size_t smem = (size_t)warps * 3 * 31 * 32 * sizeof(double);
+  int sms = 0, max_smem = 0;
+  int st = device_limits(sms, max_smem);
+  if (st) return st;
+  auto kern = fused_tmem_kernel<MODE, IT>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  int64_t blocks = (pr.P + warps - 1) / warps;
+  if (blocks > sms) blocks = sms;                // one CTA per SM: it holds the SM's whole TMEM
+  kern<<<(unsigned)blocks, warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
+  return (int)cudaGetLastError();
+}
+
+// FVM_FUSED_STORE=smem forces the shared-memory kernel (A/B comparison and profiling).
+static bool tmem_enabled() {
+  const char* s = getenv("FVM_FUSED_STORE");
+  return !(s && s[0] == 's');
+}
+
 template <int C>
 static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
                          int64_t ckpt_every, double* w, double* ckpt, cudaStream_t stream) {
@@ -253,6 +594,17 @@ static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, 
                   ((pr.J - 1) % C) != C - 1;
   constexpr bool Q = true;
   if (rb) return launch_fused<C, 0, true, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  if (C == 32 && tmem_enabled()) {
+    const char* its = getenv("FVM_TMEM_IT");     // 2: .x16 loads (experiments); default 4: .x32
+    if (its && its[0] == '2') {
+      if (theta == 0.5) return launch_fused_tmem<1, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      if (theta == 1.0) return launch_fused_tmem<2, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      return launch_fused_tmem<0, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    }
+    if (theta == 0.5) return launch_fused_tmem<1, 4>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    if (theta == 1.0) return launch_fused_tmem<2, 4>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    return launch_fused_tmem<0, 4>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  }
   if (theta == 0.5) return launch_fused<C, 1, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
   if (theta == 1.0) return launch_fused<C, 2, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
   return launch_fused<C, 0, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);

@@ -118,6 +118,39 @@ __device__ __forceinline__ Row matrix_row(const double f[4], double am, double a
   return r;
 }
 
+// Modified diffusivity of cell j of problem p (0 outside the mesh, where it is never used).
+__device__ __forceinline__ double cell_D(const fvm_problem& pr, int64_t p, int64_t j) {
+  if (j < 0 || j >= pr.J) return 0.0;
+  double kap, D;
+  cell_kappa_D(pr.scheme, pr.a[p * pr.a_ps + j * pr.a_cs], pr.d[p * pr.d_ps + j * pr.d_cs],
+               sub(pr.faces[j + 1], pr.faces[j]), kap, D);
+  return D;
+}
+
+// Row j of M given the modified diffusivities of cells j-1, j, j+1 (a sweep over consecutive
+// cells keeps them in a sliding window instead of evaluating expm1 three times per row).
+__device__ __forceinline__ Row assemble_row_D(const fvm_problem& pr, int64_t p, int64_t j,
+                                              double Dm, double D0, double Dp) {
+  const int64_t J = pr.J;
+  const bool first = (j == 0), last = (j == J - 1);
+  double f[4];
+  f[0] = first ? 0.0 : pr.faces[j - 1];
+  f[1] = pr.faces[j];
+  f[2] = pr.faces[j + 1];
+  f[3] = last ? 0.0 : pr.faces[j + 2];
+  const double* ap_ = pr.a + p * pr.a_ps;
+  const double a0 = ap_[j * pr.a_cs];
+  const double am = first ? 0.0 : ap_[(j - 1) * pr.a_cs];
+  const double ap = last ? 0.0 : ap_[(j + 1) * pr.a_cs];
+  Row r = matrix_row(f, am, a0, ap, Dm, D0, Dp, first, last, pr.left_kind, pr.right_kind);
+  if (pr.reaction != nullptr) {
+    const bool dirichlet_row = (first && pr.left_kind == FVM_BC_DIRICHLET) ||
+                               (last && pr.right_kind == FVM_BC_DIRICHLET);
+    if (!dirichlet_row) r.di = sub(r.di, pr.reaction[p * pr.r_ps + j * pr.r_cs]);
+  }
+  return r;
+}
+
 // Loads what row j of problem p needs and returns the row of M (with the optional
 // reaction term folded into the diagonal); also kappa and D of cell j.
 __device__ __forceinline__ Row assemble_row(const fvm_problem& pr, int64_t p, int64_t j,
