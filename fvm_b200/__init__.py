@@ -6,6 +6,7 @@
 from .classes import (AdvectionDiffusionModel, CellVariable, H, Mesh, Model, TH,  # noqa: F401
                       check_index_within_bounds, dia_matrix, gaussian, linalg, np, sparse)
 from .batched import BatchedAdvectionDiffusionModel  # noqa: F401
+from .partitioned import PartitionedAdvectionDiffusionModel, plan_partition  # noqa: F401
 
-__all__ = ["AdvectionDiffusionModel", "BatchedAdvectionDiffusionModel", "CellVariable", "H", "Mesh",
+__all__ = ["AdvectionDiffusionModel", "BatchedAdvectionDiffusionModel", "PartitionedAdvectionDiffusionModel", "CellVariable", "H", "Mesh",
            "Model", "TH", "check_index_within_bounds", "dia_matrix", "gaussian", "linalg", "np", "sparse"]

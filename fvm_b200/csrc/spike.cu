@@ -1,0 +1,487 @@
+// Variant 3: partitioned SPIKE / Thomas for LONG systems, streaming from HBM.
+//
+// A system of J cells is cut into tiles of T = TPB*CPT consecutive cells; the LAST cell of
+// every tile is a separator.  With the separators known the tile interiors decouple:
+//
+//   set-up (once per model)
+//     spike_assemble_kernel : rows of A = I - dt*theta*alpha*M for every local cell
+//     spike_tile_factor_kernel : per tile, LU of the interior block (p, q, b as in the other
+//                             variants, factorisation restarted at the tile's first cell) and
+//                             the tile spikes Vt = T^-1(lo_first e_first), Wt = T^-1(up_last e_last)
+//     (host)                  reduced tridiagonal over ALL tile separators of ALL ranks,
+//     reduced_factor_kernel   factored once
+//   every step
+//     tile_solve_kernel     : one CTA per tile: r~ = inv*(B w); tile-local Thomas, parallelised
+//                             over the CTA by a scan of affine maps g_out = A*g_in + B (each
+//                             thread owns CPT consecutive cells: one sequential pass for its
+//                             (A, B), a shuffle/shared-memory scan, one pass with the true carry);
+//                             same backwards.  Reads w, p, q, b and writes g: 40 B per cell.
+//     reduced_rhs_kernel    : rr_k = rs_k - lo_k g_last(k) - up_k g_first(k+1)
+//     (host, multi-GPU)       all-gather of rr over the ranks (NCCL), nT doubles per rank
+//     reduced_solve_kernel  : Thomas on the factored separator system, one CTA, affine scans
+//     correct_kernel        : x = g - Vt xs(k-1) - Wt xs(k), only over the extent where a spike
+//                             exceeds `spike_tol` (spikes decay away from the tile edges)
+//
+// All indices are LOCAL to the rank's slab unless they say "global"; the slab starts at global
+// cell j_offset = tile_offset*T.  State arrays carry one ghost cell on each side
+// (w[-1], w[n_local]) that holds the neighbouring rank's edge value.
+#include "fvm_device.cuh"
+
+namespace fvm {
+
+constexpr unsigned kAll = 0xffffffffu;
+
+struct Affine { double A, B; };   // x -> A*x + B
+
+// later o earlier
+__device__ __forceinline__ Affine compose(const Affine& later, const Affine& earlier) {
+  Affine r;
+  r.A = later.A * earlier.A;
+  r.B = fma(later.A, earlier.B, later.B);
+  return r;
+}
+
+// Exclusive scan of affine maps over the threads of a CTA, in thread order (REVERSE = false)
+// or in reverse thread order (REVERSE = true).  Returns the VALUE entering this thread when the
+// value entering the first thread of the order is `carry_in`; *total receives the map of the
+// whole CTA (valid in every thread).  sm: 2*32 doubles of shared memory.
+template <int TPB, bool REVERSE>
+__device__ __forceinline__ double cta_scan_affine(Affine m, double carry_in, double* sm, Affine* total) {
+  constexpr int NW = TPB / 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int pos = REVERSE ? 31 - lane : lane;              // position inside the warp's order
+  Affine inc = m;                                          // inclusive scan inside the warp
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    Affine o;
+    o.A = REVERSE ? __shfl_down_sync(kAll, inc.A, d) : __shfl_up_sync(kAll, inc.A, d);
+    o.B = REVERSE ? __shfl_down_sync(kAll, inc.B, d) : __shfl_up_sync(kAll, inc.B, d);
+    if (pos >= d) inc = compose(inc, o);
+  }
+  Affine exc;                                              // exclusive inside the warp
+  exc.A = REVERSE ? __shfl_down_sync(kAll, inc.A, 1) : __shfl_up_sync(kAll, inc.A, 1);
+  exc.B = REVERSE ? __shfl_down_sync(kAll, inc.B, 1) : __shfl_up_sync(kAll, inc.B, 1);
+  if (pos == 0) { exc.A = 1.0; exc.B = 0.0; }
+  if (NW == 1) {
+    if (total) {
+      total->A = __shfl_sync(kAll, inc.A, REVERSE ? 0 : 31);
+      total->B = __shfl_sync(kAll, inc.B, REVERSE ? 0 : 31);
+    }
+    return fma(exc.A, carry_in, exc.B);
+  }
+  __syncthreads();                                         // sm may still be in use by a previous scan
+  if (pos == 31) { sm[warp] = inc.A; sm[32 + warp] = inc.B; }
+  __syncthreads();
+  if (warp == 0) {                                         // scan of the warp totals
+    const int wi = REVERSE ? NW - 1 - lane : lane;         // warp index at this lane's position
+    Affine t; t.A = 1.0; t.B = 0.0;
+    if (lane < NW) { t.A = sm[wi]; t.B = sm[32 + wi]; }
+    Affine ti = t;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      Affine o;
+      o.A = __shfl_up_sync(kAll, ti.A, d);
+      o.B = __shfl_up_sync(kAll, ti.B, d);
+      if (lane >= d) ti = compose(ti, o);
+    }
+    Affine te;
+    te.A = __shfl_up_sync(kAll, ti.A, 1);
+    te.B = __shfl_up_sync(kAll, ti.B, 1);
+    if (lane == 0) { te.A = 1.0; te.B = 0.0; }
+    __syncwarp();
+    if (lane < NW) { sm[wi] = te.A; sm[32 + wi] = te.B; }  // exclusive prefix of warp wi
+    if (lane == NW - 1) { sm[64] = ti.A; sm[65] = ti.B; }  // map of the whole CTA
+  }
+  __syncthreads();
+  Affine wp; wp.A = sm[warp]; wp.B = sm[32 + warp];
+  if (total) { total->A = sm[64]; total->B = sm[65]; }
+  const double into_warp = fma(wp.A, carry_in, wp.B);
+  return fma(exc.A, into_warp, exc.B);
+}
+
+// g_c <- r_c - p_c * g_{c-1} along the CTA's TPB*CPT positions (thread-blocked), carry-in 0.
+template <int TPB, int CPT>
+__device__ __forceinline__ void cta_forward(double (&g)[CPT], const double (&p)[CPT], double* sm,
+                                            double carry_in, Affine* total) {
+  Affine m; m.A = 1.0; m.B = 0.0;
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) { m.B = fma(-p[c], m.B, g[c]); m.A = -p[c] * m.A; }
+  double prev = cta_scan_affine<TPB, false>(m, carry_in, sm, total);
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) { prev = fma(-p[c], prev, g[c]); g[c] = prev; }
+}
+
+// x_c <- g_c - q_c * x_{c+1}, from the last position to the first, carry-in (x beyond the end).
+template <int TPB, int CPT>
+__device__ __forceinline__ void cta_backward(double (&x)[CPT], const double (&q)[CPT], double* sm,
+                                             double carry_in, Affine* total) {
+  Affine m; m.A = 1.0; m.B = 0.0;
+#pragma unroll
+  for (int c = CPT - 1; c >= 0; --c) { m.B = fma(-q[c], m.B, x[c]); m.A = -q[c] * m.A; }
+  double nxt = cta_scan_affine<TPB, true>(m, carry_in, sm, total);
+#pragma unroll
+  for (int c = CPT - 1; c >= 0; --c) { nxt = fma(-q[c], nxt, x[c]); x[c] = nxt; }
+}
+
+// Per-tile constants, SEP_STRIDE doubles per tile.
+enum { SEP_LO = 0, SEP_UP, SEP_BLO, SEP_BDI, SEP_BUP, SEP_BETA, SEP_RL, SEP_RDA, SEP_V0, SEP_W0, SEP_STRIDE };
+
+// ------------------------------------------------------------------------------------------ set-up
+// Rows of A for the local cells; lo -> p, di -> b, up -> q (transformed in place by the next kernel).
+__global__ void __launch_bounds__(256) spike_assemble_kernel(fvm_problem pr, const double* __restrict__ dt,
+                                                             double theta, int64_t j_offset, int64_t n_local,
+                                                             double* __restrict__ p, double* __restrict__ q,
+                                                             double* __restrict__ b) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t pi = blockIdx.y;
+  if (i >= n_local) return;
+  const int64_t j = j_offset + i;
+  Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;             // cells past the end of the mesh: identity
+  if (j < pr.J) {
+    double kap, D;
+    Row m = assemble_row(pr, pi, j, kap, D);
+    a = theta_lhs_row(m, mul(dt[pi], theta), alpha_of(j, pr.J, pr.alpha_left, pr.alpha_right));
+  }
+  const int64_t o = pi * n_local + i;
+  p[o] = a.lo; b[o] = a.di; q[o] = a.up;
+}
+
+// One thread per tile: LU of the interior block restarted at the tile's first cell, the tile
+// spikes, the separator's rows and the tile's contribution to the reduced system.
+__global__ void __launch_bounds__(128) spike_tile_factor_kernel(
+    fvm_problem pr, double theta, int64_t tile_offset, int64_t n_tiles, int T, double* __restrict__ p,
+    double* __restrict__ q, double* __restrict__ b, double* __restrict__ Vt, double* __restrict__ Wt,
+    double* __restrict__ sep, double* __restrict__ bends, int* __restrict__ extents, double spike_tol) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t pi = blockIdx.y;
+  if (k >= n_tiles) return;
+  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
+  const int64_t base = (pi * n_tiles + k) * T;
+  const int64_t jg0 = (tile_offset + k) * T;               // global index of the tile's first cell
+  double beta_l = 0.0, beta_r = 0.0;
+  if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
+    beta_l = dvd(pr.left_flux[pi], sub(pr.faces[1], pr.faces[0]));
+  if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
+    beta_r = dvd(-pr.right_flux[pi], sub(pr.faces[pr.J], pr.faces[pr.J - 1]));
+  const int N = T - 1;                                     // interior cells
+  double q_prev = 0.0, gv = 0.0;
+  for (int c = 0; c < N; ++c) {
+    const double lo = p[base + c], di = b[base + c], up = q[base + c];
+    const double inv = 1.0 / (di - lo * q_prev);
+    const double pc = lo * inv;
+    q_prev = up * inv;
+    gv = (c == 0) ? pc : -pc * gv;                         // forward sweep of the left spike
+    p[base + c] = pc; q[base + c] = q_prev; b[base + c] = inv * (rth - cth * di);
+    Vt[base + c] = gv;
+    if (jg0 + c == 0) bends[2 * pi] = beta_l * inv;        // beta[0] as it enters the sweep
+    if (jg0 + c == pr.J - 1) bends[2 * pi + 1] = beta_r * inv;   // beta[J-1] when cell J-1 is a tile-interior cell
+  }
+  double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
+  {
+    const double lo = p[base + N], di = b[base + N], up = q[base + N];
+    s[SEP_LO] = lo; s[SEP_UP] = up;
+    s[SEP_BLO] = -cth * lo; s[SEP_BDI] = rth - cth * di; s[SEP_BUP] = -cth * up;
+    double bs = 0.0;
+    if (jg0 + N == 0) bs += beta_l;
+    if (jg0 + N == pr.J - 1) bs += beta_r;
+    s[SEP_BETA] = bs;
+    p[base + N] = 0.0; q[base + N] = 0.0; b[base + N] = 0.0;   // separator: not part of the tile solve
+    Vt[base + N] = 0.0; Wt[base + N] = 0.0;
+    // backward sweeps of both spikes
+    double vn = Vt[base + N - 1], un = q[base + N - 1];
+    Wt[base + N - 1] = un;
+    int eL = (fabs(vn) > spike_tol) ? N : 0, eR = 1;
+    for (int c = N - 2; c >= 0; --c) {
+      const double qc = q[base + c];
+      vn = Vt[base + c] - qc * vn;
+      un = -qc * un;
+      Vt[base + c] = vn; Wt[base + c] = un;
+      if (fabs(vn) > spike_tol && c + 1 > eL) eL = c + 1;  // cells [0, eL) need the left correction
+      if (fabs(un) > spike_tol) eR = N - c;                // cells [N-eR, N) need the right correction
+    }
+    const double vlast = Vt[base + N - 1], ulast = Wt[base + N - 1];
+    s[SEP_RL] = -lo * vlast;
+    s[SEP_RDA] = di - lo * ulast;                          // the -up*V0(k+1) term is added by the host
+    s[SEP_V0] = vn; s[SEP_W0] = un;
+    atomicMax(&extents[0], eL);
+    atomicMax(&extents[1], eR);
+  }
+}
+
+// Thomas factorisation of the reduced tridiagonal (one thread per problem; n = global tiles).
+__global__ void reduced_factor_kernel(int64_t n, int64_t P, const double* __restrict__ RL,
+                                      const double* __restrict__ RD, const double* __restrict__ RU,
+                                      double* __restrict__ rp, double* __restrict__ rq, double* __restrict__ rinv) {
+  const int64_t pi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pi >= P) return;
+  double q_prev = 0.0;
+  for (int64_t k = 0; k < n; ++k) {
+    const int64_t o = pi * n + k;
+    const double inv = 1.0 / (RD[o] - RL[o] * q_prev);
+    rp[o] = RL[o] * inv;
+    q_prev = RU[o] * inv;
+    rq[o] = q_prev;
+    rinv[o] = inv;
+  }
+}
+
+// ------------------------------------------------------------------------------------------ per step
+template <int TPB, int CPT, int MODE>
+__global__ void __launch_bounds__(TPB) tile_solve_kernel(
+    int64_t n_tiles, const double* __restrict__ p, const double* __restrict__ q,
+    const double* __restrict__ b, const double* __restrict__ sep, const double* __restrict__ bends,
+    int has_first_cell, int64_t jl_last, double cth, const double* __restrict__ w_in,
+    double* __restrict__ w_out, double* __restrict__ rs, int64_t w_stride) {
+  constexpr int T = TPB * CPT;
+  __shared__ double sm[66];
+  const int64_t k = blockIdx.x, pi = blockIdx.y;
+  const int64_t base = (pi * n_tiles + k) * T + (int64_t)threadIdx.x * CPT;     // into p, q, b
+  const int64_t wbase = pi * w_stride + k * T + (int64_t)threadIdx.x * CPT;     // into w (ghosted)
+  double w[CPT + 2], pc[CPT], qc[CPT], g[CPT];
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) { pc[c] = p[base + c]; qc[c] = q[base + c]; g[c] = b[base + c]; }
+#pragma unroll
+  for (int c = 0; c < CPT + 2; ++c) w[c] = w_in[wbase + c - 1];
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) {
+    if (MODE == 2) {
+      g[c] = g[c] * w[c + 1];
+    } else {
+      const double t = fma(qc[c], w[c + 2], pc[c] * w[c]);
+      g[c] = (MODE == 1) ? fma(g[c], w[c + 1], -t) : fma(-cth, t, g[c] * w[c + 1]);
+    }
+  }
+  if (has_first_cell && k == 0 && threadIdx.x == 0) g[0] += bends[2 * pi];
+  {                                                        // beta[J-1] at a tile-interior cell (rare)
+    const int64_t l0 = k * T + (int64_t)threadIdx.x * CPT;
+    if (jl_last >= l0 && jl_last < l0 + CPT) {
+      const int cl = (int)(jl_last - l0);
+#pragma unroll
+      for (int c = 0; c < CPT; ++c) if (c == cl) g[c] += bends[2 * pi + 1];
+    }
+  }
+  if (threadIdx.x == TPB - 1) {                            // the separator's right-hand side
+    const double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
+    rs[pi * n_tiles + k] = fma(s[SEP_BUP], w[CPT + 1], fma(s[SEP_BDI], w[CPT], fma(s[SEP_BLO], w[CPT - 1], s[SEP_BETA])));
+  }
+  cta_forward<TPB, CPT>(g, pc, sm, 0.0, nullptr);
+  cta_backward<TPB, CPT>(g, qc, sm, 0.0, nullptr);
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) w_out[wbase + c] = g[c];
+}
+
+// rr_k = rs_k - lo_k g_last(k) - up_k g_first(k+1); the last local tile leaves the g_first term
+// to whoever knows the next rank's first cell (g_first_out[pi] = this rank's own first value).
+__global__ void __launch_bounds__(256) reduced_rhs_kernel(int64_t n_tiles, int T, const double* __restrict__ sep,
+                                                          const double* __restrict__ rs, const double* __restrict__ g,
+                                                          int64_t w_stride, double* __restrict__ rr,
+                                                          int64_t rr_stride, double* __restrict__ g_first_out) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t pi = blockIdx.y;
+  if (k >= n_tiles) return;
+  const double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
+  const double* gp = g + pi * w_stride + k * T;
+  double r = fma(-s[SEP_LO], gp[T - 2], rs[pi * n_tiles + k]);
+  if (k + 1 < n_tiles) r = fma(-s[SEP_UP], gp[T], r);
+  rr[pi * rr_stride + k] = r;
+  if (k == 0) g_first_out[pi] = gp[0];
+}
+
+// Thomas solve of the factored reduced system by ONE CTA per problem, in chunks of TPB*CPT
+// unknowns with the carry handed from chunk to chunk.
+template <int TPB, int CPT>
+__global__ void __launch_bounds__(TPB) reduced_solve_kernel(int64_t n, const double* __restrict__ rp,
+                                                            const double* __restrict__ rq,
+                                                            const double* __restrict__ rinv,
+                                                            const double* __restrict__ rr, double* __restrict__ xs) {
+  constexpr int CH = TPB * CPT;
+  __shared__ double sm[66];
+  const int64_t pi = blockIdx.x;
+  const double* P_ = rp + pi * n; const double* Q_ = rq + pi * n; const double* I_ = rinv + pi * n;
+  const double* R_ = rr + pi * n; double* X_ = xs + pi * n;
+  double carry = 0.0;
+  for (int64_t c0 = 0; c0 < n; c0 += CH) {                 // forward: g_k = rr_k*inv_k - p_k g_{k-1}
+    double g[CPT], pc[CPT];
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      const int64_t k = c0 + (int64_t)threadIdx.x * CPT + c;
+      const bool in = k < n;
+      pc[c] = in ? P_[k] : 0.0;
+      g[c] = in ? R_[k] * I_[k] : 0.0;
+    }
+    Affine tot;
+    cta_forward<TPB, CPT>(g, pc, sm, carry, &tot);
+    carry = fma(tot.A, carry, tot.B);
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      const int64_t k = c0 + (int64_t)threadIdx.x * CPT + c;
+      if (k < n) X_[k] = g[c];
+    }
+  }
+  __syncthreads();
+  carry = 0.0;
+  const int64_t nch = (n + CH - 1) / CH;
+  for (int64_t ch = nch - 1; ch >= 0; --ch) {              // backward: x_k = g_k - q_k x_{k+1}
+    const int64_t c0 = ch * CH;
+    double x[CPT], qc[CPT];
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      const int64_t k = c0 + (int64_t)threadIdx.x * CPT + c;
+      const bool in = k < n;
+      qc[c] = in ? Q_[k] : 0.0;
+      x[c] = in ? X_[k] : 0.0;
+    }
+    Affine tot;
+    cta_backward<TPB, CPT>(x, qc, sm, carry, &tot);
+    carry = fma(tot.A, carry, tot.B);
+#pragma unroll
+    for (int c = 0; c < CPT; ++c) {
+      const int64_t k = c0 + (int64_t)threadIdx.x * CPT + c;
+      if (k < n) X_[k] = x[c];
+    }
+  }
+}
+
+// x = g - Vt*xs(k-1) - Wt*xs(k) over the spike extents, x_sep = xs(k); also refreshes the two
+// ghost cells of the local state.  xs is indexed GLOBALLY (tile_offset + k).
+__global__ void __launch_bounds__(256) correct_kernel(int64_t n_tiles, int T, int eL, int eR, int64_t tile_offset,
+                                                      int64_t n_tiles_global, const double* __restrict__ Vt,
+                                                      const double* __restrict__ Wt, const double* __restrict__ xs,
+                                                      double* __restrict__ w, int64_t w_stride,
+                                                      const double* __restrict__ next_first) {
+  const int per_tile = eL + eR + 1;
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t pi = blockIdx.y;
+  if (idx >= n_tiles * per_tile) return;
+  const int64_t k = idx / per_tile;
+  const int r = (int)(idx - k * per_tile);
+  const int N = T - 1;
+  const double* X_ = xs + pi * n_tiles_global;
+  const int64_t kg = tile_offset + k;
+  const double xk = X_[kg];
+  const double xl = (kg > 0) ? X_[kg - 1] : 0.0;
+  double* wp = w + pi * w_stride + k * T;
+  if (r == eL + eR) {                                      // the separator itself, and the ghosts
+    wp[N] = xk;
+    if (k == 0) wp[-1] = xl;                               // left ghost = previous rank's last separator
+    if (k == n_tiles - 1) wp[T] = next_first ? next_first[pi] : 0.0;   // right ghost = next rank's first cell
+    return;
+  }
+  int c;
+  if (r < eL) c = r;
+  else { c = N - eR + (r - eL); if (c < eL) return; }      // extents overlap: each cell once
+  const int64_t o = (pi * n_tiles + k) * T + c;
+  wp[c] = fma(-Wt[o], xk, fma(-Vt[o], xl, wp[c]));
+}
+
+}  // namespace fvm
+
+// ------------------------------------------------------------------------------------------ C-ABI
+namespace {
+constexpr int kTileCfgs = 2;
+inline int tile_cells(int cfg) { return cfg == 0 ? 512 * 16 : 64 * 4; }
+}
+
+extern "C" int64_t fvm_spike_tile_cells(int32_t config) {
+  return (config >= 0 && config < kTileCfgs) ? tile_cells(config) : 0;
+}
+
+extern "C" int fvm_spike_setup(const fvm_problem* prob, const double* dt, double theta, int64_t tile_offset,
+                               int64_t n_tiles, int32_t config, double* p, double* q, double* b, double* Vt,
+                               double* Wt, double* sep, double* bends, int32_t* extents, double spike_tol,
+                               void* stream) {
+  if (!prob || !prob->faces || !prob->a || !prob->d || !dt || !p || !q || !b || !Vt || !Wt || !sep || !bends ||
+      !extents)
+    return FVM_ERR_INVALID_ARG;
+  if (prob->J < 3 || prob->P < 1 || n_tiles < 1 || tile_offset < 0 || !(theta > 0.0 && theta <= 1.0))
+    return FVM_ERR_INVALID_ARG;
+  if (config < 0 || config >= kTileCfgs) return FVM_ERR_INVALID_ARG;
+  if (prob->P > 65535) return FVM_ERR_UNSUPPORTED;
+  const int T = tile_cells(config);
+  const int64_t n_local = n_tiles * T;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(extents, 0, 2 * sizeof(int32_t), s);
+  if (e != cudaSuccess) return (int)e;
+  e = cudaMemsetAsync(bends, 0, 2 * prob->P * sizeof(double), s);
+  if (e != cudaSuccess) return (int)e;
+  dim3 g1((unsigned)((n_local + 255) / 256), (unsigned)prob->P);
+  fvm::spike_assemble_kernel<<<g1, 256, 0, s>>>(*prob, dt, theta, tile_offset * T, n_local, p, q, b);
+  dim3 g2((unsigned)((n_tiles + 127) / 128), (unsigned)prob->P);
+  fvm::spike_tile_factor_kernel<<<g2, 128, 0, s>>>(*prob, theta, tile_offset, n_tiles, T, p, q, b, Vt, Wt, sep,
+                                                   bends, (int*)extents, spike_tol);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_spike_reduced_factor(int64_t n, int64_t P, const double* RL, const double* RD,
+                                        const double* RU, double* rp, double* rq, double* rinv, void* stream) {
+  if (!RL || !RD || !RU || !rp || !rq || !rinv || n < 1 || P < 1) return FVM_ERR_INVALID_ARG;
+  fvm::reduced_factor_kernel<<<(unsigned)((P + 63) / 64), 64, 0, (cudaStream_t)stream>>>(n, P, RL, RD, RU, rp, rq,
+                                                                                       rinv);
+  return (int)cudaGetLastError();
+}
+
+template <int TPB, int CPT>
+static int launch_tile_solve(int64_t n_tiles, int64_t P, const double* p, const double* q, const double* b,
+                             const double* sep, const double* bfirst, int has_first, int64_t jl_last, double theta,
+                             const double* w_in, double* w_out, double* rs, int64_t w_stride, cudaStream_t s) {
+  dim3 grid((unsigned)n_tiles, (unsigned)P);
+  const double cth = (1.0 - theta) / theta;
+  if (theta == 0.5)
+    fvm::tile_solve_kernel<TPB, CPT, 1><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last, cth, w_in,
+                                                            w_out, rs, w_stride);
+  else if (theta == 1.0)
+    fvm::tile_solve_kernel<TPB, CPT, 2><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last, cth, w_in,
+                                                            w_out, rs, w_stride);
+  else
+    fvm::tile_solve_kernel<TPB, CPT, 0><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last, cth, w_in,
+                                                            w_out, rs, w_stride);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                               const double* b, const double* sep, const double* bends, int32_t has_first_cell,
+                               int64_t last_cell_local, double theta, const double* w_in, double* w_out,
+                               int64_t w_stride, double* rs,
+                               double* rr, int64_t rr_stride, double* g_first, void* stream) {
+  if (!p || !q || !b || !sep || !bends || !w_in || !w_out || !rs || !rr || !g_first) return FVM_ERR_INVALID_ARG;
+  if (n_tiles < 1 || P < 1 || P > 65535 || !(theta > 0.0 && theta <= 1.0)) return FVM_ERR_INVALID_ARG;
+  if (config < 0 || config >= kTileCfgs || n_tiles > 0x7fffffffLL) return FVM_ERR_INVALID_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  int st = config == 0
+               ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+                                            w_in, w_out, rs, w_stride, s)
+               : launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+                                          w_in, w_out, rs, w_stride, s);
+  if (st) return st;
+  dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
+  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_cells(config), sep, rs, w_out, w_stride, rr, rr_stride,
+                                            g_first);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_spike_reduce_solve(int64_t n_global, int64_t P, const double* rp, const double* rq,
+                                      const double* rinv, const double* rr, double* xs, void* stream) {
+  if (!rp || !rq || !rinv || !rr || !xs || n_global < 1 || P < 1) return FVM_ERR_INVALID_ARG;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n_global <= 1024)
+    fvm::reduced_solve_kernel<128, 8><<<(unsigned)P, 128, 0, s>>>(n_global, rp, rq, rinv, rr, xs);
+  else
+    fvm::reduced_solve_kernel<1024, 8><<<(unsigned)P, 1024, 0, s>>>(n_global, rp, rq, rinv, rr, xs);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, const int32_t* extents_host,
+                                  int64_t tile_offset, int64_t n_tiles_global, const double* Vt, const double* Wt,
+                                  const double* xs, double* w, int64_t w_stride, const double* next_first,
+                                  void* stream) {
+  if (!extents_host || !Vt || !Wt || !xs || !w || n_tiles < 1 || P < 1 || P > 65535) return FVM_ERR_INVALID_ARG;
+  if (config < 0 || config >= kTileCfgs) return FVM_ERR_INVALID_ARG;
+  const int T = tile_cells(config);
+  int eL = extents_host[0], eR = extents_host[1];
+  if (eL < 0 || eR < 0 || eL > T - 1 || eR > T - 1) return FVM_ERR_INVALID_ARG;
+  const int64_t total = n_tiles * (int64_t)(eL + eR + 1);
+  dim3 g((unsigned)((total + 255) / 256), (unsigned)P);
+  fvm::correct_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(n_tiles, T, eL, eR, tile_offset, n_tiles_global, Vt, Wt, xs,
+                                                          w, w_stride, next_first);
+  return (int)cudaGetLastError();
+}

@@ -1,0 +1,315 @@
+"""Long systems: one huge mesh (or a batch of long ones) partitioned into tiles, optionally
+with the cells split in contiguous slabs over the ranks of a torch.distributed group
+(BASELINE.json cfg 4 and cfg 5).  Drives variant 3 of the C-ABI
+(fvm_spike_*): tile-local Thomas solves, a reduced tridiagonal over the tile separators that
+every rank solves redundantly after ONE all-gather per step, and a spike correction near
+the tile edges.
+
+Semantics are those of the reference's loop (fvm_classes.py:373-377,408-411).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from .batched import _alpha_ends, _bc_kinds
+
+SEP_LO, SEP_UP, SEP_BLO, SEP_BDI, SEP_BUP, SEP_BETA, SEP_RL, SEP_RDA, SEP_V0, SEP_W0, SEP_STRIDE = range(11)
+
+
+def plan_partition(J, tile_cells, world):
+    """How a J-cell mesh is cut: global tiles (padded so that every rank owns the same number),
+    tiles per rank, and for each rank the global cell range [j0, j1) it really holds."""
+    J, T, world = int(J), int(tile_cells), int(world)
+    n_tiles = -(-J // T)
+    per_rank = -(-n_tiles // world)
+    ranges = []
+    for r in range(world):
+        j0 = r * per_rank * T
+        ranges.append((min(j0, J), min(j0 + per_rank * T, J)))
+    return dict(tiles_per_rank=per_rank, tiles_global=per_rank * world, ranges=ranges)
+
+
+class Comm(object):
+    """The one collective the data path needs: all-gather of a small tensor over the ranks.
+    world == 1: no-op.  NCCL groups gather on the device; a gloo group (tests: several ranks
+    sharing one GPU) stages through host memory."""
+
+    def __init__(self, group=None):
+        self.group = group
+        if group is None:
+            self.rank, self.world, self.backend = 0, 1, None
+        else:
+            import torch.distributed as dist
+            self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+            self.backend = dist.get_backend(group)
+
+    def all_gather(self, t):
+        """t: tensor of identical shape on every rank -> tensor [world, *t.shape]."""
+        import torch
+        if self.world == 1:
+            return t.unsqueeze(0)
+        import torch.distributed as dist
+        if self.backend == "gloo":
+            host = t.detach().cpu().contiguous()
+            parts = [torch.empty_like(host) for _ in range(self.world)]
+            dist.all_gather(parts, host, group=self.group)
+            return torch.stack(parts).to(t.device)
+        t = t.contiguous()
+        out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t, group=self.group)
+        return out
+
+    def all_reduce_max_int(self, values):
+        import torch
+        if self.world == 1:
+            return [int(v) for v in values]
+        import torch.distributed as dist
+        t = torch.tensor([int(v) for v in values], dtype=torch.int64)
+        if self.backend == "nccl":
+            t = t.cuda()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return [int(v) for v in t.cpu()]
+
+
+class PartitionedAdvectionDiffusionModel(object):
+    """P long problems on one mesh of ``J`` cells, this rank holding the cells
+    ``plan_partition(J, T, world)['ranges'][rank]``.
+
+    Two ways to pass the mesh and the coefficients:
+      * global (default): ``faces`` has J+1 entries, per-cell ``a``/``d`` have J entries
+        ((J,) or (P, J)); every rank slices what it needs.  Fine while J fits host memory.
+      * local (``J=...`` given): ``faces`` covers the global faces
+        [max(j0-1, 0), min(j1+1, J)] of this rank's range [j0, j1), per-cell coefficients
+        cover the cells [max(j0-1, 0), min(j1, J-1)].
+    ``a``, ``d``, ``reaction`` may also be scalars or (P,) per-problem scalars; ``k`` (the time
+    step) is a scalar or (P,).
+    """
+
+    def __init__(self, faces, a, d, k, discretisation="central", P=1, reaction=None, strict_bc=False,
+                 J=None, group=None, config=0, spike_tol=1e-30, device=None):
+        torch = _lib.require_cuda()
+        lib = _lib.lib()
+        if discretisation not in _lib.SCHEMES:
+            raise AttributeError("discretisation must be one of `upwind`, `central` or `exponential`")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.comm = Comm(group)
+        self.config = int(config)
+        self.T = int(lib.fvm_spike_tile_cells(self.config))
+        if self.T == 0:
+            raise ValueError("unknown tile configuration %r" % (config,))
+        self.local_input = J is not None
+        self.J = int(J) if J is not None else int(np.shape(faces)[-1]) - 1
+        if self.J < 3:
+            raise IndexError("at least 3 cells are needed (the reference fails at fvm_classes.py:292)")
+        self.P = int(P)
+        self.discretisation, self.strict_bc, self.spike_tol = discretisation, strict_bc, float(spike_tol)
+        plan = plan_partition(self.J, self.T, self.comm.world)
+        self.nt = plan["tiles_per_rank"]
+        self.nt_global = plan["tiles_global"]
+        self.tile_offset = self.comm.rank * self.nt
+        self.j0, self.j1 = plan["ranges"][self.comm.rank]
+        self.n_local = self.nt * self.T                      # padded slab length
+        # global index of the first face / cell this rank holds in its local arrays
+        self.f_lo = max(self.j0 - 1, 0) if self.j1 > self.j0 else min(self.j0, self.J)
+        self.c_lo = self.f_lo
+        f_hi = min(self.j1 + 1, self.J)
+        c_hi = min(self.j1, self.J - 1)
+        self.faces = self._slab(faces, self.f_lo, f_hi + 1, self.J + 1)
+        self.a, self._a_str = self._coef(a, c_hi)
+        self.d, self._d_str = self._coef(d, c_hi)
+        self.reaction, self._r_str = (None, (0, 0)) if reaction is None else self._coef(reaction, c_hi)
+        kk = self._dev(k).reshape(-1)
+        self.k = (kk.expand(self.P) if kk.numel() == 1 else kk).contiguous()
+        self._ready = None
+
+    # ------------------------------------------------------------------ inputs
+    def _dev(self, x):
+        torch = _lib.require_cuda()
+        if isinstance(x, torch.Tensor):
+            return x.to(device=self.device, dtype=torch.float64)
+        return torch.as_tensor(np.asarray(x, dtype=np.float64), device=self.device)
+
+    def _slab(self, x, lo, hi, n_global):
+        """Entries [lo, hi) of a global per-face/per-cell array (last axis), or the local array as is."""
+        t = self._dev(x)
+        if self.local_input:
+            if t.shape[-1] != max(hi - lo, 0):
+                raise ValueError("local array has %d entries, expected %d" % (t.shape[-1], hi - lo))
+            return t.contiguous()
+        if t.shape[-1] != n_global:
+            raise ValueError("global array has %d entries, expected %d" % (t.shape[-1], n_global))
+        return t[..., lo:hi].contiguous()
+
+    def _coef(self, x, c_hi):
+        """Tensor, (problem stride, cell stride) and the global cell its element 0 refers to."""
+        t = self._dev(x)
+        if t.ndim == 0:
+            return t.reshape(1).contiguous(), (0, 0)
+        if t.ndim == 1 and t.numel() == self.P and (self.local_input or t.numel() != self.J):
+            return t.contiguous(), (1, 0)
+        s = self._slab(t, self.c_lo, c_hi + 1, self.J)
+        if s.ndim == 1:
+            return s, (0, 1)
+        if s.ndim == 2 and s.shape[0] == self.P:
+            return s, (s.shape[1], 1)
+        raise ValueError("coefficient must be scalar, (P,), per-cell or (P, per-cell)")
+
+    def set_boundary_conditions(self, left_flux=None, right_flux=None, left_value=None, right_value=None):
+        """Same keywords as the reference (fvm_classes.py:141-147); fluxes may be per problem."""
+        self.left_flux, self.right_flux = left_flux, right_flux
+        self.left_value, self.right_value = left_value, right_value
+        self._ready = None
+
+    def _flux(self, x):
+        t = self._dev(x).reshape(-1)
+        return (t.expand(self.P) if t.numel() == 1 else t).contiguous()
+
+    def _problem(self):
+        if not hasattr(self, "left_flux"):
+            raise AttributeError("boundary conditions are not set: call set_boundary_conditions first")
+        lk, rk = _bc_kinds(self.left_flux, self.right_flux, self.left_value, self.right_value)
+        al, ar = _alpha_ends(self.left_flux, lk, rk, self.strict_bc)
+        self._lf = self._flux(self.left_flux) if lk == _lib.BC_ROBIN else None
+        self._rf = self._flux(self.right_flux) if rk == _lib.BC_ROBIN else None
+        pr = _lib.FvmProblem()
+        pr.J, pr.P = self.J, self.P
+        # the kernels index by GLOBAL cell: shift the base pointers by what this rank does not hold
+        pr.faces = self.faces.data_ptr() - 8 * self.f_lo
+        pr.a = self.a.data_ptr() - 8 * self.c_lo * self._a_str[1]
+        pr.a_ps, pr.a_cs = self._a_str
+        pr.d = self.d.data_ptr() - 8 * self.c_lo * self._d_str[1]
+        pr.d_ps, pr.d_cs = self._d_str
+        if self.reaction is not None:
+            pr.reaction = self.reaction.data_ptr() - 8 * self.c_lo * self._r_str[1]
+            pr.r_ps, pr.r_cs = self._r_str
+        pr.scheme = _lib.SCHEMES[self.discretisation]
+        pr.left_kind, pr.right_kind, pr.alpha_left, pr.alpha_right = lk, rk, al, ar
+        self._has_lf = self._lf is not None and bool((self._lf != 0).any())
+        self._has_rf = self._rf is not None and bool((self._rf != 0).any())
+        pr.left_flux = self._lf.data_ptr() if self._has_lf else None
+        pr.right_flux = self._rf.data_ptr() if self._has_rf else None
+        return pr
+
+    # ------------------------------------------------------------------ set-up
+    def prepare(self, theta):
+        """Assembly, tile factorisation, spikes and the factored reduced system for this theta."""
+        torch = _lib.require_cuda()
+        theta = float(theta)
+        if self._ready == theta:
+            return
+        lib, dev, P, nt, T = _lib.lib(), self.device, self.P, self.nt, self.T
+        pr = self._problem()
+        new = lambda *shape: torch.empty(shape, dtype=torch.float64, device=dev)
+        self.p, self.q, self.b = new(P, self.n_local), new(P, self.n_local), new(P, self.n_local)
+        self.Vt, self.Wt = new(P, self.n_local), new(P, self.n_local)
+        self.sep = new(P, nt, SEP_STRIDE)
+        self.bends = new(P, 2)
+        ext = torch.zeros(2, dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            st = lib.fvm_spike_setup(ctypes.byref(pr), _lib.ptr(self.k), theta, self.tile_offset, nt, self.config,
+                                     _lib.ptr(self.p), _lib.ptr(self.q), _lib.ptr(self.b), _lib.ptr(self.Vt),
+                                     _lib.ptr(self.Wt), _lib.ptr(self.sep), _lib.ptr(self.bends),
+                                     ctypes.c_void_p(ext.data_ptr()), self.spike_tol, _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_setup")
+        # reduced tridiagonal over the separators of every rank
+        sep_all = self.comm.all_gather(self.sep).permute(1, 0, 2, 3).reshape(P, self.nt_global, SEP_STRIDE)
+        self.sup_all = sep_all[..., SEP_UP].contiguous()
+        self.V0_all = sep_all[..., SEP_V0].contiguous()
+        self.W0_all = sep_all[..., SEP_W0].contiguous()
+        nxt = lambda x: torch.cat([x[:, 1:], torch.zeros_like(x[:, :1])], dim=1)
+        RL = sep_all[..., SEP_RL].contiguous()
+        RD = (sep_all[..., SEP_RDA] - self.sup_all * nxt(self.V0_all)).contiguous()
+        RU = (-self.sup_all * nxt(self.W0_all)).contiguous()
+        self.rp, self.rq, self.rinv = new(P, self.nt_global), new(P, self.nt_global), new(P, self.nt_global)
+        with torch.cuda.device(dev):
+            st = lib.fvm_spike_reduced_factor(self.nt_global, P, _lib.ptr(RL), _lib.ptr(RD), _lib.ptr(RU),
+                                              _lib.ptr(self.rp), _lib.ptr(self.rq), _lib.ptr(self.rinv),
+                                              _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_reduced_factor")
+        e = self.comm.all_reduce_max_int(ext.cpu().tolist())
+        self.extents = (ctypes.c_int32 * 2)(min(e[0], T - 1), min(e[1], T - 1))
+        # work arrays of a step
+        self.rs, self.rr, self.g_first = new(P, nt), new(P, nt), new(P)
+        self.xs = new(P, self.nt_global)
+        self.w_stride = self.n_local + 2
+        self._wbuf = [torch.zeros((P, self.w_stride), dtype=torch.float64, device=dev) for _ in range(2)]
+        jl = self.J - 1 - self.j0
+        self._last_local = jl if (self._has_rf and 0 <= jl < self.n_local and jl % T != T - 1) else -1
+        self._theta = theta
+        self._ready = theta
+
+    # ------------------------------------------------------------------ state
+    def set_state(self, w):
+        """w: (P, J) global state (global input mode) or (P, j1-j0) this rank's cells."""
+        torch = _lib.require_cuda()
+        w = self._dev(w).reshape(self.P, -1)
+        n_real = self.j1 - self.j0
+        if w.shape[1] == self.J and not (self.local_input and self.comm.world > 1):
+            w = w[:, self.j0:self.j1]
+        if w.shape[1] != n_real:
+            raise ValueError("state has %d cells per problem, expected %d" % (w.shape[1], n_real))
+        buf = self._wbuf[0]
+        buf.zero_()
+        buf[:, 1:1 + n_real] = w
+        edges = torch.stack([buf[:, 1], buf[:, self.n_local]], dim=1)          # first / last local cell
+        if self.comm.world > 1:
+            allv = self.comm.all_gather(edges)                                  # [world, P, 2]
+            r = self.comm.rank
+            if r > 0:
+                buf[:, 0] = allv[r - 1, :, 1]
+            if r < self.comm.world - 1:
+                buf[:, self.n_local + 1] = allv[r + 1, :, 0]
+        self._cur = 0
+
+    def get_state(self):
+        """This rank's cells, (P, j1-j0)."""
+        return self._wbuf[self._cur][:, 1:1 + (self.j1 - self.j0)].clone()
+
+    # ------------------------------------------------------------------ stepping
+    def step(self, nsteps=1):
+        """``nsteps`` theta steps of the state set by :meth:`set_state` (theta of :meth:`prepare`)."""
+        torch = _lib.require_cuda()
+        lib, P, nt, cfg, comm = _lib.lib(), self.P, self.nt, self.config, self.comm
+        wptr = lambda t: ctypes.c_void_p(t.data_ptr() + 8)                      # skip the left ghost
+        with torch.cuda.device(self.device):
+            for _ in range(int(nsteps)):
+                w_in, w_out = self._wbuf[self._cur], self._wbuf[1 - self._cur]
+                st = lib.fvm_spike_local(nt, P, cfg, _lib.ptr(self.p), _lib.ptr(self.q), _lib.ptr(self.b),
+                                         _lib.ptr(self.sep), _lib.ptr(self.bends), int(comm.rank == 0),
+                                         self._last_local, self._theta, wptr(w_in), wptr(w_out), self.w_stride,
+                                         _lib.ptr(self.rs), _lib.ptr(self.rr), nt, _lib.ptr(self.g_first),
+                                         _lib.stream_ptr())
+                _lib.check(st, "fvm_spike_local")
+                next_first = None
+                if comm.world == 1:
+                    rr_all = self.rr
+                else:
+                    packet = torch.cat([self.rr, self.g_first[:, None]], dim=1)            # [P, nt+1]
+                    allp = comm.all_gather(packet)                                          # [world, P, nt+1]
+                    rr_all = allp[:, :, :nt].permute(1, 0, 2).reshape(P, self.nt_global).contiguous()
+                    gf = allp[:, :, nt]                                                     # [world, P]
+                    last = torch.arange(1, comm.world, device=self.device) * nt - 1        # last tile of ranks 0..W-2
+                    rr_all[:, last] -= self.sup_all[:, last] * gf[1:].t()
+                st = lib.fvm_spike_reduce_solve(self.nt_global, P, _lib.ptr(self.rp), _lib.ptr(self.rq),
+                                                _lib.ptr(self.rinv), _lib.ptr(rr_all), _lib.ptr(self.xs),
+                                                _lib.stream_ptr())
+                _lib.check(st, "fvm_spike_reduce_solve")
+                if comm.world > 1 and comm.rank < comm.world - 1:
+                    k1 = (comm.rank + 1) * nt                                               # next rank's first tile
+                    next_first = (gf[comm.rank + 1] - self.V0_all[:, k1] * self.xs[:, k1 - 1]
+                                  - self.W0_all[:, k1] * self.xs[:, k1]).contiguous()
+                st = lib.fvm_spike_finalize(nt, P, cfg, self.extents, self.tile_offset, self.nt_global,
+                                            _lib.ptr(self.Vt), _lib.ptr(self.Wt), _lib.ptr(self.xs), wptr(w_out),
+                                            self.w_stride, _lib.ptr(next_first), _lib.stream_ptr())
+                _lib.check(st, "fvm_spike_finalize")
+                self._cur = 1 - self._cur
+
+    def run(self, w, theta, nsteps):
+        """set_state + prepare + step; returns this rank's cells of the final state."""
+        self.prepare(theta)
+        self.set_state(w)
+        self.step(nsteps)
+        return self.get_state()

@@ -123,6 +123,62 @@ int64_t fvm_fused_max_cells(void);
 int fvm_theta_run_fused(const fvm_problem* prob, const double* dt, double theta, int64_t nsteps,
                         int64_t checkpoint_every, double* w, double* ckpt, void* stream);
 
+/* ---- Variant 3: partitioned SPIKE/Thomas for LONG systems (one huge mesh, or a batch of long
+ * ones), optionally with the cells split in contiguous slabs over several GPUs.  Replaces the
+ * same loop (fvm_classes.py:373-377,408-411) where J is far beyond what fits on chip; the
+ * reference itself cannot assemble such sizes (.todok() at :303).
+ *
+ * A slab of n_tiles tiles of T = fvm_spike_tile_cells(config) cells starts at global tile
+ * `tile_offset`.  The last cell of a tile is a separator; the separators of ALL tiles of ALL
+ * slabs form one tridiagonal "reduced" system (n_global unknowns per problem) that every rank
+ * solves redundantly after an all-gather of its right-hand side (the host layer owns the NCCL
+ * call).  State arrays are ghosted: `w` points at the slab's first cell, w[-1] and w[n_tiles*T]
+ * hold the neighbouring slabs' edge values, and w_stride >= n_tiles*T + 2 separates problems.
+ * Work arrays (all caller-owned): p, q, b, Vt, Wt [P][n_tiles*T]; sep [P][n_tiles][10];
+ * bends [P][2]; rs, rr [P][n_tiles]; g_first [P]; xs, rp, rq, rinv [P][n_global]. */
+
+/* Cells per tile of a tile configuration (0: production, 8192; 1: small tiles for tests), 0 if
+ * the configuration does not exist. */
+int64_t fvm_spike_tile_cells(int32_t config);
+
+/* Once per model: rows of A = I - dt*theta*alpha*M for the slab (prob->faces / a / d are indexed
+ * by GLOBAL cell, so pass base pointers shifted by the slab offset), tile-local LU (p, q, b),
+ * tile spikes (Vt, Wt), per-tile separator rows and reduced-system contributions (sep), the
+ * scaled beta entries (bends) and, in extents[0..1] (device int32), how many cells from the
+ * left/right tile edge carry a spike larger than spike_tol. */
+int fvm_spike_setup(const fvm_problem* prob, const double* dt, double theta, int64_t tile_offset,
+                    int64_t n_tiles, int32_t config, double* p, double* q, double* b, double* Vt,
+                    double* Wt, double* sep, double* bends, int32_t* extents, double spike_tol,
+                    void* stream);
+
+/* Once per model: Thomas factors (rp, rq, rinv) of the reduced tridiagonal (RL, RD, RU), n
+ * unknowns per problem. */
+int fvm_spike_reduced_factor(int64_t n, int64_t P, const double* RL, const double* RD,
+                             const double* RU, double* rp, double* rq, double* rinv, void* stream);
+
+/* Step, part 1: r~ = inv*(B w) and the tile-local solves (w_in -> w_out = g), the separators'
+ * right-hand sides rs, the reduced right-hand side rr (the last tile of the slab leaves out the
+ * term that needs the next slab's first cell) and g_first = g at the slab's first cell.
+ * has_first_cell: the slab holds global cell 0; last_cell_local: local index of global cell J-1
+ * if it is a tile-interior cell of this slab and carries a nonzero beta, else -1. */
+int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                    const double* b, const double* sep, const double* bends,
+                    int32_t has_first_cell, int64_t last_cell_local, double theta,
+                    const double* w_in, double* w_out, int64_t w_stride, double* rs, double* rr,
+                    int64_t rr_stride, double* g_first, void* stream);
+
+/* Step, part 2: solve the factored reduced system, rr -> xs, n_global unknowns per problem. */
+int fvm_spike_reduce_solve(int64_t n_global, int64_t P, const double* rp, const double* rq,
+                           const double* rinv, const double* rr, double* xs, void* stream);
+
+/* Step, part 3: x = g - Vt*xs(k-1) - Wt*xs(k) over the spike extents (extents_host: the two
+ * HOST integers read back from fvm_spike_setup), separators = xs, ghost cells refreshed
+ * (next_first [P]: the next slab's new first value, NULL on the last slab).  In place on w. */
+int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, const int32_t* extents_host,
+                       int64_t tile_offset, int64_t n_tiles_global, const double* Vt,
+                       const double* Wt, const double* xs, double* w, int64_t w_stride,
+                       const double* next_first, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
