@@ -59,6 +59,7 @@ _SIGNATURES = {
     "fvm_theta_run_fused": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_dbl, c_i64, c_i64,
                                            c_ptr, c_ptr, c_ptr]),
     "fvm_spike_tile_cells": (c_i64, [c_i32]),
+    "fvm_spike_tile_threads": (c_i64, [c_i32]),
     "fvm_spike_setup": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_dbl, c_i64, c_i64, c_i32,
                                        c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_dbl, c_ptr]),
     "fvm_spike_reduced_factor": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),

@@ -25,6 +25,14 @@
 // All indices are LOCAL to the rank's slab unless they say "global"; the slab starts at global
 // cell j_offset = tile_offset*T.  State arrays carry one ghost cell on each side
 // (w[-1], w[n_local]) that holds the neighbouring rank's edge value.
+//
+// LAYOUT.  Thread t of a tile's CTA owns the CPT consecutive cells [t*CPT, (t+1)*CPT) (the
+// recurrences need a blocked ownership), but every per-cell array of the library (p, q, b, Vt,
+// Wt and the state w) stores cell r = t*CPT + c of a tile at  c*TPB + t  ("tiled" order), so that
+// a warp's load of its c-th cells is two full 128-byte lines.  With the natural order the same
+// loads touch 32 lines each and the kernel is bound by L1 tag look-ups at 30 % of HBM speed
+// (profiles/r01_spike_launches_natural.csv).  The first and last positions of a tile are its
+// first and last cell in both orders, so ghosts and tile neighbours need no special casing.
 #include "fvm_device.cuh"
 
 namespace fvm {
@@ -123,6 +131,9 @@ __device__ __forceinline__ void cta_backward(double (&x)[CPT], const double (&q)
   for (int c = CPT - 1; c >= 0; --c) { nxt = fma(-q[c], nxt, x[c]); x[c] = nxt; }
 }
 
+// Position of cell r (0..T-1) of a tile in the tiled order.
+__device__ __forceinline__ int tiled_pos(int r, int TPB, int CPT) { return (r % CPT) * TPB + r / CPT; }
+
 // Per-tile constants, SEP_STRIDE doubles per tile.
 enum { SEP_LO = 0, SEP_UP, SEP_BLO, SEP_BDI, SEP_BUP, SEP_BETA, SEP_RL, SEP_RDA, SEP_V0, SEP_W0, SEP_STRIDE };
 
@@ -130,8 +141,8 @@ enum { SEP_LO = 0, SEP_UP, SEP_BLO, SEP_BDI, SEP_BUP, SEP_BETA, SEP_RL, SEP_RDA,
 // Rows of A for the local cells; lo -> p, di -> b, up -> q (transformed in place by the next kernel).
 __global__ void __launch_bounds__(256) spike_assemble_kernel(fvm_problem pr, const double* __restrict__ dt,
                                                              double theta, int64_t j_offset, int64_t n_local,
-                                                             double* __restrict__ p, double* __restrict__ q,
-                                                             double* __restrict__ b) {
+                                                             int TPB, int CPT, double* __restrict__ p,
+                                                             double* __restrict__ q, double* __restrict__ b) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t pi = blockIdx.y;
   if (i >= n_local) return;
@@ -142,22 +153,25 @@ __global__ void __launch_bounds__(256) spike_assemble_kernel(fvm_problem pr, con
     Row m = assemble_row(pr, pi, j, kap, D);
     a = theta_lhs_row(m, mul(dt[pi], theta), alpha_of(j, pr.J, pr.alpha_left, pr.alpha_right));
   }
-  const int64_t o = pi * n_local + i;
+  const int T = TPB * CPT;
+  const int64_t o = pi * n_local + (i / T) * T + tiled_pos((int)(i % T), TPB, CPT);
   p[o] = a.lo; b[o] = a.di; q[o] = a.up;
 }
 
 // One thread per tile: LU of the interior block restarted at the tile's first cell, the tile
 // spikes, the separator's rows and the tile's contribution to the reduced system.
 __global__ void __launch_bounds__(128) spike_tile_factor_kernel(
-    fvm_problem pr, double theta, int64_t tile_offset, int64_t n_tiles, int T, double* __restrict__ p,
+    fvm_problem pr, double theta, int64_t tile_offset, int64_t n_tiles, int TPB, int CPT, double* __restrict__ p,
     double* __restrict__ q, double* __restrict__ b, double* __restrict__ Vt, double* __restrict__ Wt,
     double* __restrict__ sep, double* __restrict__ bends, int* __restrict__ extents, double spike_tol) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t pi = blockIdx.y;
   if (k >= n_tiles) return;
   const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
+  const int T = TPB * CPT;
   const int64_t base = (pi * n_tiles + k) * T;
   const int64_t jg0 = (tile_offset + k) * T;               // global index of the tile's first cell
+  auto at = [&](int r) { return base + tiled_pos(r, TPB, CPT); };
   double beta_l = 0.0, beta_r = 0.0;
   if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
     beta_l = dvd(pr.left_flux[pi], sub(pr.faces[1], pr.faces[0]));
@@ -166,40 +180,43 @@ __global__ void __launch_bounds__(128) spike_tile_factor_kernel(
   const int N = T - 1;                                     // interior cells
   double q_prev = 0.0, gv = 0.0;
   for (int c = 0; c < N; ++c) {
-    const double lo = p[base + c], di = b[base + c], up = q[base + c];
+    const int64_t o = at(c);
+    const double lo = p[o], di = b[o], up = q[o];
     const double inv = 1.0 / (di - lo * q_prev);
     const double pc = lo * inv;
     q_prev = up * inv;
     gv = (c == 0) ? pc : -pc * gv;                         // forward sweep of the left spike
-    p[base + c] = pc; q[base + c] = q_prev; b[base + c] = inv * (rth - cth * di);
-    Vt[base + c] = gv;
+    p[o] = pc; q[o] = q_prev; b[o] = inv * (rth - cth * di);
+    Vt[o] = gv;
     if (jg0 + c == 0) bends[2 * pi] = beta_l * inv;        // beta[0] as it enters the sweep
     if (jg0 + c == pr.J - 1) bends[2 * pi + 1] = beta_r * inv;   // beta[J-1] when cell J-1 is a tile-interior cell
   }
   double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
   {
-    const double lo = p[base + N], di = b[base + N], up = q[base + N];
+    const int64_t oN = at(N);
+    const double lo = p[oN], di = b[oN], up = q[oN];
     s[SEP_LO] = lo; s[SEP_UP] = up;
     s[SEP_BLO] = -cth * lo; s[SEP_BDI] = rth - cth * di; s[SEP_BUP] = -cth * up;
     double bs = 0.0;
     if (jg0 + N == 0) bs += beta_l;
     if (jg0 + N == pr.J - 1) bs += beta_r;
     s[SEP_BETA] = bs;
-    p[base + N] = 0.0; q[base + N] = 0.0; b[base + N] = 0.0;   // separator: not part of the tile solve
-    Vt[base + N] = 0.0; Wt[base + N] = 0.0;
+    p[oN] = 0.0; q[oN] = 0.0; b[oN] = 0.0;                 // separator: not part of the tile solve
+    Vt[oN] = 0.0; Wt[oN] = 0.0;
     // backward sweeps of both spikes
-    double vn = Vt[base + N - 1], un = q[base + N - 1];
-    Wt[base + N - 1] = un;
+    double vn = Vt[at(N - 1)], un = q[at(N - 1)];
+    Wt[at(N - 1)] = un;
+    const double vlast = vn, ulast = un;
     int eL = (fabs(vn) > spike_tol) ? N : 0, eR = 1;
     for (int c = N - 2; c >= 0; --c) {
-      const double qc = q[base + c];
-      vn = Vt[base + c] - qc * vn;
+      const int64_t o = at(c);
+      const double qc = q[o];
+      vn = Vt[o] - qc * vn;
       un = -qc * un;
-      Vt[base + c] = vn; Wt[base + c] = un;
+      Vt[o] = vn; Wt[o] = un;
       if (fabs(vn) > spike_tol && c + 1 > eL) eL = c + 1;  // cells [0, eL) need the left correction
       if (fabs(un) > spike_tol) eR = N - c;                // cells [N-eR, N) need the right correction
     }
-    const double vlast = Vt[base + N - 1], ulast = Wt[base + N - 1];
     s[SEP_RL] = -lo * vlast;
     s[SEP_RDA] = di - lo * ulast;                          // the -up*V0(k+1) term is added by the host
     s[SEP_V0] = vn; s[SEP_W0] = un;
@@ -235,13 +252,19 @@ __global__ void __launch_bounds__(TPB) tile_solve_kernel(
   constexpr int T = TPB * CPT;
   __shared__ double sm[66];
   const int64_t k = blockIdx.x, pi = blockIdx.y;
-  const int64_t base = (pi * n_tiles + k) * T + (int64_t)threadIdx.x * CPT;     // into p, q, b
-  const int64_t wbase = pi * w_stride + k * T + (int64_t)threadIdx.x * CPT;     // into w (ghosted)
+  const int tid = threadIdx.x;
+  const int64_t base = (pi * n_tiles + k) * T + tid;                 // into p, q, b (tiled: + c*TPB)
+  const int64_t wbase = pi * w_stride + k * T;                       // tile's first position in w (ghosted)
   double w[CPT + 2], pc[CPT], qc[CPT], g[CPT];
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) { pc[c] = p[base + c]; qc[c] = q[base + c]; g[c] = b[base + c]; }
-#pragma unroll
-  for (int c = 0; c < CPT + 2; ++c) w[c] = w_in[wbase + c - 1];
+  for (int c = 0; c < CPT; ++c) {
+    pc[c] = p[base + c * TPB]; qc[c] = q[base + c * TPB]; g[c] = b[base + c * TPB];
+    w[c + 1] = w_in[wbase + c * TPB + tid];
+  }
+  // left neighbour of this thread's first cell = last cell of thread tid-1 (or the position just
+  // before the tile: previous tile's separator / the left ghost); right neighbour likewise
+  w[0] = w_in[tid == 0 ? wbase - 1 : wbase + (CPT - 1) * TPB + tid - 1];
+  w[CPT + 1] = w_in[tid == TPB - 1 ? wbase + T : wbase + tid + 1];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
     if (MODE == 2) {
@@ -253,7 +276,7 @@ __global__ void __launch_bounds__(TPB) tile_solve_kernel(
   }
   if (has_first_cell && k == 0 && threadIdx.x == 0) g[0] += bends[2 * pi];
   {                                                        // beta[J-1] at a tile-interior cell (rare)
-    const int64_t l0 = k * T + (int64_t)threadIdx.x * CPT;
+    const int64_t l0 = k * T + (int64_t)tid * CPT;
     if (jl_last >= l0 && jl_last < l0 + CPT) {
       const int cl = (int)(jl_last - l0);
 #pragma unroll
@@ -267,21 +290,22 @@ __global__ void __launch_bounds__(TPB) tile_solve_kernel(
   cta_forward<TPB, CPT>(g, pc, sm, 0.0, nullptr);
   cta_backward<TPB, CPT>(g, qc, sm, 0.0, nullptr);
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) w_out[wbase + c] = g[c];
+  for (int c = 0; c < CPT; ++c) w_out[wbase + c * TPB + tid] = g[c];
 }
 
 // rr_k = rs_k - lo_k g_last(k) - up_k g_first(k+1); the last local tile leaves the g_first term
 // to whoever knows the next rank's first cell (g_first_out[pi] = this rank's own first value).
-__global__ void __launch_bounds__(256) reduced_rhs_kernel(int64_t n_tiles, int T, const double* __restrict__ sep,
+__global__ void __launch_bounds__(256) reduced_rhs_kernel(int64_t n_tiles, int TPB, int CPT, const double* __restrict__ sep,
                                                           const double* __restrict__ rs, const double* __restrict__ g,
                                                           int64_t w_stride, double* __restrict__ rr,
                                                           int64_t rr_stride, double* __restrict__ g_first_out) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t pi = blockIdx.y;
   if (k >= n_tiles) return;
+  const int T = TPB * CPT;
   const double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
   const double* gp = g + pi * w_stride + k * T;
-  double r = fma(-s[SEP_LO], gp[T - 2], rs[pi * n_tiles + k]);
+  double r = fma(-s[SEP_LO], gp[tiled_pos(T - 2, TPB, CPT)], rs[pi * n_tiles + k]);
   if (k + 1 < n_tiles) r = fma(-s[SEP_UP], gp[T], r);
   rr[pi * rr_stride + k] = r;
   if (k == 0) g_first_out[pi] = gp[0];
@@ -343,35 +367,39 @@ __global__ void __launch_bounds__(TPB) reduced_solve_kernel(int64_t n, const dou
 }
 
 // x = g - Vt*xs(k-1) - Wt*xs(k) over the spike extents, x_sep = xs(k); also refreshes the two
-// ghost cells of the local state.  xs is indexed GLOBALLY (tile_offset + k).
-__global__ void __launch_bounds__(256) correct_kernel(int64_t n_tiles, int T, int eL, int eR, int64_t tile_offset,
-                                                      int64_t n_tiles_global, const double* __restrict__ Vt,
-                                                      const double* __restrict__ Wt, const double* __restrict__ xs,
-                                                      double* __restrict__ w, int64_t w_stride,
-                                                      const double* __restrict__ next_first) {
-  const int per_tile = eL + eR + 1;
+// ghost cells of the local state.  xs is indexed GLOBALLY (tile_offset + k).  The extents are
+// rounded up to whole threads' chunks: tl threads from the left edge, tr from the right; items
+// are enumerated in tiled order so that the accesses coalesce.
+__global__ void __launch_bounds__(256) correct_kernel(int64_t n_tiles, int TPB, int CPT, int tl, int tr,
+                                                      int64_t tile_offset, int64_t n_tiles_global,
+                                                      const double* __restrict__ Vt, const double* __restrict__ Wt,
+                                                      const double* __restrict__ xs, double* __restrict__ w,
+                                                      int64_t w_stride, const double* __restrict__ next_first) {
+  const int T = TPB * CPT;
+  const int per_tile = (tl + tr) * CPT + 1;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t pi = blockIdx.y;
   if (idx >= n_tiles * per_tile) return;
   const int64_t k = idx / per_tile;
-  const int r = (int)(idx - k * per_tile);
-  const int N = T - 1;
+  const int m = (int)(idx - k * per_tile);
   const double* X_ = xs + pi * n_tiles_global;
   const int64_t kg = tile_offset + k;
   const double xk = X_[kg];
   const double xl = (kg > 0) ? X_[kg - 1] : 0.0;
   double* wp = w + pi * w_stride + k * T;
-  if (r == eL + eR) {                                      // the separator itself, and the ghosts
-    wp[N] = xk;
+  if (m == (tl + tr) * CPT) {                              // the separator itself, and the ghosts
+    wp[T - 1] = xk;
     if (k == 0) wp[-1] = xl;                               // left ghost = previous rank's last separator
     if (k == n_tiles - 1) wp[T] = next_first ? next_first[pi] : 0.0;   // right ghost = next rank's first cell
     return;
   }
-  int c;
-  if (r < eL) c = r;
-  else { c = N - eR + (r - eL); if (c < eL) return; }      // extents overlap: each cell once
-  const int64_t o = (pi * n_tiles + k) * T + c;
-  wp[c] = fma(-Wt[o], xk, fma(-Vt[o], xl, wp[c]));
+  int t, c;
+  if (m < tl * CPT) { c = m / tl; t = m % tl; }
+  else { const int m2 = m - tl * CPT; c = m2 / tr; t = TPB - tr + m2 % tr; }
+  if (t == TPB - 1 && c == CPT - 1) return;                // the separator is written above
+  const int pos = c * TPB + t;
+  const int64_t o = (pi * n_tiles + k) * T + pos;
+  wp[pos] = fma(-Wt[o], xk, fma(-Vt[o], xl, wp[pos]));
 }
 
 }  // namespace fvm
@@ -379,11 +407,17 @@ __global__ void __launch_bounds__(256) correct_kernel(int64_t n_tiles, int T, in
 // ------------------------------------------------------------------------------------------ C-ABI
 namespace {
 constexpr int kTileCfgs = 2;
-inline int tile_cells(int cfg) { return cfg == 0 ? 512 * 16 : 64 * 4; }
+inline int tile_threads(int cfg) { return cfg == 0 ? 512 : 64; }
+inline int tile_cpt(int cfg) { return cfg == 0 ? 16 : 4; }
+inline int tile_cells(int cfg) { return tile_threads(cfg) * tile_cpt(cfg); }
 }
 
 extern "C" int64_t fvm_spike_tile_cells(int32_t config) {
   return (config >= 0 && config < kTileCfgs) ? tile_cells(config) : 0;
+}
+
+extern "C" int64_t fvm_spike_tile_threads(int32_t config) {
+  return (config >= 0 && config < kTileCfgs) ? tile_threads(config) : 0;
 }
 
 extern "C" int fvm_spike_setup(const fvm_problem* prob, const double* dt, double theta, int64_t tile_offset,
@@ -405,10 +439,12 @@ extern "C" int fvm_spike_setup(const fvm_problem* prob, const double* dt, double
   e = cudaMemsetAsync(bends, 0, 2 * prob->P * sizeof(double), s);
   if (e != cudaSuccess) return (int)e;
   dim3 g1((unsigned)((n_local + 255) / 256), (unsigned)prob->P);
-  fvm::spike_assemble_kernel<<<g1, 256, 0, s>>>(*prob, dt, theta, tile_offset * T, n_local, p, q, b);
+  fvm::spike_assemble_kernel<<<g1, 256, 0, s>>>(*prob, dt, theta, tile_offset * T, n_local, tile_threads(config),
+                                                tile_cpt(config), p, q, b);
   dim3 g2((unsigned)((n_tiles + 127) / 128), (unsigned)prob->P);
-  fvm::spike_tile_factor_kernel<<<g2, 128, 0, s>>>(*prob, theta, tile_offset, n_tiles, T, p, q, b, Vt, Wt, sep,
-                                                   bends, (int*)extents, spike_tol);
+  fvm::spike_tile_factor_kernel<<<g2, 128, 0, s>>>(*prob, theta, tile_offset, n_tiles, tile_threads(config),
+                                                   tile_cpt(config), p, q, b, Vt, Wt, sep, bends, (int*)extents,
+                                                   spike_tol);
   return (int)cudaGetLastError();
 }
 
@@ -454,8 +490,8 @@ extern "C" int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const
                                           w_in, w_out, rs, w_stride, s);
   if (st) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
-  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_cells(config), sep, rs, w_out, w_stride, rr, rr_stride,
-                                            g_first);
+  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,
+                                            rr, rr_stride, g_first);
   return (int)cudaGetLastError();
 }
 
@@ -476,12 +512,16 @@ extern "C" int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, co
                                   void* stream) {
   if (!extents_host || !Vt || !Wt || !xs || !w || n_tiles < 1 || P < 1 || P > 65535) return FVM_ERR_INVALID_ARG;
   if (config < 0 || config >= kTileCfgs) return FVM_ERR_INVALID_ARG;
-  const int T = tile_cells(config);
-  int eL = extents_host[0], eR = extents_host[1];
+  const int T = tile_cells(config), TPB = tile_threads(config), CPT = tile_cpt(config);
+  const int eL = extents_host[0], eR = extents_host[1];
   if (eL < 0 || eR < 0 || eL > T - 1 || eR > T - 1) return FVM_ERR_INVALID_ARG;
-  const int64_t total = n_tiles * (int64_t)(eL + eR + 1);
+  int tl = (eL + CPT - 1) / CPT;                           // whole threads' chunks from the left edge
+  int tr = TPB - (T - 1 - eR) / CPT;                       // ... and from the right edge
+  if (tl > TPB) tl = TPB;
+  if (tr > TPB - tl) tr = TPB - tl;                        // the two ranges never overlap
+  const int64_t total = n_tiles * (int64_t)((tl + tr) * CPT + 1);
   dim3 g((unsigned)((total + 255) / 256), (unsigned)P);
-  fvm::correct_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(n_tiles, T, eL, eR, tile_offset, n_tiles_global, Vt, Wt, xs,
-                                                          w, w_stride, next_first);
+  fvm::correct_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(n_tiles, TPB, CPT, tl, tr, tile_offset, n_tiles_global, Vt,
+                                                          Wt, xs, w, w_stride, next_first);
   return (int)cudaGetLastError();
 }

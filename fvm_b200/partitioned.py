@@ -100,6 +100,8 @@ class PartitionedAdvectionDiffusionModel(object):
         self.T = int(lib.fvm_spike_tile_cells(self.config))
         if self.T == 0:
             raise ValueError("unknown tile configuration %r" % (config,))
+        self.TPB = int(lib.fvm_spike_tile_threads(self.config))
+        self.CPT = self.T // self.TPB
         self.local_input = J is not None
         self.J = int(J) if J is not None else int(np.shape(faces)[-1]) - 1
         if self.J < 3:
@@ -253,7 +255,10 @@ class PartitionedAdvectionDiffusionModel(object):
             raise ValueError("state has %d cells per problem, expected %d" % (w.shape[1], n_real))
         buf = self._wbuf[0]
         buf.zero_()
-        buf[:, 1:1 + n_real] = w
+        nat = torch.zeros((self.P, self.n_local), dtype=torch.float64, device=self.device)
+        nat[:, :n_real] = w
+        # natural -> tiled order inside every tile (include/fvm_b200.h: fvm_spike_tile_threads)
+        buf[:, 1:1 + self.n_local] = nat.view(self.P, self.nt, self.TPB, self.CPT).transpose(2, 3).reshape(self.P, -1)
         edges = torch.stack([buf[:, 1], buf[:, self.n_local]], dim=1)          # first / last local cell
         if self.comm.world > 1:
             allv = self.comm.all_gather(edges)                                  # [world, P, 2]
@@ -266,7 +271,8 @@ class PartitionedAdvectionDiffusionModel(object):
 
     def get_state(self):
         """This rank's cells, (P, j1-j0)."""
-        return self._wbuf[self._cur][:, 1:1 + (self.j1 - self.j0)].clone()
+        til = self._wbuf[self._cur][:, 1:1 + self.n_local].view(self.P, self.nt, self.CPT, self.TPB)
+        return til.transpose(2, 3).reshape(self.P, -1)[:, :self.j1 - self.j0].contiguous()
 
     # ------------------------------------------------------------------ stepping
     def step(self, nsteps=1):

@@ -84,3 +84,25 @@ def stiff_reaction(P=4096, J=1 << 20, seed=0, first=0, count=None):
     w0 = 0.1 + np.exp(-((c[None, :] - x0[:, None]) / 0.05) ** 2)
     return dict(faces=faces, a=a, d=d, k=k, reaction=r, w0=w0, theta=1.0,
                 bc=dict(left_flux=0.0, right_flux=0.0))
+
+
+def graded_slab(J, j0, j1, device, ratio=100.0):
+    """cfg 5: the cells [j0, j1) of a J-cell graded mesh (h_0/h_{J-1} = ratio) generated ON THE
+    DEVICE from the closed form of the geometric series, faces_j = (1 - r^j)/(1 - r^J), so that
+    no rank ever holds the whole 2^30-cell mesh and every rank computes identical values for the
+    faces it shares with its neighbours.  Returns the local arrays in the layout
+    PartitionedAdvectionDiffusionModel(J=...) expects (one ghost face/cell on each side where the
+    mesh continues), the scalar d for Pe_max = 2 with a = 1, dt = 4 h_min / a, and the initial
+    state sin(pi c)^100 + 0.1 for the owned cells."""
+    import math
+    import torch
+    lr = -math.log(ratio) / (J - 1)
+    f_lo, f_hi = max(j0 - 1, 0), min(j1 + 1, J)
+    j = torch.arange(f_lo, f_hi + 1, device=device, dtype=torch.float64)
+    faces = torch.expm1(j * lr) / math.expm1(J * lr)
+    h_max = math.expm1(lr) / math.expm1(J * lr)              # width of cell 0
+    h_min = h_max / ratio
+    own = faces[(j0 - f_lo):(j1 - f_lo + 1)]
+    c = 0.5 * (own[1:] + own[:-1])
+    w0 = torch.sin(math.pi * c) ** 100 + 0.1
+    return dict(faces=faces, d_pe2=h_max / 2.0, dt=4.0 * h_min, w0=w0[None, :], h_min=h_min, h_max=h_max)

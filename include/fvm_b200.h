@@ -141,6 +141,12 @@ int fvm_theta_run_fused(const fvm_problem* prob, const double* dt, double theta,
  * the configuration does not exist. */
 int64_t fvm_spike_tile_cells(int32_t config);
 
+/* Threads TPB of the CTA that owns a tile.  Every per-cell array of variant 3 (p, q, b, Vt, Wt
+ * and the state w) is stored TILED: cell r of a tile (thread r/CPT, its cell r%CPT, with
+ * CPT = tile_cells/TPB) sits at position (r % CPT)*TPB + r/CPT of the tile, so that the CTA's
+ * loads coalesce.  Callers convert their state once on the way in and once on the way out. */
+int64_t fvm_spike_tile_threads(int32_t config);
+
 /* Once per model: rows of A = I - dt*theta*alpha*M for the slab (prob->faces / a / d are indexed
  * by GLOBAL cell, so pass base pointers shifted by the slab offset), tile-local LU (p, q, b),
  * tile spikes (Vt, Wt), per-tile separator rows and reduced-system contributions (sep), the
