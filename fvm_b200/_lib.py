@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libfvm_b200.so")
 FVM_OK = 0
 FVM_ERR_INVALID_ARG = -1
 FVM_ERR_UNSUPPORTED = -2
+FVM_ERR_SCRATCH_LIMIT = -3
 CENTRAL, UPWIND, EXPONENTIAL = 0, 1, 2
 SCHEMES = {"central": CENTRAL, "upwind": UPWIND, "exponential": EXPONENTIAL}
 BC_DIRICHLET, BC_ROBIN = 0, 1
@@ -65,6 +66,9 @@ _SIGNATURES = {
     "fvm_spike_reduced_factor": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "fvm_spike_local": (ctypes.c_int, [c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_i64,
                                        c_dbl, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr, c_ptr]),
+    "fvm_spike_static_max_tiles": (c_i64, []),
+    "fvm_spike_local_static": (ctypes.c_int, [c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_i64,
+                                              c_dbl, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr]),
     "fvm_spike_reduce_solve": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "fvm_spike_finalize": (ctypes.c_int, [c_i64, c_i64, c_i32, ctypes.POINTER(c_i32), c_i64, c_i64, c_ptr, c_ptr,
                                           c_ptr, c_ptr, c_i64, c_ptr, c_ptr]),

@@ -34,6 +34,7 @@
 // (profiles/r01_spike_launches_natural.csv).  The first and last positions of a tile are its
 // first and last cell in both orders, so ghosts and tile neighbours need no special casing.
 #include "fvm_device.cuh"
+#include <mutex>
 
 namespace fvm {
 
@@ -523,5 +524,75 @@ extern "C" int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, co
   dim3 g((unsigned)((total + 255) / 256), (unsigned)P);
   fvm::correct_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(n_tiles, TPB, CPT, tl, tr, tile_offset, n_tiles_global, Vt,
                                                           Wt, xs, w, w_stride, next_first);
+  return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
+// fvm_spike_local_static: fvm_spike_local for callers that cannot provide the `rs` work array.
+//
+// Between its two kernels fvm_spike_local parks the separators' right-hand sides in `rs`, an
+// array the caller must allocate.  A time loop that lives inside a larger application often
+// cannot do that: the application may have handed every byte of device memory to its own pool
+// when it started, or the step may sit in a latency-critical section where cudaMalloc is not
+// acceptable because it synchronises the whole device.  For such callers the scratch lives in
+// the library image itself, in the fixed-size device array below: every GPU that loads
+// libfvm_b200.so carries these 512 KiB until the process exits, and a call needs
+// P * n_tiles <= FVM_SPIKE_STATIC_MAX_TILES.
+namespace {
+constexpr int64_t kStaticMaxTiles = 65536;
+static __device__ __align__(256) double g_spike_rs_scratch[kStaticMaxTiles];
+
+constexpr int kMaxDevices = 64;
+double* g_scratch_addr[kMaxDevices];      // device address of the array above, per device
+bool g_scratch_known[kMaxDevices];
+std::mutex g_scratch_mutex;
+
+// The array's name is only a handle in host code; the address a kernel can use has to be asked
+// for, once per device, while that device is current.
+int static_scratch(double** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kMaxDevices) return FVM_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_scratch_mutex);
+  if (!g_scratch_known[dev]) {
+    double* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_spike_rs_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (ptr == nullptr) return (int)cudaErrorInvalidSymbol;
+    g_scratch_addr[dev] = ptr;
+    g_scratch_known[dev] = true;
+  }
+  *out = g_scratch_addr[dev];
+  return FVM_OK;
+}
+}  // namespace
+
+extern "C" int64_t fvm_spike_static_max_tiles(void) { return kStaticMaxTiles; }
+
+extern "C" int fvm_spike_local_static(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                                      const double* b, const double* sep, const double* bends,
+                                      int32_t has_first_cell, int64_t last_cell_local, double theta,
+                                      const double* w_in, double* w_out, int64_t w_stride, double* rr,
+                                      int64_t rr_stride, double* g_first, void* stream) {
+  if (!p || !q || !b || !sep || !bends || !w_in || !w_out || !rr || !g_first) return FVM_ERR_INVALID_ARG;
+  if (n_tiles < 1 || P < 1 || P > 65535 || !(theta > 0.0 && theta <= 1.0)) return FVM_ERR_INVALID_ARG;
+  if (config < 0 || config >= kTileCfgs || n_tiles > 0x7fffffffLL) return FVM_ERR_INVALID_ARG;
+  if (n_tiles > kStaticMaxTiles || P * n_tiles > kStaticMaxTiles) return FVM_ERR_SCRATCH_LIMIT;
+  double* rs = nullptr;
+  int st = static_scratch(&rs);
+  if (st) return st;
+  // Nothing in the scratch has to start at zero: the first kernel writes every entry
+  // [0, P*n_tiles) before the second one reads it; what earlier calls left behind is overwritten.
+  cudaStream_t s = (cudaStream_t)stream;
+  st = config == 0
+           ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
+                                        w_out, rs, w_stride, s)
+           : launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
+                                      w_out, rs, w_stride, s);
+  if (st) return st;
+  dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
+  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,
+                                            rr, rr_stride, g_first);
   return (int)cudaGetLastError();
 }

@@ -30,6 +30,7 @@ extern "C" {
 #define FVM_OK 0
 #define FVM_ERR_INVALID_ARG (-1)  /* NULL pointer, J < 3, P < 1, theta outside (0, 1], bad enum */
 #define FVM_ERR_UNSUPPORTED (-2)  /* size outside what this entry point handles               */
+#define FVM_ERR_SCRATCH_LIMIT (-3) /* fvm_spike_local_static: P*n_tiles exceeds the built-in scratch */
 
 /* discretisation of the advective flux [fvm_classes.py:116-128] */
 #define FVM_CENTRAL 0
@@ -184,6 +185,30 @@ int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, const int32_t
                        int64_t tile_offset, int64_t n_tiles_global, const double* Vt,
                        const double* Wt, const double* xs, double* w, int64_t w_stride,
                        const double* next_first, void* stream);
+
+/* Largest P * n_tiles fvm_spike_local_static accepts (65536 tiles = 512 KiB of scratch). */
+int64_t fvm_spike_static_max_tiles(void);
+
+/* fvm_spike_local without the `rs` work array.  NO COUNTERPART IN THE REFERENCE: it exists for
+ * callers of this library that cannot allocate device memory for a step -- an application that
+ * gave all of the GPU's memory to its own pool at start-up, or a time loop in a latency-critical
+ * section where cudaMalloc (which synchronises the device) must not be called.  The scratch that
+ * fvm_spike_local takes from the caller lives in a fixed device array inside the library
+ * instead: 512 KiB that every GPU which loads the library holds until the process exits.
+ *  - Same arguments, results and status codes as fvm_spike_local, minus `rs`; allocates nothing.
+ *  - P * n_tiles must not exceed fvm_spike_static_max_tiles(); beyond that the call returns
+ *    FVM_ERR_SCRATCH_LIMIT and launches nothing (use fvm_spike_local with your own `rs`).
+ *  - The first call on each device looks up the device address of the built-in array (with that
+ *    device current) and remembers it; make that first call before any stream capture begins.
+ *  - All calls on a device share the one array, and it keeps what the last call wrote.  Nothing in
+ *    it needs clearing (each call overwrites the part it uses before reading it), but two calls
+ *    whose kernels overlap on the GPU -- different streams, or several host threads -- race on it:
+ *    keep calls on one device in stream order. */
+int fvm_spike_local_static(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                           const double* b, const double* sep, const double* bends,
+                           int32_t has_first_cell, int64_t last_cell_local, double theta,
+                           const double* w_in, double* w_out, int64_t w_stride, double* rr,
+                           int64_t rr_stride, double* g_first, void* stream);
 
 #ifdef __cplusplus
 }
