@@ -33,6 +33,7 @@ FLOP_PER_CELL_UPDATE = 11.0          # RHS 3 FMA, forward 1 FMA, backward 1 FMA 
 FP64_INSTR_PER_CELL_UPDATE = 7.0     # what the partitioned on-chip solver issues: + 2 spike-correction FMAs
 ONCHIP_B_PER_CELL_UPDATE = 40.0      # five factored coefficients read once per step (32 B TMEM + 8 B registers)
 HBM_B_PER_CELL_UPDATE_THOMAS = 64.0  # variant 1: w, fp, fq, fb in; g out; g, fq in; w out
+HBM_B_PER_CELL_UPDATE_SPIKE = 40.0   # variant 3: w, p, q, b in; g out (three per-cell arrays streamed)
 
 
 def parse():
@@ -44,6 +45,9 @@ def parse():
     ap.add_argument("--problems", type=int, default=65536, help="problems per GPU")
     ap.add_argument("--cells", type=int, default=1024)
     ap.add_argument("--inner", type=int, default=1000, help="theta steps per bench step (one launch)")
+    ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg4", "cfg5"],
+                    help="cfg3 (default, the headline): batched on-chip; cfg4: batched long systems; "
+                         "cfg5: one mesh of 2^27 cells per GPU split over the ranks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -176,6 +180,145 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback (B200_PROFILING.md)"
 
 
+def partitioned_leg(dev, peaks, peak_src, log2_cells=26, nsteps=10):
+    """Variant 3 on one long system (cfg 5 parameters, single GPU): HBM roofline evidence."""
+    import torch
+    from fvm_b200 import PartitionedAdvectionDiffusionModel, workloads as W
+    J = 1 << log2_cells
+    sl = W.graded_slab(J, 0, J, dev)
+    m = PartitionedAdvectionDiffusionModel(sl["faces"], 1.0, sl["d_pe2"], sl["dt"], "exponential", P=1, J=J, device=dev)
+    m.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
+    m.prepare(0.5)
+    m.set_state(sl["w0"])
+    m.step(3)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(); m.step(nsteps); e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / nsteps
+    gbs = HBM_B_PER_CELL_UPDATE_SPIKE * J / (ms * 1e-3) / 1e9
+    return {"kernel": "tile_solve_kernel + reduced + correct (variant 3, one system of 2^%d cells)" % log2_cells,
+            "bound": "hbm", "cell_updates_per_s": J / (ms * 1e-3), "ms_per_theta_step": ms, "achieved": gbs,
+            "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "peak_source": peak_src,
+            "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_SPIKE,
+            "spike_extents_cells": [int(m.extents[0]), int(m.extents[1])], "tile_cells": m.T, "traffic": None}
+
+
+def run_partitioned(args):
+    """--workload cfg5: ONE graded mesh of world * 2^27 cells (2^30 at 8 GPUs), contiguous slabs per rank,
+    exponential fitting, zero-flux Robin, Crank-Nicolson, dt = 4 h_min/a; the reduced separator system is
+    all-gathered over NCCL once per theta step.
+    --workload cfg4: 256 problems per GPU x 2^20 cells, per-problem a/d/reaction, theta = 1, dt = 100 h_min/a
+    (independent problems: sharded, no communication).  One bench step = --inner theta steps (default 20/10)."""
+    import torch
+    import torch.distributed as dist
+    from fvm_b200 import PartitionedAdvectionDiffusionModel, workloads as W
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    K, Wm = args.steps, max(args.warmup, 3)
+    if args.workload == "cfg5":
+        inner = 20 if args.inner == 1000 else args.inner
+        J = world << 27
+        from fvm_b200.partitioned import plan_partition
+        T = 8192
+        j0, j1 = plan_partition(J, T, world)["ranges"][rank]
+        sl = W.graded_slab(J, j0, j1, dev)
+        m = PartitionedAdvectionDiffusionModel(sl["faces"], 1.0, sl["d_pe2"], sl["dt"], "exponential", P=1, J=J,
+                                               group=dist.group.WORLD if world > 1 else None, device=dev)
+        theta, w0, cells_rank = 0.5, sl["w0"], j1 - j0
+        desc = "cfg5 one graded mesh of %d x 2^27 = %d cells split over %d GPU(s), exponential, zero-flux Robin, " \
+               "Crank-Nicolson, dt = 4 h_min/a, SPIKE reduced system all-gathered over NCCL each step" % (world, J, world)
+    else:
+        inner = 10 if args.inner == 1000 else args.inner
+        Pn, J = 256, 1 << 20
+        wl = W.stiff_reaction(P=world * Pn, J=J, first=rank * Pn, count=Pn)
+        m = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=Pn,
+                                               reaction=wl["reaction"], device=dev)
+        theta, w0, cells_rank = 1.0, torch.as_tensor(wl["w0"], device=dev), Pn * J
+        desc = "cfg4 stiff reaction-diffusion: %d problems/GPU x 2^20 cells (BASELINE's 4,096 do not fit one GPU), " \
+               "per-problem a/d/reaction, theta = 1, dt = 100 h_min/a" % Pn
+    m.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
+    m.prepare(theta)
+    m.set_state(w0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(Wm):
+        m.step(inner)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(K):
+        m.step(inner)
+    t1.record()
+    barrier()
+    clocks = sampler.stop()
+    t = torch.tensor([t0.elapsed_time(t1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    cu_step = float(cells_rank) * inner
+    value = world * cu_step * K / (ms_total * 1e-3)
+    finite = bool(torch.isfinite(m.get_state()).all())
+    # end to end: pinned host state in, `inner` steps, pinned host state out
+    n_real = m.j1 - m.j0
+    h_in = torch.empty((m.P, n_real), dtype=torch.float64).pin_memory()
+    h_out = torch.empty((m.P, n_real), dtype=torch.float64).pin_memory()
+    h_in.copy_(w0 if w0.shape[1] == n_real else w0[:, :n_real])
+    stage = torch.empty((m.P, n_real), dtype=torch.float64, device=dev)
+
+    def e2e_step():
+        stage.copy_(h_in, non_blocking=True)
+        m.set_state(stage)
+        m.step(inner)
+        h_out.copy_(m.get_state(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    e2e_step()
+    barrier()
+    t0.record()
+    for _ in range(K):
+        e2e_step()
+    t1.record()
+    barrier()
+    te = torch.tensor([t0.elapsed_time(t1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        peaks, peak_src = measured_peaks()
+        gbs = HBM_B_PER_CELL_UPDATE_SPIKE * cu_step * K / (ms_total * 1e-3) / 1e9      # per GPU
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+                "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": desc, "theta_steps_per_bench_step": inner, "cells_per_gpu": cells_rank,
+                           "tile_cells": m.T, "spike_extents_cells": [int(m.extents[0]), int(m.extents[1])],
+                           "l2": "state and factors (%.1f GiB/GPU) exceed the 126 MB L2; no flush needed"
+                                 % (7 * cells_rank * 8 / 2 ** 30)},
+                "e2e": {"value": world * cu_step * K / (float(te.item()) * 1e-3), "unit": UNIT,
+                        "h2d_bytes_per_step": m.P * n_real * 8, "d2h_bytes_per_step": m.P * n_real * 8,
+                        "api": "PartitionedAdvectionDiffusionModel.set_state/step/get_state with pinned host state"},
+                "gpu_launches": K * inner * 5, "clocks": clocks,
+                "roofline": {"kernel": "tile_solve_kernel (variant 3)", "bound": "hbm", "achieved": gbs,
+                             "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+                             "peak_source": peak_src, "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_SPIKE,
+                             "traffic": None, "note": "per GPU; whole theta step incl. reduced solve, correction and all-gather"},
+                "cpu_baseline": None if args.no_cpu_baseline else cpu_baseline_single(1024), "finite": finite}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -277,6 +420,13 @@ def run_b200(args):
         except Exception as exc:  # noqa: BLE001
             hbm = {"error": repr(exc)}
 
+    long_leg = None
+    if rank == 0:
+        try:
+            long_leg = partitioned_leg(dev, peaks, peak_src, log2_cells=26)
+        except Exception as exc:  # noqa: BLE001
+            long_leg = {"error": repr(exc)}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -292,7 +442,7 @@ def run_b200(args):
     cu_s_kernel = cu_per_step_rank / (kernel_ms * 1e-3)
     fp64_peak = sms * 64.0 * 2.0 * f_max / 1e12                # TFLOP/s at max clock
     fp64_ach = FLOP_PER_CELL_UPDATE * cu_s_kernel / 1e12
-    issue_frac = FP64_INSTR_PER_CELL_UPDATE * cu_s_kernel / (sms * 32.0 * f_clk)   # warp-DFMA slots: 64 lanes/clk = 2 cycles per warp instruction
+    issue_frac = FP64_INSTR_PER_CELL_UPDATE * cu_s_kernel / (sms * 64.0 * f_clk)   # thread-level DFMAs issued / (64 lanes per clk per SM)
     smem_peak = sms * 128.0 * f_max / 1e9
     onchip = ONCHIP_B_PER_CELL_UPDATE * cu_s_kernel / 1e9
     roofline = {"kernel": "fused_tmem_kernel<CN> (variant 2: state in registers, coefficients in TMEM)",
@@ -317,8 +467,8 @@ def run_b200(args):
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": config(args), "e2e": e2e, "gpu_launches": K,
-            "clocks": clocks, "roofline": roofline, "roofline_streaming_variant": hbm, "cpu_baseline": cpu,
-            "finite": finite}
+            "clocks": clocks, "roofline": roofline, "roofline_streaming_variant": hbm,
+            "roofline_long_system_variant": long_leg, "cpu_baseline": cpu, "finite": finite}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -328,5 +478,7 @@ if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
         run_reference_arm(a)
-    else:
+    elif a.workload == "cfg3":
         run_b200(a)
+    else:
+        run_partitioned(a)
