@@ -610,9 +610,13 @@ static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, 
   return launch_fused<C, 0, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
 }
 
+// fused_cta.cu
+int run_fused_cta(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps, int64_t ckpt_every,
+                  double* w, double* ckpt, cudaStream_t stream);
+
 }  // namespace fvm
 
-extern "C" int64_t fvm_fused_max_cells(void) { return 32 * fvm::kFusedMaxC; }
+extern "C" int64_t fvm_fused_max_cells(void) { return 8192; }
 
 extern "C" int fvm_theta_run_fused(const fvm_problem* prob, const double* dt, double theta,
                                    int64_t nsteps, int64_t checkpoint_every, double* w,
@@ -633,5 +637,6 @@ extern "C" int fvm_theta_run_fused(const fvm_problem* prob, const double* dt, do
   if (J <= 128) return dispatch_mode<4>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
   if (J <= 256) return dispatch_mode<8>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
   if (J <= 512) return dispatch_mode<16>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
-  return dispatch_mode<32>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
+  if (J <= 32 * kFusedMaxC) return dispatch_mode<32>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
+  return run_fused_cta(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
 }

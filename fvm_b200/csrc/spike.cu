@@ -34,103 +34,10 @@
 // (profiles/r01_spike_launches_natural.csv).  The first and last positions of a tile are its
 // first and last cell in both orders, so ghosts and tile neighbours need no special casing.
 #include "fvm_device.cuh"
+#include "cta_scan.cuh"
 #include <mutex>
 
 namespace fvm {
-
-constexpr unsigned kAll = 0xffffffffu;
-
-struct Affine { double A, B; };   // x -> A*x + B
-
-// later o earlier
-__device__ __forceinline__ Affine compose(const Affine& later, const Affine& earlier) {
-  Affine r;
-  r.A = later.A * earlier.A;
-  r.B = fma(later.A, earlier.B, later.B);
-  return r;
-}
-
-// Exclusive scan of affine maps over the threads of a CTA, in thread order (REVERSE = false)
-// or in reverse thread order (REVERSE = true).  Returns the VALUE entering this thread when the
-// value entering the first thread of the order is `carry_in`; *total receives the map of the
-// whole CTA (valid in every thread).  sm: 2*32 doubles of shared memory.
-template <int TPB, bool REVERSE>
-__device__ __forceinline__ double cta_scan_affine(Affine m, double carry_in, double* sm, Affine* total) {
-  constexpr int NW = TPB / 32;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int pos = REVERSE ? 31 - lane : lane;              // position inside the warp's order
-  Affine inc = m;                                          // inclusive scan inside the warp
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    Affine o;
-    o.A = REVERSE ? __shfl_down_sync(kAll, inc.A, d) : __shfl_up_sync(kAll, inc.A, d);
-    o.B = REVERSE ? __shfl_down_sync(kAll, inc.B, d) : __shfl_up_sync(kAll, inc.B, d);
-    if (pos >= d) inc = compose(inc, o);
-  }
-  Affine exc;                                              // exclusive inside the warp
-  exc.A = REVERSE ? __shfl_down_sync(kAll, inc.A, 1) : __shfl_up_sync(kAll, inc.A, 1);
-  exc.B = REVERSE ? __shfl_down_sync(kAll, inc.B, 1) : __shfl_up_sync(kAll, inc.B, 1);
-  if (pos == 0) { exc.A = 1.0; exc.B = 0.0; }
-  if (NW == 1) {
-    if (total) {
-      total->A = __shfl_sync(kAll, inc.A, REVERSE ? 0 : 31);
-      total->B = __shfl_sync(kAll, inc.B, REVERSE ? 0 : 31);
-    }
-    return fma(exc.A, carry_in, exc.B);
-  }
-  __syncthreads();                                         // sm may still be in use by a previous scan
-  if (pos == 31) { sm[warp] = inc.A; sm[32 + warp] = inc.B; }
-  __syncthreads();
-  if (warp == 0) {                                         // scan of the warp totals
-    const int wi = REVERSE ? NW - 1 - lane : lane;         // warp index at this lane's position
-    Affine t; t.A = 1.0; t.B = 0.0;
-    if (lane < NW) { t.A = sm[wi]; t.B = sm[32 + wi]; }
-    Affine ti = t;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      Affine o;
-      o.A = __shfl_up_sync(kAll, ti.A, d);
-      o.B = __shfl_up_sync(kAll, ti.B, d);
-      if (lane >= d) ti = compose(ti, o);
-    }
-    Affine te;
-    te.A = __shfl_up_sync(kAll, ti.A, 1);
-    te.B = __shfl_up_sync(kAll, ti.B, 1);
-    if (lane == 0) { te.A = 1.0; te.B = 0.0; }
-    __syncwarp();
-    if (lane < NW) { sm[wi] = te.A; sm[32 + wi] = te.B; }  // exclusive prefix of warp wi
-    if (lane == NW - 1) { sm[64] = ti.A; sm[65] = ti.B; }  // map of the whole CTA
-  }
-  __syncthreads();
-  Affine wp; wp.A = sm[warp]; wp.B = sm[32 + warp];
-  if (total) { total->A = sm[64]; total->B = sm[65]; }
-  const double into_warp = fma(wp.A, carry_in, wp.B);
-  return fma(exc.A, into_warp, exc.B);
-}
-
-// g_c <- r_c - p_c * g_{c-1} along the CTA's TPB*CPT positions (thread-blocked), carry-in 0.
-template <int TPB, int CPT>
-__device__ __forceinline__ void cta_forward(double (&g)[CPT], const double (&p)[CPT], double* sm,
-                                            double carry_in, Affine* total) {
-  Affine m; m.A = 1.0; m.B = 0.0;
-#pragma unroll
-  for (int c = 0; c < CPT; ++c) { m.B = fma(-p[c], m.B, g[c]); m.A = -p[c] * m.A; }
-  double prev = cta_scan_affine<TPB, false>(m, carry_in, sm, total);
-#pragma unroll
-  for (int c = 0; c < CPT; ++c) { prev = fma(-p[c], prev, g[c]); g[c] = prev; }
-}
-
-// x_c <- g_c - q_c * x_{c+1}, from the last position to the first, carry-in (x beyond the end).
-template <int TPB, int CPT>
-__device__ __forceinline__ void cta_backward(double (&x)[CPT], const double (&q)[CPT], double* sm,
-                                             double carry_in, Affine* total) {
-  Affine m; m.A = 1.0; m.B = 0.0;
-#pragma unroll
-  for (int c = CPT - 1; c >= 0; --c) { m.B = fma(-q[c], m.B, x[c]); m.A = -q[c] * m.A; }
-  double nxt = cta_scan_affine<TPB, true>(m, carry_in, sm, total);
-#pragma unroll
-  for (int c = CPT - 1; c >= 0; --c) { nxt = fma(-q[c], nxt, x[c]); x[c] = nxt; }
-}
 
 // Position of cell r (0..T-1) of a tile in the tiled order.
 __device__ __forceinline__ int tiled_pos(int r, int TPB, int CPT) { return (r % CPT) * TPB + r / CPT; }
@@ -288,8 +195,8 @@ __global__ void __launch_bounds__(TPB) tile_solve_kernel(
     const double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
     rs[pi * n_tiles + k] = fma(s[SEP_BUP], w[CPT + 1], fma(s[SEP_BDI], w[CPT], fma(s[SEP_BLO], w[CPT - 1], s[SEP_BETA])));
   }
-  cta_forward<TPB, CPT>(g, pc, sm, 0.0, nullptr);
-  cta_backward<TPB, CPT>(g, qc, sm, 0.0, nullptr);
+  cta_forward<TPB, CPT>(g, [&](int c) { return pc[c]; }, sm, 0.0, nullptr);
+  cta_backward<TPB, CPT>(g, [&](int c) { return qc[c]; }, sm, 0.0, nullptr);
 #pragma unroll
   for (int c = 0; c < CPT; ++c) w_out[wbase + c * TPB + tid] = g[c];
 }
@@ -335,7 +242,7 @@ __global__ void __launch_bounds__(TPB) reduced_solve_kernel(int64_t n, const dou
       g[c] = in ? R_[k] * I_[k] : 0.0;
     }
     Affine tot;
-    cta_forward<TPB, CPT>(g, pc, sm, carry, &tot);
+    cta_forward<TPB, CPT>(g, [&](int c) { return pc[c]; }, sm, carry, &tot);
     carry = fma(tot.A, carry, tot.B);
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {
@@ -357,7 +264,7 @@ __global__ void __launch_bounds__(TPB) reduced_solve_kernel(int64_t n, const dou
       x[c] = in ? X_[k] : 0.0;
     }
     Affine tot;
-    cta_backward<TPB, CPT>(x, qc, sm, carry, &tot);
+    cta_backward<TPB, CPT>(x, [&](int c) { return qc[c]; }, sm, carry, &tot);
     carry = fma(tot.A, carry, tot.B);
 #pragma unroll
     for (int c = 0; c < CPT; ++c) {

@@ -114,10 +114,11 @@ int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, const double* 
 /* Largest J the fused on-chip variant accepts. */
 int64_t fvm_fused_max_cells(void);
 
-/* Variant 2: assembly + factorisation + `nsteps` theta steps in ONE launch, one warp per
- * system, state in registers and coefficients in shared memory; HBM is touched when the
- * state is loaded, at checkpoints, and when it is stored.  Replaces the whole of
- * fvm_classes.py:367-377,408-411 for a batch.  J <= fvm_fused_max_cells().
+/* Variant 2: assembly + factorisation + `nsteps` theta steps in ONE launch with the state in
+ * registers for the whole launch: one warp per system up to 1024 cells (coefficients in shared
+ * or tensor memory), one CTA per system up to 8192 cells (coefficients in shared memory); HBM is
+ * touched when the state is loaded, at checkpoints, and when it is stored.  Replaces the whole
+ * of fvm_classes.py:367-377,408-411 for a batch.  J <= fvm_fused_max_cells().
  * w: [P][J] problem-major, in/out.  dt: [P].
  * checkpoint_every > 0: after every that many steps the state is also written to
  * ckpt[(n-1)*P*J + p*J + j], n = 1..nsteps/checkpoint_every (ckpt may be NULL: none). */

@@ -71,8 +71,33 @@ def test_cfg3_subset_2000_steps(variant):
         assert err < TOL, (s, err)
 
 
-def test_cfg2_subset_thomas_2000_steps():
-    """cfg 2 (J=4096, Dirichlet flags) on the golden subset of the sweep, streaming variant."""
+@pytest.mark.parametrize("J", [1025, 2000, 2048, 2049, 3000, 4096, 5000, 8192])
+def test_cta_per_system_sizes(J):
+    """The CTA-per-system fused kernel (1024 < J <= 8192): every thread-count configuration,
+    ragged ends, all BC combinations with nonzero fluxes, three values of theta."""
+    rng = np.random.default_rng(J)
+    f = W.graded_faces(J, 50.0)
+    c = 0.5 * (f[1:] + f[:-1])
+    h = np.diff(f)
+    P = 2
+    a = rng.uniform(0.5, 2.0, P) * np.array([1.0, -1.0])
+    d = np.abs(a) * h.max() / rng.uniform(0.3, 1.5, P)
+    k = rng.uniform(2.0, 10.0, P) * h.min()
+    w0 = 0.2 + np.exp(-((c[None, :] - rng.uniform(0.3, 0.7, (P, 1))) / 0.1) ** 2)
+    bcs = [dict(left_flux=0.3, right_flux=-0.2), dict(left_value=1., right_value=0.),
+           dict(left_value=1., right_flux=0.1)]
+    for bc, theta, scheme in zip(bcs, (0.5, 1.0, 0.7), ("exponential", "upwind", "central")):
+        _, ck = run_gpu(f, a, d, k, scheme, bc, theta, w0, 20, 10, "fused")
+        for p in range(P):
+            asm = O.assemble(f, a[p], d[p], scheme, **bc)
+            want = O.theta_run_scipy(asm, k[p], theta, w0[p], 20, every=10)
+            assert step_error(ck[:, p], want, np.max(np.abs(w0[p]))) < TOL, (J, bc, theta, p)
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_cfg2_subset_2000_steps(variant):
+    """cfg 2 (J=4096, Dirichlet flags) on the golden subset of the sweep: the streaming variant
+    and the on-chip CTA-per-system variant."""
     g = load_golden("cfg2_subset")
     wl = W.peclet_sweep(4096)
     snaps = list(g["snaps"])
@@ -83,7 +108,7 @@ def test_cfg2_subset_thomas_2000_steps():
         w = torch.as_tensor(wl["w0"][pick], device="cuda")
         done = 0
         for s in snaps:
-            w, _ = m.run(w, 0.5, s - done, variant="thomas")
+            w, _ = m.run(w, 0.5, s - done, variant=variant)
             done = s
             got = w.cpu().numpy()
             for n, j in enumerate(pick):
@@ -196,14 +221,14 @@ def test_full_size_properties_cfg3():
 
 def test_rejects_bad_arguments():
     from fvm_b200._lib import FvmError
-    f = W.graded_faces(2048)
+    f = W.graded_faces(10000)
     m = BatchedAdvectionDiffusionModel(f, 1.0, 0.1, 1e-3, "central")
     m.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
     with pytest.raises(FvmError) as e:
-        m.run(np.ones((1, 2048)), 0.5, 1, variant="fused")        # J > fused maximum
+        m.run(np.ones((1, 10000)), 0.5, 1, variant="fused")       # J > fused maximum (8192)
     assert e.value.status == -2
     with pytest.raises(FvmError):
-        m.run(np.ones((1, 2048)), 0.0, 1, variant="thomas")       # theta must be in (0, 1]
+        m.run(np.ones((1, 10000)), 0.0, 1, variant="thomas")      # theta must be in (0, 1]
     with pytest.raises(UnboundLocalError):
         m2 = BatchedAdvectionDiffusionModel(f, 1.0, 0.1, 1e-3, "central")
         m2.set_boundary_conditions()
