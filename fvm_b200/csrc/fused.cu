@@ -77,17 +77,20 @@ __device__ __forceinline__ void setup_rows(const fvm_problem& pr, int64_t p, int
   R.rb_c = RB ? (int)((J - 1) % C) : -1;
   double q_prev = 0.0, gv_prev = 0.0;
   const int64_t j0 = (int64_t)lane * C;
-  double Dm = cell_D(pr, p, j0 - 1), D0 = cell_D(pr, p, j0);     // sliding window of modified D
+  // sliding window over faces: one expm1 and one face (5 divisions) per row
+  double D0 = cell_D(pr, p, j0);
+  Face FL = problem_face(pr, p, j0 - 1, cell_D(pr, p, j0 - 1), D0);
 #pragma unroll 1
   for (int c = 0; c < C; ++c) {
     const int64_t j = j0 + c;
     const double Dp = cell_D(pr, p, j + 1);
+    const Face FR = problem_face(pr, p, j, D0, Dp);
     Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;      // padding rows (j >= J) are identity
     if (j < J) {
-      Row m = assemble_row_D(pr, p, j, Dm, D0, Dp);
+      Row m = problem_row(pr, p, j, FL, FR);
       a = theta_lhs_row(m, dt_theta, alpha_of(j, J, pr.alpha_left, pr.alpha_right));
     }
-    Dm = D0; D0 = Dp;
+    D0 = Dp; FL = FR;
     if (c < N) {
       const double inv = 1.0 / (a.di - a.lo * q_prev);
       const double pc = a.lo * inv;
@@ -348,27 +351,36 @@ fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, i
         beta_r = dvd(-pr.right_flux[p], sub(pr.faces[J], pr.faces[J - 1]));
       R.bfirst = 0.0; R.bint = 0.0; R.bsep = 0.0; R.rb_c = -1;
       const int64_t j0 = (int64_t)lane * C;
-      auto row_of = [&](int c, double Dm, double D0, double Dp) {
+      Row asep;
+      auto row_of = [&](int c, const Face& FL, const Face& FR) {
         const int64_t j = j0 + c;
         Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;    // padding rows (j >= J) are identity
         if (j < J) {
-          Row m = assemble_row_D(pr, p, j, Dm, D0, Dp);
+          Row m = problem_row(pr, p, j, FL, FR);
           a = theta_lhs_row(m, dt_theta, alpha_of(j, J, pr.alpha_left, pr.alpha_right));
         }
         return a;
       };
-      // modified diffusivity in sliding windows: one expm1 per cell and sweep direction
-      double lDm = cell_D(pr, p, j0 - 1), lD0 = cell_D(pr, p, j0);
-      double rDp = cell_D(pr, p, j0 + C), rD0 = cell_D(pr, p, j0 + C - 1);
-      const Row asep = row_of(C - 1, cell_D(pr, p, j0 + C - 2), rD0, rDp);   // the separator's row
-      rDp = rD0; rD0 = cell_D(pr, p, j0 + C - 2);
+      // sliding windows over faces, one per sweep direction: one expm1 and one face (5 divisions)
+      // per row instead of three and two
+      double lD0 = cell_D(pr, p, j0);
+      Face lFL = problem_face(pr, p, j0 - 1, cell_D(pr, p, j0 - 1), lD0);
+      double rD0 = cell_D(pr, p, j0 + C - 1);                                 // the separator's cell
+      Face rFR = problem_face(pr, p, j0 + C - 1, rD0, cell_D(pr, p, j0 + C));
+      {
+        const double Dm = cell_D(pr, p, j0 + C - 2);
+        const Face F = problem_face(pr, p, j0 + C - 2, Dm, rD0);
+        asep = row_of(C - 1, F, rFR);                                         // the separator's row
+        rFR = F; rD0 = Dm;
+      }
       double sl_prev = 0.0, sr_prev = 0.0, gv_prev = 0.0, gu_prev = 0.0;
 #pragma unroll 1
       for (int i = 0; i < M; ++i) {
         {                                            // left cell i: top-down elimination
           const double lDp = cell_D(pr, p, j0 + i + 1);
-          const Row a = row_of(i, lDm, lD0, lDp);
-          lDm = lD0; lD0 = lDp;
+          const Face lFR = problem_face(pr, p, j0 + i, lD0, lDp);
+          const Row a = row_of(i, lFL, lFR);
+          lD0 = lDp; lFL = lFR;
           const double inv = 1.0 / (a.di - a.lo * sl_prev);
           const double e = a.lo * inv;
           sl_prev = a.up * inv;
@@ -380,8 +392,9 @@ fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, i
         if (i < N - M) {                             // right cell 30-i: bottom-up elimination
           const int c = N - 1 - i;
           const double rDm = cell_D(pr, p, j0 + c - 1);
-          const Row a = row_of(c, rDm, rD0, rDp);
-          rDp = rD0; rD0 = rDm;
+          const Face rFL = problem_face(pr, p, j0 + c - 1, rDm, rD0);
+          const Row a = row_of(c, rFL, rFR);
+          rD0 = rDm; rFR = rFL;
           const double inv = 1.0 / (a.di - a.up * sr_prev);
           const double e = a.up * inv;
           sr_prev = a.lo * inv;

@@ -36,17 +36,19 @@ fused_cta_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, in
     {
       const double dt_theta = mul(dt[p], theta);
       const int64_t j0 = (int64_t)tid * CPT;
-      double Dm = cell_D(pr, p, j0 - 1), D0 = cell_D(pr, p, j0);
+      double D0 = cell_D(pr, p, j0);
+      Face FL = problem_face(pr, p, j0 - 1, cell_D(pr, p, j0 - 1), D0);
 #pragma unroll 1
       for (int c = 0; c < CPT; ++c) {
         const int64_t j = j0 + c;
         const double Dp = cell_D(pr, p, j + 1);
+        const Face FR = problem_face(pr, p, j, D0, Dp);
         Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;          // padding rows (j >= J) are identity
         if (j < J) {
-          Row m = assemble_row_D(pr, p, j, Dm, D0, Dp);
+          Row m = problem_row(pr, p, j, FL, FR);
           a = theta_lhs_row(m, dt_theta, alpha_of(j, J, pr.alpha_left, pr.alpha_right));
         }
-        Dm = D0; D0 = Dp;
+        D0 = Dp; FL = FR;
         const int o = c * TPB + tid;
         sp[o] = a.lo; sb[o] = a.di; sq[o] = a.up;
       }

@@ -64,56 +64,85 @@ __device__ __forceinline__ void cell_kappa_D(int scheme, double a, double d, dou
 
 struct Row { double lo, di, up; };
 
-// Row j of M.  f[0..3] = faces[j-1], faces[j], faces[j+1], faces[j+2] (entries outside
-// the mesh are never used); am/a0/ap and Dm/D0/Dp are a and the MODIFIED diffusivity at
-// cells j-1, j, j+1.  kind = 0 interior, 1 first row, 2 last row.
-// Face interpolation is CellVariable.m/p [fvm_classes.py:83,87]; rows are :151-153
-// (interior), :158-159 / :169-170 (Robin) and :200-201 / :214-215 (Dirichlet).
-__device__ __forceinline__ Row matrix_row(const double f[4], double am, double a0, double ap,
-                                          double Dm, double D0, double Dp, bool first, bool last,
-                                          int left_kind, int right_kind) {
+// What the face between cells f and f+1 contributes to the two rows it touches
+// [fvm_classes.py:151-153 through CellVariable.m/p, :83,87]:
+//   A_hi = a_face*h(f+1)/(2 dx)   (lo of row f+1; enters di of row f with a minus sign)
+//   A_lo = a_face*h(f)  /(2 dx)   (di of row f+1; -A_lo is the advective part of up of row f)
+//   Dd   = D_face/dx
+// with dx = cells[f+1]-cells[f] (Mesh.hp(f) = Mesh.hm(f+1)) and the face values interpolated
+// as h(f+1)/(2dx)*v[f] + h(f)/(2dx)*v[f+1].  Every operation is rounded as numpy rounds it.
+struct Face { double A_hi, A_lo, Dd; };
+
+// ff[0..2] = faces[f], faces[f+1], faces[f+2]; (a0, D0) belong to cell f, (a1, D1) to cell f+1.
+__device__ __forceinline__ Face face_terms(const double ff[3], double a0, double a1, double D0, double D1) {
+  const double h0 = sub(ff[1], ff[0]), h1 = sub(ff[2], ff[1]);
+  const double c0 = mul(0.5, add(ff[0], ff[1])), c1 = mul(0.5, add(ff[1], ff[2]));
+  const double dx = sub(c1, c0);
+  const double two_dx = mul(2.0, dx);
+  const double wl = dvd(h1, two_dx), wr = dvd(h0, two_dx);
+  const double af = add(mul(wl, a0), mul(wr, a1));
+  const double Df = add(mul(wl, D0), mul(wr, D1));
+  Face F;
+  F.A_hi = dvd(mul(af, h1), two_dx);
+  F.A_lo = dvd(mul(af, h0), two_dx);
+  F.Dd = dvd(Df, dx);
+  return F;
+}
+
+// Row j of M from its two faces (L = face j-1, R = face j; the one outside the mesh is ignored).
+// rh = 1/h(j).  Interior rows :151-153, Robin :158-159 / :169-170, Dirichlet :200-201 / :214-215.
+__device__ __forceinline__ Row row_from_faces(double rh, const Face& L, const Face& R, bool first, bool last,
+                                              int left_kind, int right_kind) {
   Row r;
   if (first && left_kind == FVM_BC_DIRICHLET) { r.lo = 0.0; r.di = 0.0; r.up = 1.0; return r; }
   if (last && right_kind == FVM_BC_DIRICHLET) { r.lo = 0.0; r.di = 1.0; r.up = 0.0; return r; }
-  const double h0 = sub(f[2], f[1]);
-  const double c0 = mul(0.5, add(f[1], f[2]));
-  const double rh = dvd(1.0, h0);
-  double l_adv = 0.0, l_dif = 0.0, l_advd = 0.0;   // left-face terms
-  double r_adv = 0.0, r_dif = 0.0, r_advd = 0.0;   // right-face terms
-  if (!first) {
-    const double hm = sub(f[1], f[0]);
-    const double cm = mul(0.5, add(f[0], f[1]));
-    const double dx = sub(c0, cm);                                  // Mesh.hm(j), :51
-    const double two_dx = mul(2.0, dx);
-    const double af = add(mul(dvd(h0, two_dx), am), mul(dvd(hm, two_dx), a0));   // a.m(j), :83
-    const double Df = add(mul(dvd(h0, two_dx), Dm), mul(dvd(hm, two_dx), D0));   // d.m(j)
-    l_adv = dvd(mul(af, h0), two_dx);     // a.m(j)*h(j)/(2 hm(j))      -> lo
-    l_advd = dvd(mul(af, hm), two_dx);    // a.m(j)*h(j-1)/(2 hm(j))    -> di
-    l_dif = dvd(Df, dx);                  // d.m(j)/hm(j)
-  }
-  if (!last) {
-    const double hp = sub(f[3], f[2]);
-    const double cp = mul(0.5, add(f[2], f[3]));
-    const double dx = sub(cp, c0);                                  // Mesh.hp(j), :57
-    const double two_dx = mul(2.0, dx);
-    const double af = add(mul(dvd(hp, two_dx), a0), mul(dvd(h0, two_dx), ap));   // a.p(j), :87
-    const double Df = add(mul(dvd(hp, two_dx), D0), mul(dvd(h0, two_dx), Dp));   // d.p(j)
-    r_adv = dvd(mul(-af, h0), two_dx);    // -a.p(j)*h(j)/(2 hp(j))     -> up
-    r_advd = dvd(mul(af, hp), two_dx);    // a.p(j)*h(j+1)/(2 hp(j))    -> di
-    r_dif = dvd(Df, dx);                  // d.p(j)/hp(j)
-  }
-  if (first) {                             // Robin, :158-159
+  if (first) {
     r.lo = 0.0;
-    r.di = mul(rh, sub(-r_advd, r_dif));
-    r.up = mul(rh, add(r_adv, r_dif));
-  } else if (last) {                       // Robin, :169-170
-    r.lo = mul(rh, add(l_adv, l_dif));
-    r.di = mul(rh, sub(l_advd, l_dif));
+    r.di = mul(rh, sub(-R.A_hi, R.Dd));
+    r.up = mul(rh, add(-R.A_lo, R.Dd));
+  } else if (last) {
+    r.lo = mul(rh, add(L.A_hi, L.Dd));
+    r.di = mul(rh, sub(L.A_lo, L.Dd));
     r.up = 0.0;
-  } else {                                 // interior, :151-153
-    r.lo = mul(rh, add(l_adv, l_dif));
-    r.di = mul(rh, sub(sub(sub(l_advd, r_advd), l_dif), r_dif));
-    r.up = mul(rh, add(r_adv, r_dif));
+  } else {
+    r.lo = mul(rh, add(L.A_hi, L.Dd));
+    r.di = mul(rh, sub(sub(sub(L.A_lo, R.A_hi), L.Dd), R.Dd));
+    r.up = mul(rh, add(-R.A_lo, R.Dd));
+  }
+  return r;
+}
+
+// Row j of M.  f[0..3] = faces[j-1], faces[j], faces[j+1], faces[j+2] (entries outside
+// the mesh are never used); am/a0/ap and Dm/D0/Dp are a and the MODIFIED diffusivity at
+// cells j-1, j, j+1.
+__device__ __forceinline__ Row matrix_row(const double f[4], double am, double a0, double ap,
+                                          double Dm, double D0, double Dp, bool first, bool last,
+                                          int left_kind, int right_kind) {
+  Face L, R;
+  L.A_hi = L.A_lo = L.Dd = 0.0; R = L;
+  if (!first) L = face_terms(f, am, a0, Dm, D0);
+  if (!last) R = face_terms(f + 1, a0, ap, D0, Dp);
+  return row_from_faces(dvd(1.0, sub(f[2], f[1])), L, R, first, last, left_kind, right_kind);
+}
+
+// The face between cells f and f+1 of problem p (zeros outside the mesh), for sweeps that keep
+// faces in a sliding window: D0, D1 = modified diffusivities of cells f and f+1.
+__device__ __forceinline__ Face problem_face(const fvm_problem& pr, int64_t p, int64_t f, double D0, double D1) {
+  Face F; F.A_hi = F.A_lo = F.Dd = 0.0;
+  if (f < 0 || f + 1 >= pr.J) return F;
+  const double ff[3] = {pr.faces[f], pr.faces[f + 1], pr.faces[f + 2]};
+  const double* ap_ = pr.a + p * pr.a_ps;
+  return face_terms(ff, ap_[f * pr.a_cs], ap_[(f + 1) * pr.a_cs], D0, D1);
+}
+
+// Row j of problem p from its two faces, with the optional reaction term.
+__device__ __forceinline__ Row problem_row(const fvm_problem& pr, int64_t p, int64_t j, const Face& L, const Face& R) {
+  const bool first = (j == 0), last = (j == pr.J - 1);
+  Row r = row_from_faces(dvd(1.0, sub(pr.faces[j + 1], pr.faces[j])), L, R, first, last, pr.left_kind, pr.right_kind);
+  if (pr.reaction != nullptr) {
+    const bool dirichlet_row = (first && pr.left_kind == FVM_BC_DIRICHLET) ||
+                               (last && pr.right_kind == FVM_BC_DIRICHLET);
+    if (!dirichlet_row) r.di = sub(r.di, pr.reaction[p * pr.r_ps + j * pr.r_cs]);
   }
   return r;
 }
@@ -125,30 +154,6 @@ __device__ __forceinline__ double cell_D(const fvm_problem& pr, int64_t p, int64
   cell_kappa_D(pr.scheme, pr.a[p * pr.a_ps + j * pr.a_cs], pr.d[p * pr.d_ps + j * pr.d_cs],
                sub(pr.faces[j + 1], pr.faces[j]), kap, D);
   return D;
-}
-
-// Row j of M given the modified diffusivities of cells j-1, j, j+1 (a sweep over consecutive
-// cells keeps them in a sliding window instead of evaluating expm1 three times per row).
-__device__ __forceinline__ Row assemble_row_D(const fvm_problem& pr, int64_t p, int64_t j,
-                                              double Dm, double D0, double Dp) {
-  const int64_t J = pr.J;
-  const bool first = (j == 0), last = (j == J - 1);
-  double f[4];
-  f[0] = first ? 0.0 : pr.faces[j - 1];
-  f[1] = pr.faces[j];
-  f[2] = pr.faces[j + 1];
-  f[3] = last ? 0.0 : pr.faces[j + 2];
-  const double* ap_ = pr.a + p * pr.a_ps;
-  const double a0 = ap_[j * pr.a_cs];
-  const double am = first ? 0.0 : ap_[(j - 1) * pr.a_cs];
-  const double ap = last ? 0.0 : ap_[(j + 1) * pr.a_cs];
-  Row r = matrix_row(f, am, a0, ap, Dm, D0, Dp, first, last, pr.left_kind, pr.right_kind);
-  if (pr.reaction != nullptr) {
-    const bool dirichlet_row = (first && pr.left_kind == FVM_BC_DIRICHLET) ||
-                               (last && pr.right_kind == FVM_BC_DIRICHLET);
-    if (!dirichlet_row) r.di = sub(r.di, pr.reaction[p * pr.r_ps + j * pr.r_cs]);
-  }
-  return r;
 }
 
 // Loads what row j of problem p needs and returns the row of M (with the optional
