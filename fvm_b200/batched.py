@@ -262,33 +262,71 @@ class BatchedAdvectionDiffusionModel(object):
             raise ValueError("variant must be 'auto', 'fused' or 'thomas'")
         return w, ckpt
 
-    def run_host(self, w_host, theta, nsteps, out=None, variant="auto"):
+    def run_host(self, w_host, theta, nsteps, out=None, variant="auto", chunks=8):
         """Host-buffer form of :meth:`run`: ``w_host`` (P, J) lives in host memory (numpy array
         or CPU tensor; pinned memory makes the copies asynchronous and fast).  Copies it to the
         device, advances it ``nsteps`` theta steps, copies the result into ``out`` (allocated
         pinned if None) and waits for it.  This is what a caller that keeps its state on the
-        host -- like every script written against the reference -- pays per call."""
+        host -- like every script written against the reference -- pays per call.
+
+        The batch is cut into ``chunks`` groups of problems that travel on three streams, so
+        that the upload of one group, the kernel of another and the download of a third overlap
+        (problems are independent: no group waits for another)."""
         torch = _lib.require_cuda()
         if isinstance(w_host, np.ndarray):
             w_host = torch.from_numpy(np.ascontiguousarray(w_host, dtype=np.float64))
         w_host = w_host.reshape(self.P, self.J)
         if getattr(self, "_stage", None) is None:
             self._stage = torch.empty((self.P, self.J), dtype=torch.float64, device=self.device)
+            self._streams = [torch.cuda.Stream(device=self.device) for _ in range(3)]
         if out is None:
             out = torch.empty((self.P, self.J), dtype=torch.float64).pin_memory()
         elif isinstance(out, np.ndarray):
             out = torch.from_numpy(out)
+        if variant == "auto":
+            variant = "fused" if self.J <= int(_lib.lib().fvm_fused_max_cells()) else "thomas"
         with torch.cuda.device(self.device):
-            self._stage.copy_(w_host, non_blocking=True)
-            if variant == "auto":
-                variant = "fused" if self.J <= int(_lib.lib().fvm_fused_max_cells()) else "thomas"
-            if variant == "fused":
-                self.run_fused_(self._stage, theta, nsteps)
-                res = self._stage
-            else:
+            if variant != "fused":
+                self._stage.copy_(w_host, non_blocking=True)
                 w_t = self._stage.t().contiguous()
                 self.step_thomas_(w_t, theta, nsteps)
-                res = w_t.t()
-            out.copy_(res, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+                out.copy_(w_t.t(), non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                return out
+            pr = self._problem()
+            n_chunks = max(1, min(int(chunks), self.P // 2048 if self.P >= 4096 else 1))
+            bounds = [self.P * i // n_chunks for i in range(n_chunks + 1)]
+            main = torch.cuda.current_stream()
+            for s in self._streams:
+                s.wait_stream(main)
+            for i in range(n_chunks):
+                lo, hi = bounds[i], bounds[i + 1]
+                st = self._streams[i % len(self._streams)]
+                with torch.cuda.stream(st):
+                    dst = self._stage[lo:hi]
+                    dst.copy_(w_host[lo:hi], non_blocking=True)
+                    sub = self._chunk_problem(pr, lo, hi)
+                    rc = _lib.lib().fvm_theta_run_fused(ctypes.byref(sub), ctypes.c_void_p(self.k.data_ptr() + 8 * lo),
+                                                        float(theta), int(nsteps), 0, _lib.ptr(dst), None,
+                                                        _lib.stream_ptr())
+                    _lib.check(rc, "fvm_theta_run_fused")
+                    out[lo:hi].copy_(dst, non_blocking=True)
+            for s in self._streams:
+                main.wait_stream(s)
+            main.synchronize()
         return out
+
+    def _chunk_problem(self, pr, lo, hi):
+        """struct fvm_problem of the problems [lo, hi) of this batch (same mesh, shifted pointers)."""
+        sub = _lib.FvmProblem()
+        ctypes.memmove(ctypes.byref(sub), ctypes.byref(pr), ctypes.sizeof(sub))
+        sub.P = hi - lo
+        sub.a = pr.a + 8 * lo * pr.a_ps
+        sub.d = pr.d + 8 * lo * pr.d_ps
+        if pr.reaction:
+            sub.reaction = pr.reaction + 8 * lo * pr.r_ps
+        if pr.left_flux:
+            sub.left_flux = pr.left_flux + 8 * lo
+        if pr.right_flux:
+            sub.right_flux = pr.right_flux + 8 * lo
+        return sub
