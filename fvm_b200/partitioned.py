@@ -89,7 +89,7 @@ class PartitionedAdvectionDiffusionModel(object):
     """
 
     def __init__(self, faces, a, d, k, discretisation="central", P=1, reaction=None, strict_bc=False,
-                 J=None, group=None, config=0, spike_tol=1e-30, device=None):
+                 J=None, group=None, config=0, spike_tol=1e-30, device=None, hierarchical=True):
         torch = _lib.require_cuda()
         lib = _lib.lib()
         if discretisation not in _lib.SCHEMES:
@@ -108,6 +108,7 @@ class PartitionedAdvectionDiffusionModel(object):
             raise IndexError("at least 3 cells are needed (the reference fails at fvm_classes.py:292)")
         self.P = int(P)
         self.discretisation, self.strict_bc, self.spike_tol = discretisation, strict_bc, float(spike_tol)
+        self.hierarchical = bool(hierarchical)
         plan = plan_partition(self.J, self.T, self.comm.world)
         self.nt = plan["tiles_per_rank"]
         self.nt_global = plan["tiles_global"]
@@ -225,12 +226,17 @@ class PartitionedAdvectionDiffusionModel(object):
         RL = sep_all[..., SEP_RL].contiguous()
         RD = (sep_all[..., SEP_RDA] - self.sup_all * nxt(self.V0_all)).contiguous()
         RU = (-self.sup_all * nxt(self.W0_all)).contiguous()
-        self.rp, self.rq, self.rinv = new(P, self.nt_global), new(P, self.nt_global), new(P, self.nt_global)
-        with torch.cuda.device(dev):
-            st = lib.fvm_spike_reduced_factor(self.nt_global, P, _lib.ptr(RL), _lib.ptr(RD), _lib.ptr(RU),
-                                              _lib.ptr(self.rp), _lib.ptr(self.rq), _lib.ptr(self.rinv),
-                                              _lib.stream_ptr())
-        _lib.check(st, "fvm_spike_reduced_factor")
+        self.hier = self.comm.world > 1 and nt >= 2 and self.hierarchical
+        if not self.hier:
+            # every rank factors (and later solves) the whole separator system
+            self.rp, self.rq, self.rinv = new(P, self.nt_global), new(P, self.nt_global), new(P, self.nt_global)
+            with torch.cuda.device(dev):
+                st = lib.fvm_spike_reduced_factor(self.nt_global, P, _lib.ptr(RL), _lib.ptr(RD), _lib.ptr(RU),
+                                                  _lib.ptr(self.rp), _lib.ptr(self.rq), _lib.ptr(self.rinv),
+                                                  _lib.stream_ptr())
+            _lib.check(st, "fvm_spike_reduced_factor")
+        else:
+            self._prepare_rank_level(RL, RD, RU)
         e = self.comm.all_reduce_max_int(ext.cpu().tolist())
         self.extents = (ctypes.c_int32 * 2)(min(e[0], T - 1), min(e[1], T - 1))
         # work arrays of a step
@@ -242,6 +248,63 @@ class PartitionedAdvectionDiffusionModel(object):
         self._last_local = jl if (self._has_rf and 0 <= jl < self.n_local and jl % T != T - 1) else -1
         self._theta = theta
         self._ready = theta
+
+    def _reduced_local_solve(self, rhs):
+        """Solve this rank's block of the separator system (its own nt unknowns, couplings to the
+        neighbouring ranks cut, last unknown = the rank's separator, decoupled): rhs (P, nt) -> (P, nt)."""
+        torch = _lib.require_cuda()
+        out = torch.empty_like(rhs)
+        with torch.cuda.device(self.device):
+            st = _lib.lib().fvm_spike_reduce_solve(self.nt, self.P, _lib.ptr(self.rp), _lib.ptr(self.rq),
+                                                   _lib.ptr(self.rinv), _lib.ptr(rhs), _lib.ptr(out),
+                                                   _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_reduce_solve")
+        return out
+
+    def _prepare_rank_level(self, RL, RD, RU):
+        """SPIKE once more, one level up.  The separator system (one unknown per tile, all ranks) is
+        itself partitioned: every rank keeps the rows of its own tiles, its LAST tile separator is the
+        rank's separator, the nt-1 others form a block that is solved locally; the rank separators
+        satisfy a `world`-unknown tridiagonal whose (dense, tiny) inverse every rank holds.  A step
+        then all-gathers 4 numbers per problem and rank instead of the rank's whole right-hand side,
+        and solves nt unknowns instead of world*nt."""
+        torch = _lib.require_cuda()
+        lib, dev, P, nt, r, W = _lib.lib(), self.device, self.P, self.nt, self.comm.rank, self.comm.world
+        sl = slice(r * nt, (r + 1) * nt)
+        rl, rd, ru = RL[:, sl].clone(), RD[:, sl].clone(), RU[:, sl].clone()
+        cut_lo, cut_up = rl[:, 0].clone(), ru[:, nt - 2].clone()       # couplings leaving the block
+        sep_l, sep_d, sep_u = rl[:, nt - 1].clone(), rd[:, nt - 1].clone(), ru[:, nt - 1].clone()
+        rl[:, 0] = 0.0
+        ru[:, nt - 2] = 0.0
+        rl[:, nt - 1], rd[:, nt - 1], ru[:, nt - 1] = 0.0, 1.0, 0.0     # the separator row: decoupled
+        new = lambda *shape: torch.empty(shape, dtype=torch.float64, device=dev)
+        self.rp, self.rq, self.rinv = new(P, nt), new(P, nt), new(P, nt)
+        with torch.cuda.device(dev):
+            st = lib.fvm_spike_reduced_factor(nt, P, _lib.ptr(rl.contiguous()), _lib.ptr(rd.contiguous()),
+                                              _lib.ptr(ru.contiguous()), _lib.ptr(self.rp), _lib.ptr(self.rq),
+                                              _lib.ptr(self.rinv), _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_reduced_factor")
+        e = torch.zeros((P, nt), dtype=torch.float64, device=dev)
+        e[:, 0] = cut_lo
+        self.Vr = self._reduced_local_solve(e)                           # response to the previous rank's separator
+        e.zero_()
+        e[:, nt - 2] = cut_up
+        self.Wr = self._reduced_local_solve(e)                           # response to this rank's own separator
+        self.Vr[:, nt - 1] = 0.0
+        self.Wr[:, nt - 1] = 0.0
+        info = torch.stack([sep_l, sep_d, sep_u, self.Vr[:, 0], self.Wr[:, 0], self.Vr[:, nt - 2],
+                            self.Wr[:, nt - 2]], dim=1)                   # (P, 7)
+        allv = self.comm.all_gather(info)                                # (W, P, 7)
+        sl_, sd_, su_, vf, wf, vl, wlast = [allv[:, :, i].t().contiguous() for i in range(7)]   # (P, W)
+        nxt = lambda x: torch.cat([x[:, 1:], torch.zeros_like(x[:, :1])], dim=1)
+        TL = -sl_ * vl
+        TD = sd_ - sl_ * wlast - su_ * nxt(vf)
+        TU = -su_ * nxt(wf)
+        top = torch.diag_embed(TD) + torch.diag_embed(TL[:, 1:], offset=-1) + torch.diag_embed(TU[:, :-1], offset=1)
+        self.top_inv = torch.linalg.inv(top)                             # (P, W, W)
+        self.top_sl, self.top_su = sl_, su_                              # separator rows' couplings, all ranks
+        self.top_vf, self.top_wf = vf, wf                                # rank spikes at every rank's first tile
+        self.xs_ext = torch.zeros((P, nt + 1), dtype=torch.float64, device=dev)
 
     # ------------------------------------------------------------------ state
     def set_state(self, w):
@@ -290,6 +353,10 @@ class PartitionedAdvectionDiffusionModel(object):
                                          _lib.stream_ptr())
                 _lib.check(st, "fvm_spike_local")
                 next_first = None
+                if self.hier:
+                    self._step_rank_level(w_out, wptr)
+                    self._cur = 1 - self._cur
+                    continue
                 if comm.world == 1:
                     rr_all = self.rr
                 else:
@@ -312,6 +379,36 @@ class PartitionedAdvectionDiffusionModel(object):
                                             self.w_stride, _lib.ptr(next_first), _lib.stream_ptr())
                 _lib.check(st, "fvm_spike_finalize")
                 self._cur = 1 - self._cur
+
+    def _step_rank_level(self, w_out, wptr):
+        """Second half of a step with the rank-level hierarchy (see _prepare_rank_level)."""
+        torch = _lib.require_cuda()
+        lib, P, nt, comm, r, W = _lib.lib(), self.P, self.nt, self.comm, self.comm.rank, self.comm.world
+        rr_sep = self.rr[:, nt - 1].clone()                              # lacks -up*g_first(next rank)
+        self.rr[:, nt - 1] = 0.0
+        gr = self._reduced_local_solve(self.rr)                          # block solution, couplings cut
+        packet = torch.stack([gr[:, 0], gr[:, nt - 2], rr_sep, self.g_first], dim=1)     # (P, 4)
+        allp = comm.all_gather(packet)                                   # (W, P, 4)
+        gfirst, glast, rsep, cell_first = [allp[:, :, i].t() for i in range(4)]          # (P, W)
+        nxt = lambda x: torch.cat([x[:, 1:], torch.zeros_like(x[:, :1])], dim=1)
+        last = torch.arange(1, W + 1, device=self.device) * nt - 1                        # separator tiles
+        rhs = rsep - self.sup_all[:, last] * nxt(cell_first) - self.top_sl * glast - self.top_su * nxt(gfirst)
+        X = torch.einsum("pij,pj->pi", self.top_inv, rhs)                # rank separators, all ranks (P, W)
+        Xl = X[:, r - 1] if r > 0 else torch.zeros_like(X[:, 0])
+        xs = gr - self.Vr * Xl[:, None] - self.Wr * X[:, r][:, None]
+        xs[:, nt - 1] = X[:, r]
+        self.xs_ext[:, 0] = Xl
+        self.xs_ext[:, 1:] = xs
+        next_first = None
+        if r < W - 1:
+            # the next rank's first separator, then its (corrected) first cell = my right ghost
+            xs_n0 = gfirst[:, r + 1] - self.top_vf[:, r + 1] * X[:, r] - self.top_wf[:, r + 1] * X[:, r + 1]
+            k1 = (r + 1) * nt
+            next_first = (cell_first[:, r + 1] - self.V0_all[:, k1] * X[:, r] - self.W0_all[:, k1] * xs_n0).contiguous()
+        st = lib.fvm_spike_finalize(nt, P, self.config, self.extents, 1, nt + 1, _lib.ptr(self.Vt),
+                                    _lib.ptr(self.Wt), _lib.ptr(self.xs_ext), wptr(w_out), self.w_stride,
+                                    _lib.ptr(next_first), _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_finalize")
 
     def run(self, w, theta, nsteps):
         """set_state + prepare + step; returns this rank's cells of the final state."""
