@@ -172,6 +172,22 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def ncu_traffic(summary_name):
+    """dram__bytes_read.sum + dram__bytes_write.sum (bytes per launch) of a committed `ncu --set full`
+    capture, parsed from profiles/<summary_name> (written by profiles/ncu_summary.py); None if absent."""
+    path = os.path.join(ROOT, "profiles", summary_name)
+    if not os.path.exists(path):
+        return None
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    total, seen = 0.0, 0
+    for ln in open(path):
+        f = ln.split()
+        if len(f) >= 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and f[1] in scale:
+            total += float(f[2]) * scale[f[1]]
+            seen += 1
+    return total if seen == 2 else None
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -201,7 +217,9 @@ def partitioned_leg(dev, peaks, peak_src, log2_cells=26, nsteps=10):
             "bound": "hbm", "cell_updates_per_s": J / (ms * 1e-3), "ms_per_theta_step": ms, "achieved": gbs,
             "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "peak_source": peak_src,
             "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_SPIKE,
-            "spike_extents_cells": [int(m.extents[0]), int(m.extents[1])], "tile_cells": m.T, "traffic": None}
+            "spike_extents_cells": [int(m.extents[0]), int(m.extents[1])], "tile_cells": m.T,
+            "traffic": ncu_traffic("r01_spike_tile_solve.summary.txt"),
+            "traffic_note": "tile_solve_kernel only, one launch at 2^26 cells (algorithmic 40 B x 2^26 = 2.68e9)"}
 
 
 def run_partitioned(args):
@@ -415,7 +433,8 @@ def run_b200(args):
             hbm = {"kernel": "thomas_steps_kernel (variant 1, one theta step per launch)", "bound": "hbm",
                    "cell_updates_per_s": P * J / (ms * 1e-3), "achieved": gbs, "peak": peaks["hbm_gbs"],
                    "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "peak_source": peak_src,
-                   "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_THOMAS, "traffic": None}
+                   "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_THOMAS,
+                   "traffic": ncu_traffic("r01_thomas_v1.summary.txt")}
             del w_t
         except Exception as exc:  # noqa: BLE001
             hbm = {"error": repr(exc)}
@@ -447,7 +466,9 @@ def run_b200(args):
     onchip = ONCHIP_B_PER_CELL_UPDATE * cu_s_kernel / 1e9
     roofline = {"kernel": "fused_tmem_kernel<CN> (variant 2: state in registers, coefficients in TMEM)",
                 "bound": "fp64", "achieved": fp64_ach, "peak": fp64_peak, "unit": "TFLOP/s",
-                "frac": fp64_ach / fp64_peak, "traffic": None,
+                "frac": fp64_ach / fp64_peak, "traffic": ncu_traffic("r01_fused_final.summary.txt"),
+                "traffic_note": "DRAM bytes per launch from profiles/r01_fused_final.summary.txt (ncu --set full, same "
+                                "command); algorithmic HBM bytes per launch = 16 B x %d x %d = %.3e" % (P, J, 16.0 * P * J),
                 "peak_source": "%d SMs x 64 DFMA/clk x 2 flop x %.0f MHz (max SM clock, %s); the 64 DFMA/clk/SM rate is "
                                "measured (profiles/microbench/r01_fp64_peak_b200.txt)" % (sms, f_max / 1e6, peak_src),
                 "flop_per_cell_update": FLOP_PER_CELL_UPDATE,
