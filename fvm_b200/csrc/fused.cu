@@ -27,6 +27,7 @@
 #include "fvm_device.cuh"
 #include "tmem.cuh"
 #include <cstdlib>
+#include <type_traits>
 
 namespace fvm {
 
@@ -279,71 +280,19 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
   }
 }
 
-// ------------------------------------------------------------------------------------------
-// Tensor-memory variant, C = 32 (512 < J <= 1024), 8 warps per CTA, one CTA per SM.
-//
-// A step of the shared-memory kernel is bound by the latency of its dependent-FMA chains
-// (31 links forward, 30 backward, ~9 cycles each; profiles/r01_fused_v3_tmem.summary.txt), not
-// by the fp64 pipe.  This kernel therefore factors each lane's interior block T with a TWISTED
-// factorisation: cells 0..15 are eliminated top-down, cells 30..16 bottom-up, the two sweeps
-// meet between cells 15 and 16, and substitution runs outwards from there.  Same flops, same
-// five coefficients per cell, but two independent chains of half the length: 16 + 1 + 16
-// dependent links per step instead of 61.  Per cell:  e = elimination coefficient (times the
-// neighbour the sweep comes from), s = substitution coefficient (times the neighbour the
-// sweep moves towards), b = diagonal of inv*B; inv*B's off-diagonals are -c*e and -c*s.
-//
-// TMEM layout per warp (256 columns of its lane quadrant), in the order the loop consumes it:
-//   columns [0,128)  : slot i = (e, b) of left cell i, then (e, b) of right cell 30-i   (8 columns)
-//   columns [128,256): slot i = (v, u) of left cell i, then (v, u) of right cell 30-i
-// s lives in registers (it is read twice per step).  IT = slots per tcgen05.ld (2 -> .x16,
-// 4 -> .x32); loads are double-buffered so the next chunk is in flight while one is consumed.
-template <int IT> struct TmemChunk;
-template <> struct TmemChunk<4> {
-  static constexpr int REGS = 32;
-  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[32]) { tmem_ld_x32(t, r); }
-  static __device__ __forceinline__ void wait(uint32_t (&r)[32]) { tmem_wait_ld_x32(r); }
-};
-template <> struct TmemChunk<2> {
-  static constexpr int REGS = 16;
-  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[16]) { tmem_ld_x16(t, r); }
-  static __device__ __forceinline__ void wait(uint32_t (&r)[16]) { tmem_wait_ld_x16(r); }
-};
-
-// k-th double of a chunk (two 32-bit columns each)
-__device__ __forceinline__ double chunk_dbl(const uint32_t* r, int k) { return __hiloint2double((int)r[2 * k + 1], (int)r[2 * k]); }
-
-template <int MODE, int IT>
-__global__ void __launch_bounds__(kFusedThreads, 1)
-fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
-                  int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
-  constexpr int C = 32, N = 31, M = 16;              // left cells 0..M-1, right cells N-1..M
-  constexpr int NCH = M / IT;                        // chunks per region
-  using TC = TmemChunk<IT>;
-  extern __shared__ double smem[];
-  __shared__ uint32_t tmem_base_slot;
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int warps = blockDim.x >> 5;
-  double* sS = smem + (size_t)warp * (3 * N * 32) + lane;        // set-up staging: s, v, u
-  double* sv = sS + N * 32;
-  double* su = sv + N * 32;
+// Set-up shared by the tensor-memory kernels (C = 32, N = 31 interior cells per lane, twisted at
+// M = 16): assembles this lane's rows of A, factors the interior block from both ends (e, b ->
+// tensor memory at t_eb; s -> sS and the registers sr), computes both spikes (sv = V, su = U in
+// shared memory, natural cell order), the separator system and its PCR factors.
+__device__ __forceinline__ void tmem_setup_common(const fvm_problem& pr, int64_t p, int lane, double dt_p, double theta,
+                                                  uint32_t t_eb, double* sS, double* sv, double* su, Reduced& R,
+                                                  double (&sr)[31], double& delta) {
+  constexpr int C = 32, N = 31, M = 16;
   const int64_t J = pr.J;
   const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
-
-  if (warp == 0) tmem_alloc_512(&tmem_base_slot);
-  tmem_fence_before_sync();
-  __syncthreads();
-  tmem_fence_after_sync();
-  const uint32_t tmem_base = tmem_base_slot;
-  const uint32_t t_eb = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
-  const uint32_t t_vu = t_eb + 128;
-
-  for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
-    // ------------------------------------------------------------------ set-up (once)
-    Reduced R;
-    double sdi = 1.0, delta;
+    double sdi = 1.0;
     {
-      const double dt_theta = mul(dt[p], theta);
+      const double dt_theta = mul(dt_p, theta);
       double beta_l = 0.0, beta_r = 0.0;
       if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
         beta_l = dvd(pr.left_flux[p], sub(pr.faces[1], pr.faces[0]));
@@ -408,7 +357,6 @@ fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, i
       if (js == J - 1) R.bsep += beta_r;
       R.sblo = -cth * R.slo; R.sbdi = rth - cth * sdi; R.sbup = -cth * R.sup;
     }
-    double sr[N];                                    // s for the whole launch
 #pragma unroll
     for (int c = 0; c < N; ++c) sr[c] = sS[c * 32];
     delta = 1.0 / (1.0 - sr[M] * sr[M - 1]);
@@ -437,6 +385,75 @@ fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, i
       const double RD = sdi - R.slo * ru - R.sup * v0n;          // sup == 0 on lane 31
       const double RU = -R.sup * u0n;
       pcr_factor(lane, RL, RD, RU, R);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Tensor-memory variant, C = 32 (512 < J <= 1024), 8 warps per CTA, one CTA per SM.
+//
+// A step of the shared-memory kernel is bound by the latency of its dependent-FMA chains
+// (31 links forward, 30 backward, ~9 cycles each; profiles/r01_fused_v3_tmem.summary.txt), not
+// by the fp64 pipe.  This kernel therefore factors each lane's interior block T with a TWISTED
+// factorisation: cells 0..15 are eliminated top-down, cells 30..16 bottom-up, the two sweeps
+// meet between cells 15 and 16, and substitution runs outwards from there.  Same flops, same
+// five coefficients per cell, but two independent chains of half the length: 16 + 1 + 16
+// dependent links per step instead of 61.  Per cell:  e = elimination coefficient (times the
+// neighbour the sweep comes from), s = substitution coefficient (times the neighbour the
+// sweep moves towards), b = diagonal of inv*B; inv*B's off-diagonals are -c*e and -c*s.
+//
+// TMEM layout per warp (256 columns of its lane quadrant), in the order the loop consumes it:
+//   columns [0,128)  : slot i = (e, b) of left cell i, then (e, b) of right cell 30-i   (8 columns)
+//   columns [128,256): slot i = (v, u) of left cell i, then (v, u) of right cell 30-i
+// s lives in registers (it is read twice per step).  IT = slots per tcgen05.ld (2 -> .x16,
+// 4 -> .x32); loads are double-buffered so the next chunk is in flight while one is consumed.
+template <int IT> struct TmemChunk;
+template <> struct TmemChunk<4> {
+  static constexpr int REGS = 32;
+  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[32]) { tmem_ld_x32(t, r); }
+  static __device__ __forceinline__ void wait(uint32_t (&r)[32]) { tmem_wait_ld_x32(r); }
+};
+template <> struct TmemChunk<2> {
+  static constexpr int REGS = 16;
+  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[16]) { tmem_ld_x16(t, r); }
+  static __device__ __forceinline__ void wait(uint32_t (&r)[16]) { tmem_wait_ld_x16(r); }
+};
+
+// k-th double of a chunk (two 32-bit columns each)
+__device__ __forceinline__ double chunk_dbl(const uint32_t* r, int k) { return __hiloint2double((int)r[2 * k + 1], (int)r[2 * k]); }
+
+template <int MODE, int IT>
+__global__ void __launch_bounds__(kFusedThreads, 1)
+fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
+                  int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
+  constexpr int C = 32, N = 31, M = 16;              // left cells 0..M-1, right cells N-1..M
+  constexpr int NCH = M / IT;                        // chunks per region
+  using TC = TmemChunk<IT>;
+  extern __shared__ double smem[];
+  __shared__ uint32_t tmem_base_slot;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int warps = blockDim.x >> 5;
+  double* sS = smem + (size_t)warp * (3 * N * 32) + lane;        // set-up staging: s, v, u
+  double* sv = sS + N * 32;
+  double* su = sv + N * 32;
+  const int64_t J = pr.J;
+  const double cth = (1.0 - theta) / theta;
+
+  if (warp == 0) tmem_alloc_512(&tmem_base_slot);
+  tmem_fence_before_sync();
+  __syncthreads();
+  tmem_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t t_eb = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
+  const uint32_t t_vu = t_eb + 128;
+
+  for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
+    // ------------------------------------------------------------------ set-up (once)
+    Reduced R;
+    double delta;
+    double sr[N];                                    // s for the whole launch
+    tmem_setup_common(pr, p, lane, dt[p], theta, t_eb, sS, sv, su, R, sr, delta);
+    {
 #pragma unroll 1
       for (int i = 0; i < M; ++i) {
         tmem_st_2d(t_vu + 8 * i, sv[i * 32], su[i * 32]);
@@ -541,6 +558,258 @@ fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, i
 }
 
 // ------------------------------------------------------------------------------------------
+// Tensor-memory variant with a DELAYED CORRECTION, the default for 512 < J <= 1024.
+//
+// In fused_tmem_kernel a step is  sweeps -> separator PCR -> correction, and the PCR (five
+// levels of shuffle + FMA, ~25 % of the step, a pure latency chain that leaves the fp64 pipe
+// idle) cannot overlap anything, because the next sweeps need the corrected state.  But the whole
+// step is linear with constant coefficients.  Keep, between steps, the UNCORRECTED block
+// solutions g and the reduced right-hand side rr; the true state is x = g - V xsl - U xs with the
+// separator values xs = R^-1 rr still to come.  Then
+//     g' = T^-1 (B~ x)_interior = T^-1 B~_ii g  +  P1 xsl  +  P2 xs ,
+//     P1 = T^-1 (b_left  - B~_ii V) ,  P2 = T^-1 (b_right - B~_ii U)      (computed once, in TMEM),
+// where b_left / b_right carry the coupling of the block's end cells to the two separators.  The
+// sweeps T^-1 B~_ii g do not need xs, so they run while the PCR of the PREVIOUS step is in
+// flight: its levels are interleaved with the elimination chunks.  P1, P2 take the place of V, U
+// in tensor memory (same traffic, same flops); V and U stay in shared memory for the points where
+// the true state is needed (checkpoints, the end of the launch), which cut the run into
+// pipelined segments.  Algebraically identical to the plain scheme (scratch/proto_pipe.py).
+template <int MODE, int IT>
+__global__ void __launch_bounds__(kFusedThreads, 1)
+fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
+                       int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
+  constexpr int C = 32, N = 31, M = 16;
+  constexpr int NCH = M / IT;
+  using TC = TmemChunk<IT>;
+  extern __shared__ double smem[];
+  __shared__ uint32_t tmem_base_slot;
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int warps = blockDim.x >> 5;
+  double* sS = smem + (size_t)warp * (3 * N * 32) + lane;        // s (set-up only), V, U
+  double* sv = sS + N * 32;
+  double* su = sv + N * 32;
+  const int64_t J = pr.J;
+  const double cth = (1.0 - theta) / theta;
+
+  if (warp == 0) tmem_alloc_512(&tmem_base_slot);
+  tmem_fence_before_sync();
+  __syncthreads();
+  tmem_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_slot;
+  const uint32_t t_eb = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
+  const uint32_t t_pp = t_eb + 128;                  // (P1, P2) pairs, same slot order as (e, b)
+
+  for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
+    // ------------------------------------------------------------------ set-up (once)
+    Reduced R;
+    double delta;
+    double sr[N];
+    tmem_setup_common(pr, p, lane, dt[p], theta, t_eb, sS, sv, su, R, sr, delta);
+    const double V0 = sv[0], U0 = su[0], VL = sv[(N - 1) * 32], UL = su[(N - 1) * 32];
+    {
+      auto tcol = [&](int c) { return (uint32_t)(c < M ? 8 * c : 8 * (N - 1 - c) + 4); };
+      tmem_wait_st();
+      // right-hand sides of P1, P2: b_left - B~_ii V and b_right - B~_ii U, into tensor memory
+#pragma unroll 1
+      for (int c = 0; c < N; ++c) {
+        double e, b;
+        tmem_ld_2d(t_eb + tcol(c), e, b);
+        const bool left = c < M;
+        const int cn_e = left ? c - 1 : c + 1, cn_s = left ? c + 1 : c - 1;
+        const bool has_e = left ? (c > 0) : (c < N - 1);
+        const double Ve = has_e ? sv[cn_e * 32] : 0.0, Ue = has_e ? su[cn_e * 32] : 0.0;
+        const double Vs = sv[cn_s * 32], Us = su[cn_s * 32];
+        const double sc = sS[c * 32];
+        double tv = b * sv[c * 32], tu = b * su[c * 32];
+        if (MODE != 2) {
+          tv = fma(-cth, fma(sc, Vs, e * Ve), tv);
+          tu = fma(-cth, fma(sc, Us, e * Ue), tu);
+        }
+        const double r1 = ((c == 0 && MODE != 2) ? -cth * e : 0.0) - tv;
+        const double r2 = ((c == N - 1 && MODE != 2) ? -cth * e : 0.0) - tu;
+        tmem_st_2d(t_pp + tcol(c), r1, r2);
+      }
+      tmem_wait_st();
+      // twisted solve of both right-hand sides, in place in tensor memory
+      double x1, x2, p1, p2, e, b;
+      tmem_ld_2d(t_pp + tcol(0), p1, p2);
+#pragma unroll 1
+      for (int c = 1; c < M; ++c) {                  // eliminate downwards
+        tmem_ld_2d(t_eb + tcol(c), e, b);
+        tmem_ld_2d(t_pp + tcol(c), x1, x2);
+        p1 = fma(-e, p1, x1); p2 = fma(-e, p2, x2);
+        tmem_st_2d(t_pp + tcol(c), p1, p2);
+      }
+      double l1 = p1, l2 = p2;                        // eliminated values at cell M-1
+      tmem_ld_2d(t_pp + tcol(N - 1), p1, p2);
+#pragma unroll 1
+      for (int c = N - 2; c >= M; --c) {             // eliminate upwards
+        tmem_ld_2d(t_eb + tcol(c), e, b);
+        tmem_ld_2d(t_pp + tcol(c), x1, x2);
+        p1 = fma(-e, p1, x1); p2 = fma(-e, p2, x2);
+        tmem_st_2d(t_pp + tcol(c), p1, p2);
+      }
+      // meet between cells M-1 and M, then substitute outwards
+      const double m1 = fma(-sS[M * 32], l1, p1) * delta, m2 = fma(-sS[M * 32], l2, p2) * delta;
+      tmem_st_2d(t_pp + tcol(M), m1, m2);
+      tmem_wait_st();
+      p1 = m1; p2 = m2;
+#pragma unroll 1
+      for (int c = M - 1; c >= 0; --c) {
+        tmem_ld_2d(t_pp + tcol(c), x1, x2);
+        const double sc = sS[c * 32];
+        p1 = fma(-sc, p1, x1); p2 = fma(-sc, p2, x2);
+        tmem_st_2d(t_pp + tcol(c), p1, p2);
+      }
+      p1 = m1; p2 = m2;
+#pragma unroll 1
+      for (int c = M + 1; c < N; ++c) {
+        tmem_ld_2d(t_pp + tcol(c), x1, x2);
+        const double sc = sS[c * 32];
+        p1 = fma(-sc, p1, x1); p2 = fma(-sc, p2, x2);
+        tmem_st_2d(t_pp + tcol(c), p1, p2);
+      }
+    }
+    tmem_wait_st();
+    __syncwarp();
+
+    double w[C];
+    load_state<C>(w_io + p * J, J, lane, w);
+
+    // ------------------------------------------------------------------ time loop
+    uint32_t ra[TC::REGS], rb[TC::REGS];
+    // Elimination and substitution, in place on w[0..N-1]; the cells outside the block that the
+    // end cells couple to contribute oldL0 / oldR0.  With PIPE the five PCR levels of the previous
+    // step's separator system (rr in, xs out) are issued between the elimination chunks.
+    auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double& rr) {
+      constexpr bool PIPE = decltype(pipe_tag)::value;
+      const double w_m_old = w[M];
+      double oldL = oldL0, gL = 0.0, oldR = oldR0, gR = 0.0;
+      int level = 0;
+#pragma unroll
+      for (int k = 0; k < NCH; ++k) {
+        uint32_t* cur = (k & 1) ? rb : ra;
+        if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, ra); }
+        else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, rb); }
+        // One PCR level per chunk.  Warps issue in order, so the level's shuffles are issued HERE and
+        // their consumer sits after the chunk's cell work: the ~26-cycle shuffle latency is covered.
+        double rm = 0.0, rp = 0.0;
+        const bool lvl = PIPE && k < 5;
+        if (lvl) { rm = shfl_up(rr, 1 << k); rp = shfl_dn(rr, 1 << k); }
+#pragma unroll
+        for (int ii = 0; ii < IT; ++ii) {
+          const int i = k * IT + ii;
+          {
+            const int c = i;
+            const double e = chunk_dbl(cur, 4 * ii), b = chunk_dbl(cur, 4 * ii + 1);
+            const double wc = w[c];
+            const double wn = (c == M - 1) ? w_m_old : w[c + 1];
+            double r = rhs_cell<MODE>(e, sr[c], b, oldL, wc, wn, cth);
+            if (c == 0) r += R.bfirst;
+            gL = (i == 0) ? r : fma(-e, gL, r);
+            w[c] = gL;
+            oldL = wc;
+          }
+          if (i < N - M) {
+            const int c = N - 1 - i;
+            const double e = chunk_dbl(cur, 4 * ii + 2), b = chunk_dbl(cur, 4 * ii + 3);
+            const double wc = w[c];
+            double r = rhs_cell<MODE>(e, sr[c], b, oldR, wc, w[c - 1], cth);
+            gR = (i == 0) ? r : fma(-e, gR, r);
+            w[c] = gR;
+            oldR = wc;
+          }
+        }
+        if (lvl) { rr = fma(R.ga[k], rp, fma(R.al[k], rm, rr)); level = k + 1; }
+      }
+      if (PIPE) {
+#pragma unroll
+        for (int l = 0; l < 5; ++l) {
+          if (l >= level) {
+            const int s = 1 << l;
+            const double rm = shfl_up(rr, s), rp = shfl_dn(rr, s);
+            rr = fma(R.ga[l], rp, fma(R.al[l], rm, rr));
+          }
+        }
+        rr *= R.invD;                                // rr now holds xs
+      }
+      w[M] = fma(-sr[M], w[M - 1], w[M]) * delta;
+#pragma unroll
+      for (int j = 0; j < M; ++j) {
+        const int cl = M - 1 - j, cr = M + 1 + j;
+        w[cl] = fma(-sr[cl], w[cl + 1], w[cl]);
+        if (cr < N) w[cr] = fma(-sr[cr], w[cr - 1], w[cr]);
+      }
+    };
+
+    int64_t remaining = nsteps, n_ckpt = 0;
+    TC::ld(t_eb, ra);                               // first (e, b) chunk
+    while (remaining > 0) {
+      const bool ck = ckpt != nullptr && ckpt_every > 0 && remaining >= ckpt_every;
+      const int64_t L = ck ? ckpt_every : remaining; // steps until the true state is needed again
+      // -------- first step of the segment: sweeps on the true state
+      double wl = shfl_up(w[C - 1], 1);
+      double wr = shfl_dn(w[0], 1);
+      if (lane == 0) wl = 0.0;
+      if (lane == 31) wr = 0.0;
+      double rs = fma(R.sbup, wr, fma(R.sbdi, w[C - 1], fma(R.sblo, w[N - 1], R.bsep)));
+      double rr = 0.0;
+      sweeps(std::false_type{}, wl, w[C - 1], t_eb, rr);
+      rr = fma(-R.sup, shfl_dn(w[0], 1), fma(-R.slo, w[N - 1], rs));
+      // -------- pipelined steps: PCR of step n overlaps the sweeps of step n+1
+      for (int64_t i = 1; i < L; ++i) {
+        const double g0_old = w[0], gl_old = w[N - 1];
+        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr);
+        const double xs = rr;
+        const double xsl = shfl_up(xs, 1);          // lane 0: V == P1 == 0, value unused
+        const double x_last = fma(-UL, xs, fma(-VL, xsl, gl_old));      // true values of the finished step
+        const double x_first = fma(-U0, xs, fma(-V0, xsl, g0_old));
+        double x_first_next = shfl_dn(x_first, 1);
+        if (lane == 31) x_first_next = 0.0;
+        rs = fma(R.sbup, x_first_next, fma(R.sbdi, xs, fma(R.sblo, x_last, R.bsep)));
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {             // g' = G + P1 xsl + P2 xs
+          uint32_t* cur = (k & 1) ? rb : ra;
+          if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra); }
+          else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb); }
+#pragma unroll
+          for (int ii = 0; ii < IT; ++ii) {
+            const int i2 = k * IT + ii;
+            w[i2] = fma(chunk_dbl(cur, 4 * ii + 1), xs, fma(chunk_dbl(cur, 4 * ii), xsl, w[i2]));
+            if (i2 < N - M) {
+              const int c = N - 1 - i2;
+              w[c] = fma(chunk_dbl(cur, 4 * ii + 3), xs, fma(chunk_dbl(cur, 4 * ii + 2), xsl, w[c]));
+            }
+          }
+        }
+        rr = fma(-R.sup, shfl_dn(w[0], 1), fma(-R.slo, w[N - 1], rs));
+      }
+      // -------- end of the segment: finish the last step and materialise the true state
+      {
+        const double xs = pcr_solve(rr, R);
+        const double xsl = shfl_up(xs, 1);
+#pragma unroll
+        for (int c = 0; c < N; ++c) w[c] = fma(-su[c * 32], xs, fma(-sv[c * 32], xsl, w[c]));
+        w[C - 1] = xs;
+      }
+      remaining -= L;
+      if (ck) {
+        store_state<C>(ckpt + (n_ckpt * pr.P + p) * J, J, lane, w);
+        ++n_ckpt;
+      }
+    }
+    TC::wait(ra);                                   // drain the prefetch of the step that never comes
+    store_state<C>(w_io + p * J, J, lane, w);
+    __syncwarp();
+  }
+
+  tmem_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc_512(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------
 static int device_limits(int& sms, int& max_smem) {
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -577,7 +846,7 @@ static int launch_fused(const fvm_problem& pr, const double* dt, double theta, i
   return (int)cudaGetLastError();
 }
 
-template <int MODE, int IT>
+template <int MODE, int IT, bool PIPE>
 static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
                              int64_t ckpt_every, double* w, double* ckpt, cudaStream_t stream) {
   constexpr int warps = kFusedThreads / 32;
@@ -585,7 +854,7 @@ static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double the
   int sms = 0, max_smem = 0;
   int st = device_limits(sms, max_smem);
   if (st) return st;
-  auto kern = fused_tmem_kernel<MODE, IT>;
+  auto kern = PIPE ? fused_tmem_pipe_kernel<MODE, IT> : fused_tmem_kernel<MODE, IT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   int64_t blocks = (pr.P + warps - 1) / warps;
@@ -608,15 +877,22 @@ static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, 
   constexpr bool Q = true;
   if (rb) return launch_fused<C, 0, true, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
   if (C == 32 && tmem_enabled()) {
-    const char* its = getenv("FVM_TMEM_IT");     // 2: .x16 loads (experiments); default 4: .x32
-    if (its && its[0] == '2') {
-      if (theta == 0.5) return launch_fused_tmem<1, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      if (theta == 1.0) return launch_fused_tmem<2, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      return launch_fused_tmem<0, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    // FVM_FUSED_PIPE=0 selects the kernel without the delayed correction (A/B runs and profiling)
+    const char* pp = getenv("FVM_FUSED_PIPE");
+    if (pp && pp[0] == '0') {
+      if (theta == 0.5) return launch_fused_tmem<1, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      if (theta == 1.0) return launch_fused_tmem<2, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      return launch_fused_tmem<0, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
     }
-    if (theta == 0.5) return launch_fused_tmem<1, 4>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    if (theta == 1.0) return launch_fused_tmem<2, 4>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    return launch_fused_tmem<0, 4>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    const char* its = getenv("FVM_TMEM_IT");     // 4: .x32 loads (experiments); default 2: .x16
+    if (its && its[0] == '4') {
+      if (theta == 0.5) return launch_fused_tmem<1, 4, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      if (theta == 1.0) return launch_fused_tmem<2, 4, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      return launch_fused_tmem<0, 4, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    }
+    if (theta == 0.5) return launch_fused_tmem<1, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    if (theta == 1.0) return launch_fused_tmem<2, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    return launch_fused_tmem<0, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
   }
   if (theta == 0.5) return launch_fused<C, 1, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
   if (theta == 1.0) return launch_fused<C, 2, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);

@@ -28,6 +28,15 @@ __device__ __forceinline__ void tmem_st_x4(uint32_t taddr, uint32_t a, uint32_t 
   asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};"
                :: "r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+// Synchronous load of two doubles (4 columns): for set-up code with run-time column indices.
+__device__ __forceinline__ void tmem_ld_2d(uint32_t taddr, double& x, double& y) {
+  uint32_t a, b, c, d;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];\n\t"
+               "tcgen05.wait::ld.sync.aligned;"
+               : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(taddr) : "memory");
+  x = __hiloint2double((int)b, (int)a);
+  y = __hiloint2double((int)d, (int)c);
+}
 __device__ __forceinline__ void tmem_st_2d(uint32_t taddr, double x, double y) {
   tmem_st_x4(taddr, (uint32_t)__double2loint(x), (uint32_t)__double2hiint(x),
              (uint32_t)__double2loint(y), (uint32_t)__double2hiint(y));
