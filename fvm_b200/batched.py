@@ -178,6 +178,35 @@ class BatchedAdvectionDiffusionModel(object):
         self._asm[key] = out
         return out
 
+    def diagnostics(self, w=None):
+        """Per problem, on the device: min/max Peclet number (a h / d with the unmodified d, what
+        the reference's constructor warns about, fvm_classes.py:103-107), min/max CFL number (:110-114)
+        and, when a state (P, J) is given, the conserved "area" sum_j w_j h_j (:420-421)."""
+        torch = _lib.require_cuda()
+        pr = self._problem() if hasattr(self, "left_flux") else self._problem_no_bc()
+        out = torch.empty((self.P, 5), dtype=torch.float64, device=self.device)
+        wt = None
+        if w is not None:
+            wt = self._dev(w).reshape(self.P, self.J).contiguous()
+        with torch.cuda.device(self.device):
+            st = _lib.lib().fvm_diagnostics(ctypes.byref(pr), _lib.ptr(self.k), _lib.ptr(wt), self.J, 1,
+                                            _lib.ptr(out), _lib.stream_ptr())
+        _lib.check(st, "fvm_diagnostics")
+        res = dict(peclet_min=out[:, 0], peclet_max=out[:, 1], cfl_min=out[:, 2], cfl_max=out[:, 3])
+        if w is not None:
+            res["area"] = out[:, 4]
+        return res
+
+    def _problem_no_bc(self):
+        """struct fvm_problem for calls that do not look at the boundary rows."""
+        pr = _lib.FvmProblem()
+        pr.J, pr.P = self.J, self.P
+        pr.faces = self.faces.data_ptr()
+        pr.a, (pr.a_ps, pr.a_cs) = self.a.data_ptr(), self._a_str
+        pr.d, (pr.d_ps, pr.d_cs) = self.d.data_ptr(), self._d_str
+        pr.scheme = _lib.SCHEMES[self.discretisation]
+        return pr
+
     # ------------------------------------------------------------------ variant 1
     def factor(self, theta):
         """Factored theta operators in the interleaved layout (fvm_theta_factor)."""

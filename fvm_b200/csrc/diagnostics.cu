@@ -1,0 +1,51 @@
+// On-device diagnostics of a batch: extrema of the cell Peclet number and of the CFL number (the
+// quantities behind the reference's warnings, fvm_classes.py:103-114,135-139, printed by the demo
+// at :379-380) and the conserved "area" sum_j w_j h_j the demo prints every step (:420-421).
+// One warp per problem, strided over the cells, shuffle reduction.
+#include "fvm_device.cuh"
+
+namespace fvm {
+
+__global__ void __launch_bounds__(256) diagnostics_kernel(fvm_problem pr, const double* __restrict__ dt,
+                                                          const double* __restrict__ w, int64_t w_ps, int64_t w_cs,
+                                                          double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t p = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (p >= pr.P) return;
+  double pe_lo = INFINITY, pe_hi = -INFINITY, cf_lo = INFINITY, cf_hi = -INFINITY, mass = 0.0;
+  const double k = dt ? dt[p] : 0.0;
+  for (int64_t j = lane; j < pr.J; j += 32) {
+    const double h = sub(pr.faces[j + 1], pr.faces[j]);
+    const double a = pr.a[p * pr.a_ps + j * pr.a_cs];
+    const double d = pr.d[p * pr.d_ps + j * pr.d_cs];
+    const double mu = dvd(mul(a, h), d);           // peclet_number() on the unmodified d, :103,135-136
+    const double c = dvd(mul(a, k), h);            // CFL_condition(), :138-139
+    pe_lo = fmin(pe_lo, mu); pe_hi = fmax(pe_hi, mu);
+    cf_lo = fmin(cf_lo, c); cf_hi = fmax(cf_hi, c);
+    if (w) mass = fma(w[p * w_ps + j * w_cs], h, mass);
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    pe_lo = fmin(pe_lo, __shfl_xor_sync(0xffffffffu, pe_lo, s));
+    pe_hi = fmax(pe_hi, __shfl_xor_sync(0xffffffffu, pe_hi, s));
+    cf_lo = fmin(cf_lo, __shfl_xor_sync(0xffffffffu, cf_lo, s));
+    cf_hi = fmax(cf_hi, __shfl_xor_sync(0xffffffffu, cf_hi, s));
+    mass += __shfl_xor_sync(0xffffffffu, mass, s);
+  }
+  if (lane == 0) {
+    double* o = out + p * 5;
+    o[0] = pe_lo; o[1] = pe_hi; o[2] = cf_lo; o[3] = cf_hi; o[4] = mass;
+  }
+}
+
+}  // namespace fvm
+
+extern "C" int fvm_diagnostics(const fvm_problem* prob, const double* dt, const double* w, int64_t w_ps,
+                               int64_t w_cs, double* out, void* stream) {
+  if (!prob || !prob->faces || !prob->a || !prob->d || !out) return FVM_ERR_INVALID_ARG;
+  if (prob->J < 1 || prob->P < 1) return FVM_ERR_INVALID_ARG;
+  const int64_t blocks = (prob->P + 7) / 8;
+  if (blocks > 0x7fffffffLL) return FVM_ERR_UNSUPPORTED;
+  fvm::diagnostics_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(*prob, dt, w, w_ps, w_cs, out);
+  return (int)cudaGetLastError();
+}

@@ -111,6 +111,14 @@ int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, const double* 
                           const double* bt_left, const double* bt_right, double* w, int64_t w_ps,
                           int64_t w_cs, int64_t nsteps, void* stream);
 
+/* Diagnostics of a batch, out[p*5 + 0..4] = min and max over the cells of the Peclet number
+ * a h / d (on the unmodified d, as AdvectionDiffusionModel.__init__ checks it,
+ * fvm_classes.py:103-107,135-136), min and max of the CFL number a dt / h (:110-114,138-139;
+ * dt may be NULL: 0), and the "area" sum_j w_j h_j the demo prints every step (:420-421; w may be
+ * NULL: 0).  w is strided like every state array. */
+int fvm_diagnostics(const fvm_problem* prob, const double* dt, const double* w, int64_t w_ps,
+                    int64_t w_cs, double* out, void* stream);
+
 /* Largest J the fused on-chip variant accepts. */
 int64_t fvm_fused_max_cells(void);
 

@@ -86,3 +86,23 @@ def test_warnings_and_errors_match_the_reference():
         h = np.diff(f)
         assert b[0] == 0.5 / h[0] and b[-1] == -0.25 / h[-1] and np.all(b[1:-1] == 0)
         assert np.all(m.alpha_matrix().diagonal() == 1)
+
+
+def test_device_diagnostics_match_numpy():
+    """Peclet / CFL extrema (fvm_classes.py:103-114,379-380) and the printed "area" (:420-421)."""
+    from fvm_b200 import BatchedAdvectionDiffusionModel, workloads as W
+    rng = np.random.default_rng(9)
+    J, P = 777, 5
+    f = W.graded_faces(J, 30.0)
+    h = np.diff(f)
+    a = rng.normal(size=(P, J))
+    d = 10 ** rng.uniform(-3, 0, size=(P, 1)) * np.ones((P, J))
+    k = rng.uniform(1e-4, 1e-2, P)
+    w = rng.random((P, J))
+    m = BatchedAdvectionDiffusionModel(f, a, d, k, "upwind")
+    out = {key: val.cpu().numpy() for key, val in m.diagnostics(w).items()}
+    mu = a * h / d
+    cfl = a * k[:, None] / h
+    assert np.array_equal(out["peclet_min"], mu.min(1)) and np.array_equal(out["peclet_max"], mu.max(1))
+    assert np.array_equal(out["cfl_min"], cfl.min(1)) and np.array_equal(out["cfl_max"], cfl.max(1))
+    assert np.allclose(out["area"], (w * h).sum(1), rtol=1e-13)
