@@ -56,6 +56,9 @@ _SIGNATURES = {
                                         c_ptr, c_ptr, c_ptr]),
     "fvm_theta_step_thomas": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_dbl,
                                              c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr]),
+    "fvm_explicit_step": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i32, c_i32,
+                                         c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr]),
+    "fvm_mesh_check": (ctypes.c_int, [c_ptr, c_i64, c_ptr, c_ptr]),
     "fvm_diagnostics": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr]),
     "fvm_fused_max_cells": (c_i64, []),
     "fvm_theta_run_fused": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_dbl, c_i64, c_i64,

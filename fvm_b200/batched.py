@@ -271,6 +271,8 @@ class BatchedAdvectionDiffusionModel(object):
         ce = int(checkpoint_every or 0)
         n_ck = nsteps // ce if ce > 0 else 0
         ckpt = torch.empty((n_ck, self.P, self.J), dtype=torch.float64, device=self.device) if n_ck else None
+        if float(theta) == 0.0:
+            return self._run_explicit(w, nsteps, ce, ckpt), ckpt
         if variant == "auto":
             variant = "fused" if self.J <= int(_lib.lib().fvm_fused_max_cells()) else "thomas"
         if variant == "fused":
@@ -290,6 +292,23 @@ class BatchedAdvectionDiffusionModel(object):
         else:
             raise ValueError("variant must be 'auto', 'fused' or 'thomas'")
         return w, ckpt
+
+    def _run_explicit(self, w, nsteps, ce, ckpt):
+        """theta = 0: A = I, a step is w <- (I + k*alpha*M) w + beta (fvm_explicit_step)."""
+        torch = _lib.require_cuda()
+        asm = self.assemble()
+        bufs = [w, torch.empty_like(w)]
+        with torch.cuda.device(self.device):
+            for n in range(nsteps):
+                src, dst = bufs[n & 1], bufs[1 - (n & 1)]
+                st = _lib.lib().fvm_explicit_step(
+                    self.J, self.P, _lib.ptr(asm["lo"]), _lib.ptr(asm["di"]), _lib.ptr(asm["up"]), self.J, 1,
+                    _lib.ptr(self.k), asm["alpha_left"], asm["alpha_right"], _lib.ptr(asm["beta_left"]),
+                    _lib.ptr(asm["beta_right"]), _lib.ptr(src), _lib.ptr(dst), self.J, 1, _lib.stream_ptr())
+                _lib.check(st, "fvm_explicit_step")
+                if ce > 0 and (n + 1) % ce == 0 and ckpt is not None:
+                    ckpt[(n + 1) // ce - 1].copy_(dst)
+        return bufs[nsteps & 1]
 
     def run_host(self, w_host, theta, nsteps, out=None, variant="auto", chunks=8):
         """Host-buffer form of :meth:`run`: ``w_host`` (P, J) lives in host memory (numpy array

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 BUILD = os.path.join(PKG, "_build")
 LIB = os.path.join(PKG, "libfvm_b200.so")
-SOURCES = ["api.cu", "assemble.cu", "thomas.cu", "fused.cu", "fused_cta.cu", "spike.cu", "diagnostics.cu"]
+SOURCES = ["api.cu", "assemble.cu", "thomas.cu", "fused.cu", "fused_cta.cu", "spike.cu", "diagnostics.cu", "explicit.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 

@@ -49,3 +49,39 @@ extern "C" int fvm_diagnostics(const fvm_problem* prob, const double* dt, const 
   fvm::diagnostics_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(*prob, dt, w, w_ps, w_cs, out);
   return (int)cudaGetLastError();
 }
+
+// Mesh validation on the device, for meshes too large for the host-side check of Mesh.__init__
+// (len(faces) != len(set(faces)), fvm_classes.py:36-37, hashes every face: infeasible at 2^30).
+// counts[0] = cells of zero width (adjacent duplicate faces: what the reference rejects for a
+// sorted mesh), counts[1] = cells of negative width (unsorted faces: the reference accepts them
+// silently); counts are accumulated, so clear them first.
+namespace fvm {
+__global__ void __launch_bounds__(256) mesh_check_kernel(const double* __restrict__ faces, int64_t n_cells,
+                                                         unsigned long long* __restrict__ counts) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  unsigned long long zero = 0, neg = 0;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_cells; j += stride) {
+    const double h = sub(faces[j + 1], faces[j]);
+    zero += (h == 0.0);
+    neg += (h < 0.0);
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    zero += __shfl_xor_sync(0xffffffffu, zero, s);
+    neg += __shfl_xor_sync(0xffffffffu, neg, s);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (zero) atomicAdd(&counts[0], zero);
+    if (neg) atomicAdd(&counts[1], neg);
+  }
+}
+}  // namespace fvm
+
+extern "C" int fvm_mesh_check(const double* faces, int64_t n_cells, uint64_t* counts, void* stream) {
+  if (!faces || !counts || n_cells < 1) return FVM_ERR_INVALID_ARG;
+  int64_t blocks = (n_cells + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  fvm::mesh_check_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(faces, n_cells,
+                                                                             (unsigned long long*)counts);
+  return (int)cudaGetLastError();
+}

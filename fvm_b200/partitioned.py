@@ -160,6 +160,23 @@ class PartitionedAdvectionDiffusionModel(object):
             return s, (s.shape[1], 1)
         raise ValueError("coefficient must be scalar, (P,), per-cell or (P, per-cell)")
 
+    def check_mesh(self):
+        """The duplicate-face check of Mesh.__init__ (fvm_classes.py:36-37) on the device, for this
+        rank's slab: raises ValueError on zero-width cells; returns the number of negative-width
+        cells (unsorted faces, which the reference accepts silently)."""
+        torch = _lib.require_cuda()
+        counts = torch.zeros(2, dtype=torch.int64, device=self.device)
+        n = int(self.faces.numel()) - 1
+        with torch.cuda.device(self.device):
+            st = _lib.lib().fvm_mesh_check(_lib.ptr(self.faces), n, ctypes.c_void_p(counts.data_ptr()),
+                                           _lib.stream_ptr())
+        _lib.check(st, "fvm_mesh_check")
+        zero, neg = (int(v) for v in counts.cpu())
+        if zero:
+            raise ValueError("The faces array contains duplicated positions (%d zero-width cells). No cell can "
+                             "have zero volume so please update with unique face positions." % zero)
+        return neg
+
     def set_boundary_conditions(self, left_flux=None, right_flux=None, left_value=None, right_value=None):
         """Same keywords as the reference (fvm_classes.py:141-147); fluxes may be per problem."""
         self.left_flux, self.right_flux = left_flux, right_flux

@@ -111,6 +111,15 @@ int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, const double* 
                           const double* bt_left, const double* bt_right, double* w, int64_t w_ps,
                           int64_t w_cs, int64_t nsteps, void* stream);
 
+/* theta = 0 (explicit Euler, A = I): one step  w_out = (I + dt*alpha*M) w_in + beta  of the same
+ * loop [fvm_classes.py:408-411 with theta = 0 at :376-377].  M diagonals from fvm_assemble
+ * (strides m_ps, m_cs); w_in and w_out must be different buffers with strides (w_ps, w_cs);
+ * beta_left/right [P] may be NULL. */
+int fvm_explicit_step(int64_t J, int64_t P, const double* lo, const double* di, const double* up,
+                      int64_t m_ps, int64_t m_cs, const double* dt, int32_t alpha_left,
+                      int32_t alpha_right, const double* beta_left, const double* beta_right,
+                      const double* w_in, double* w_out, int64_t w_ps, int64_t w_cs, void* stream);
+
 /* Diagnostics of a batch, out[p*5 + 0..4] = min and max over the cells of the Peclet number
  * a h / d (on the unmodified d, as AdvectionDiffusionModel.__init__ checks it,
  * fvm_classes.py:103-107,135-136), min and max of the CFL number a dt / h (:110-114,138-139;
@@ -118,6 +127,13 @@ int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, const double* 
  * NULL: 0).  w is strided like every state array. */
 int fvm_diagnostics(const fvm_problem* prob, const double* dt, const double* w, int64_t w_ps,
                     int64_t w_cs, double* out, void* stream);
+
+/* Mesh validation for meshes too large for the reference's host-side duplicate check
+ * (Mesh.__init__, fvm_classes.py:36-37): adds to counts[0] the number of zero-width cells
+ * (adjacent duplicate faces) and to counts[1] the number of negative-width cells (unsorted faces,
+ * which the reference accepts) among the n_cells cells of faces[0..n_cells].  counts: two device
+ * uint64, cleared by the caller. */
+int fvm_mesh_check(const double* faces, int64_t n_cells, uint64_t* counts, void* stream);
 
 /* Largest J the fused on-chip variant accepts. */
 int64_t fvm_fused_max_cells(void);

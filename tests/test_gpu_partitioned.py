@@ -155,3 +155,14 @@ def test_cells_split_over_ranks(tmp_path, world, J):
     for p in range(2):
         want = oracle_run(f, a[p], d[p], k[p], "exponential", bc, 0.5, w0[p], 30)
         assert step_error(got[p], want, 1.3) < TOL
+
+
+def test_device_mesh_check():
+    f = W.graded_faces(5000, 10.0)
+    m = PartitionedAdvectionDiffusionModel(f, 1.0, 0.1, 1e-3, "central", config=1)
+    assert m.check_mesh() == 0
+    g = f.copy(); g[1234] = g[1233]                           # duplicate face -> zero-width cell
+    with pytest.raises(ValueError):
+        PartitionedAdvectionDiffusionModel(g, 1.0, 0.1, 1e-3, "central", config=1).check_mesh()
+    g = f.copy(); g[[100, 101]] = g[[101, 100]]               # unsorted: accepted, reported
+    assert PartitionedAdvectionDiffusionModel(g, 1.0, 0.1, 1e-3, "central", config=1).check_mesh() == 1

@@ -233,7 +233,7 @@ def test_rejects_bad_arguments():
         m.run(np.ones((1, 10000)), 0.5, 1, variant="fused")       # J > fused maximum (8192)
     assert e.value.status == -2
     with pytest.raises(FvmError):
-        m.run(np.ones((1, 10000)), 0.0, 1, variant="thomas")      # theta must be in (0, 1]
+        m.run(np.ones((1, 10000)), 1.5, 1, variant="thomas")      # theta must be in [0, 1]
     with pytest.raises(UnboundLocalError):
         m2 = BatchedAdvectionDiffusionModel(f, 1.0, 0.1, 1e-3, "central")
         m2.set_boundary_conditions()
@@ -257,3 +257,21 @@ def test_run_host_pipelined_chunks_equal_device_run():
     assert torch.equal(out, w_dev.cpu())
     out1 = m.run_host(wl["w0"], 0.5, 30, chunks=1)         # numpy input, single chunk
     assert torch.equal(out1, w_dev.cpu())
+
+
+def test_theta_zero_explicit_euler():
+    """theta = 0 is legal in the reference's loop (A = I, fvm_classes.py:376-377): routed to the
+    explicit kernel; checked against the oracle's literal loop inside the stability limit."""
+    J = 60
+    f = W.graded_faces(J, 3.0)
+    h = np.diff(f)
+    c = 0.5 * (f[1:] + f[:-1])
+    a = np.array([1.0, -0.5]); d = np.array([0.02, 0.05])
+    k = 0.2 * h.min() ** 2 / d                              # explicit diffusion limit with margin
+    w0 = np.stack([W.pulse(c) + 0.2, np.cos(np.pi * c) ** 2])
+    for bc in (dict(left_flux=0.1, right_flux=-0.2), dict(left_value=1.0, right_value=0.0)):
+        _, ck = run_gpu(f, a, d, k, "upwind", bc, 0.0, w0, 40, 20, "auto")
+        for p in range(2):
+            asm = O.assemble(f, a[p], d[p], "upwind", **bc)
+            want = O.theta_run_scipy(asm, k[p], 0.0, w0[p], 40, every=20)
+            assert step_error(ck[:, p], want, np.max(np.abs(w0[p]))) < 1e-12
