@@ -503,3 +503,86 @@ extern "C" int fvm_spike_local_static(int64_t n_tiles, int64_t P, int32_t config
                                             rr, rr_stride, g_first);
   return (int)cudaGetLastError();
 }
+
+// ------------------------------------------------------------------------------------------
+// Rank-level SPIKE over the separator system (partitioned.py: _prepare_rank_level): the two small
+// kernels around the per-step all-gather.
+namespace fvm {
+
+// What a rank contributes to the gather, 4 doubles per problem: first and last value of its block
+// solution gr, its separator's right-hand side (the local solve passes it through: that row is
+// decoupled) and the first cell of its slab.
+__global__ void rank_pack_kernel(int64_t P, int64_t nt, const double* __restrict__ gr,
+                                 const double* __restrict__ g_first, double* __restrict__ packet) {
+  const int64_t pi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pi >= P) return;
+  const double* g = gr + pi * nt;
+  double* o = packet + pi * 4;
+  o[0] = g[0]; o[1] = g[nt - 2]; o[2] = g[nt - 1]; o[3] = g_first[pi];
+}
+
+// After the gather (allp[rank][problem][4]): right-hand side and solution of the `world`-unknown
+// top system (dense inverse), this rank's separator values xs_ext[1..nt] with the previous rank's
+// separator in xs_ext[0], and the new value of the next rank's first cell (this rank's right ghost).
+// cst[problem][7][world]: sup of every rank's last tile, the separator rows' couplings (lo, up), the
+// rank spikes at every rank's first tile (vf, wf) and the tile spikes (V0, W0) of every rank's first tile.
+__global__ void __launch_bounds__(256) rank_top_kernel(int64_t P, int64_t nt, int world, int rank,
+                                                       const double* __restrict__ allp,
+                                                       const double* __restrict__ top_inv,
+                                                       const double* __restrict__ cst,
+                                                       const double* __restrict__ gr, const double* __restrict__ Vr,
+                                                       const double* __restrict__ Wr, double* __restrict__ xs_ext,
+                                                       double* __restrict__ next_first) {
+  __shared__ double rhs[64], X[64];
+  const int64_t pi = blockIdx.x;
+  const int t = threadIdx.x;
+  const double* c = cst + pi * 7 * world;
+  auto pk = [&](int r, int i) { return allp[((int64_t)r * P + pi) * 4 + i]; };
+  if (t < world) {
+    const bool has_next = t + 1 < world;
+    const double gfirst_n = has_next ? pk(t + 1, 0) : 0.0, cell_n = has_next ? pk(t + 1, 3) : 0.0;
+    rhs[t] = pk(t, 2) - c[0 * world + t] * cell_n - c[1 * world + t] * pk(t, 1) - c[2 * world + t] * gfirst_n;
+  }
+  __syncthreads();
+  if (t < world) {
+    const double* row = top_inv + (pi * world + t) * world;
+    double acc = 0.0;
+    for (int j = 0; j < world; ++j) acc = fma(row[j], rhs[j], acc);
+    X[t] = acc;
+  }
+  __syncthreads();
+  const double Xr = X[rank], Xl = rank > 0 ? X[rank - 1] : 0.0;
+  double* xe = xs_ext + pi * (nt + 1);
+  for (int64_t k = t; k < nt; k += blockDim.x) {
+    const int64_t o = pi * nt + k;
+    xe[1 + k] = (k == nt - 1) ? Xr : fma(-Wr[o], Xr, fma(-Vr[o], Xl, gr[o]));
+  }
+  if (t == 0) {
+    xe[0] = Xl;
+    if (rank + 1 < world) {
+      const int n = rank + 1;
+      const double xs_n0 = fma(-c[4 * world + n], X[n], fma(-c[3 * world + n], Xr, pk(n, 0)));   // next rank's first separator
+      next_first[pi] = fma(-c[6 * world + n], xs_n0, fma(-c[5 * world + n], Xr, pk(n, 3)));
+    }
+  }
+}
+
+}  // namespace fvm
+
+extern "C" int fvm_spike_rank_pack(int64_t P, int64_t nt, const double* gr, const double* g_first, double* packet,
+                                   void* stream) {
+  if (!gr || !g_first || !packet || P < 1 || nt < 2) return FVM_ERR_INVALID_ARG;
+  fvm::rank_pack_kernel<<<(unsigned)((P + 127) / 128), 128, 0, (cudaStream_t)stream>>>(P, nt, gr, g_first, packet);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_spike_rank_top(int64_t P, int64_t nt, int32_t world, int32_t rank, const double* allp,
+                                  const double* top_inv, const double* cst, const double* gr, const double* Vr,
+                                  const double* Wr, double* xs_ext, double* next_first, void* stream) {
+  if (!allp || !top_inv || !cst || !gr || !Vr || !Wr || !xs_ext || !next_first) return FVM_ERR_INVALID_ARG;
+  if (P < 1 || P > 0x7fffffffLL || nt < 2 || world < 2 || world > 64 || rank < 0 || rank >= world)
+    return FVM_ERR_INVALID_ARG;
+  fvm::rank_top_kernel<<<(unsigned)P, 256, 0, (cudaStream_t)stream>>>(P, nt, world, rank, allp, top_inv, cst, gr, Vr,
+                                                                     Wr, xs_ext, next_first);
+  return (int)cudaGetLastError();
+}

@@ -318,10 +318,16 @@ class PartitionedAdvectionDiffusionModel(object):
         TD = sd_ - sl_ * wlast - su_ * nxt(vf)
         TU = -su_ * nxt(wf)
         top = torch.diag_embed(TD) + torch.diag_embed(TL[:, 1:], offset=-1) + torch.diag_embed(TU[:, :-1], offset=1)
-        self.top_inv = torch.linalg.inv(top)                             # (P, W, W)
-        self.top_sl, self.top_su = sl_, su_                              # separator rows' couplings, all ranks
-        self.top_vf, self.top_wf = vf, wf                                # rank spikes at every rank's first tile
+        self.top_inv = torch.linalg.inv(top).contiguous()                # (P, W, W)
+        last = torch.arange(1, W + 1, device=dev) * nt - 1              # every rank's last (separator) tile
+        first = torch.arange(0, W, device=dev) * nt                      # every rank's first tile
+        # constants of fvm_spike_rank_top, (P, 7, W): up of the last tiles; lo, up of the rank separators'
+        # rows; rank spikes and tile spikes at the first tiles
+        self.top_cst = torch.stack([self.sup_all[:, last], sl_, su_, vf, wf, self.V0_all[:, first],
+                                    self.W0_all[:, first]], dim=1).contiguous()
         self.xs_ext = torch.zeros((P, nt + 1), dtype=torch.float64, device=dev)
+        self.packet = torch.zeros((P, 4), dtype=torch.float64, device=dev)
+        self.next_first = torch.zeros(P, dtype=torch.float64, device=dev)
 
     # ------------------------------------------------------------------ state
     def set_state(self, w):
@@ -398,33 +404,22 @@ class PartitionedAdvectionDiffusionModel(object):
                 self._cur = 1 - self._cur
 
     def _step_rank_level(self, w_out, wptr):
-        """Second half of a step with the rank-level hierarchy (see _prepare_rank_level)."""
-        torch = _lib.require_cuda()
-        lib, P, nt, comm, r, W = _lib.lib(), self.P, self.nt, self.comm, self.comm.rank, self.comm.world
-        rr_sep = self.rr[:, nt - 1].clone()                              # lacks -up*g_first(next rank)
-        self.rr[:, nt - 1] = 0.0
-        gr = self._reduced_local_solve(self.rr)                          # block solution, couplings cut
-        packet = torch.stack([gr[:, 0], gr[:, nt - 2], rr_sep, self.g_first], dim=1)     # (P, 4)
-        allp = comm.all_gather(packet)                                   # (W, P, 4)
-        gfirst, glast, rsep, cell_first = [allp[:, :, i].t() for i in range(4)]          # (P, W)
-        nxt = lambda x: torch.cat([x[:, 1:], torch.zeros_like(x[:, :1])], dim=1)
-        last = torch.arange(1, W + 1, device=self.device) * nt - 1                        # separator tiles
-        rhs = rsep - self.sup_all[:, last] * nxt(cell_first) - self.top_sl * glast - self.top_su * nxt(gfirst)
-        X = torch.einsum("pij,pj->pi", self.top_inv, rhs)                # rank separators, all ranks (P, W)
-        Xl = X[:, r - 1] if r > 0 else torch.zeros_like(X[:, 0])
-        xs = gr - self.Vr * Xl[:, None] - self.Wr * X[:, r][:, None]
-        xs[:, nt - 1] = X[:, r]
-        self.xs_ext[:, 0] = Xl
-        self.xs_ext[:, 1:] = xs
-        next_first = None
-        if r < W - 1:
-            # the next rank's first separator, then its (corrected) first cell = my right ghost
-            xs_n0 = gfirst[:, r + 1] - self.top_vf[:, r + 1] * X[:, r] - self.top_wf[:, r + 1] * X[:, r + 1]
-            k1 = (r + 1) * nt
-            next_first = (cell_first[:, r + 1] - self.V0_all[:, k1] * X[:, r] - self.W0_all[:, k1] * xs_n0).contiguous()
+        """Second half of a step with the rank-level hierarchy (see _prepare_rank_level): local block
+        solve of the separator system, ONE all-gather of 4 doubles per problem, top system, finalize."""
+        lib, P, nt, comm = _lib.lib(), self.P, self.nt, self.comm
+        gr = self._reduced_local_solve(self.rr)       # block solution; the separator row passes its rhs through
+        st = lib.fvm_spike_rank_pack(P, nt, _lib.ptr(gr), _lib.ptr(self.g_first), _lib.ptr(self.packet),
+                                     _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_rank_pack")
+        allp = comm.all_gather(self.packet)                              # (W, P, 4)
+        st = lib.fvm_spike_rank_top(P, nt, comm.world, comm.rank, _lib.ptr(allp), _lib.ptr(self.top_inv),
+                                    _lib.ptr(self.top_cst), _lib.ptr(gr), _lib.ptr(self.Vr), _lib.ptr(self.Wr),
+                                    _lib.ptr(self.xs_ext), _lib.ptr(self.next_first), _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_rank_top")
+        nf = self.next_first if comm.rank < comm.world - 1 else None
         st = lib.fvm_spike_finalize(nt, P, self.config, self.extents, 1, nt + 1, _lib.ptr(self.Vt),
                                     _lib.ptr(self.Wt), _lib.ptr(self.xs_ext), wptr(w_out), self.w_stride,
-                                    _lib.ptr(next_first), _lib.stream_ptr())
+                                    _lib.ptr(nf), _lib.stream_ptr())
         _lib.check(st, "fvm_spike_finalize")
 
     def run(self, w, theta, nsteps):

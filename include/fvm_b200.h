@@ -211,6 +211,24 @@ int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, const int32_t
                        const double* Wt, const double* xs, double* w, int64_t w_stride,
                        const double* next_first, void* stream);
 
+/* Rank-level SPIKE over the separator system (cells split over GPUs; no counterpart in the
+ * reference, which is single-process).  Each rank solves the block of its own nt tile separators
+ * with fvm_spike_reduce_solve (couplings to the neighbouring ranks cut, its last separator
+ * decoupled), then:
+ *  fvm_spike_rank_pack: packet[P][4] = what the rank contributes to the per-step all-gather
+ *    (first and last block value, its separator's right-hand side, its slab's first cell);
+ *  fvm_spike_rank_top: from the gathered packets allp[world][P][4], the dense inverse
+ *    top_inv[P][world][world] of the rank-separator system and the constants cst[P][7][world]
+ *    (rows: up of every rank's last tile; lo, up of the rank separators' rows; rank spikes Vr, Wr
+ *    and tile spikes V0, W0 at every rank's first tile) it writes this rank's separator values
+ *    xs_ext[P][nt+1] (entry 0 = the previous rank's separator) and next_first[P], the new value
+ *    of the next rank's first cell. */
+int fvm_spike_rank_pack(int64_t P, int64_t nt, const double* gr, const double* g_first, double* packet,
+                        void* stream);
+int fvm_spike_rank_top(int64_t P, int64_t nt, int32_t world, int32_t rank, const double* allp,
+                       const double* top_inv, const double* cst, const double* gr, const double* Vr,
+                       const double* Wr, double* xs_ext, double* next_first, void* stream);
+
 /* Largest P * n_tiles fvm_spike_local_static accepts (65536 tiles = 512 KiB of scratch). */
 int64_t fvm_spike_static_max_tiles(void);
 
