@@ -151,14 +151,26 @@ __global__ void reduced_factor_kernel(int64_t n, int64_t P, const double* __rest
 }
 
 // ------------------------------------------------------------------------------------------ per step
-template <int TPB, int CPT, int MODE>
+// LAZY correction: w_in holds the previous step's UNCORRECTED tile solutions g (true values only at
+// the separators and in the ghosts); the correction x = g - Vt xs(k-1) - Wt xs(k) is applied while
+// the tile is loaded, by the threads whose cells lie inside the spike extents (the first tl and the
+// last tr threads of the CTA).  This replaces correct_kernel's separate read-modify-write pass:
+// Vt, Wt are still read (16 B per corrected cell) but g is not re-read and x is never written.
+struct LazyCorrection {
+  const double* Vt; const double* Wt; const double* xs;   // xs indexed by tile_offset + k, per problem n_tiles_global
+  int64_t tile_offset, n_tiles_global;
+  int tl, tr;
+};
+
+template <int TPB, int CPT, int MODE, bool LAZY>
 __global__ void __launch_bounds__(TPB) tile_solve_kernel(
     int64_t n_tiles, const double* __restrict__ p, const double* __restrict__ q,
     const double* __restrict__ b, const double* __restrict__ sep, const double* __restrict__ bends,
     int has_first_cell, int64_t jl_last, double cth, const double* __restrict__ w_in,
-    double* __restrict__ w_out, double* __restrict__ rs, int64_t w_stride) {
+    double* __restrict__ w_out, double* __restrict__ rs, int64_t w_stride, LazyCorrection lz) {
   constexpr int T = TPB * CPT;
   __shared__ double sm[66];
+  __shared__ double sedge[LAZY ? 2 * TPB : 1];
   const int64_t k = blockIdx.x, pi = blockIdx.y;
   const int tid = threadIdx.x;
   const int64_t base = (pi * n_tiles + k) * T + tid;                 // into p, q, b (tiled: + c*TPB)
@@ -169,10 +181,34 @@ __global__ void __launch_bounds__(TPB) tile_solve_kernel(
     pc[c] = p[base + c * TPB]; qc[c] = q[base + c * TPB]; g[c] = b[base + c * TPB];
     w[c + 1] = w_in[wbase + c * TPB + tid];
   }
-  // left neighbour of this thread's first cell = last cell of thread tid-1 (or the position just
-  // before the tile: previous tile's separator / the left ghost); right neighbour likewise
-  w[0] = w_in[tid == 0 ? wbase - 1 : wbase + (CPT - 1) * TPB + tid - 1];
-  w[CPT + 1] = w_in[tid == TPB - 1 ? wbase + T : wbase + tid + 1];
+  if (!LAZY) {
+    // left neighbour of this thread's first cell = last cell of thread tid-1 (or the position just
+    // before the tile: previous tile's separator / the left ghost); right neighbour likewise
+    w[0] = w_in[tid == 0 ? wbase - 1 : wbase + (CPT - 1) * TPB + tid - 1];
+    w[CPT + 1] = w_in[tid == TPB - 1 ? wbase + T : wbase + tid + 1];
+  } else {
+    const int64_t kg = lz.tile_offset + k;
+    const double* X_ = lz.xs + pi * lz.n_tiles_global;
+    const double xk = X_[kg];
+    const double xl = kg > 0 ? X_[kg - 1] : 0.0;
+    if (tid < lz.tl || tid >= TPB - lz.tr) {               // (the separator's Vt, Wt are 0: it stays xs)
+#pragma unroll
+      for (int c = 0; c < CPT; ++c)
+        w[c + 1] = fma(-lz.Wt[base + c * TPB], xk, fma(-lz.Vt[base + c * TPB], xl, w[c + 1]));
+    }
+    sedge[tid] = w[1];
+    sedge[TPB + tid] = w[CPT];
+    __syncthreads();
+    w[0] = tid == 0 ? w_in[wbase - 1] : sedge[TPB + tid - 1];   // before the tile: a separator or the ghost, both true
+    if (tid < TPB - 1) {
+      w[CPT + 1] = sedge[tid + 1];
+    } else if (k + 1 < n_tiles) {                          // next tile's first cell, corrected with ITS separators
+      const int64_t on = (pi * n_tiles + k + 1) * T;
+      w[CPT + 1] = fma(-lz.Wt[on], X_[kg + 1], fma(-lz.Vt[on], xk, w_in[wbase + T]));
+    } else {
+      w[CPT + 1] = w_in[wbase + T];                        // right ghost: already a true value
+    }
+  }
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
     if (MODE == 2) {
@@ -367,18 +403,32 @@ extern "C" int fvm_spike_reduced_factor(int64_t n, int64_t P, const double* RL, 
 template <int TPB, int CPT>
 static int launch_tile_solve(int64_t n_tiles, int64_t P, const double* p, const double* q, const double* b,
                              const double* sep, const double* bfirst, int has_first, int64_t jl_last, double theta,
-                             const double* w_in, double* w_out, double* rs, int64_t w_stride, cudaStream_t s) {
+                             const double* w_in, double* w_out, double* rs, int64_t w_stride, cudaStream_t s,
+                             const fvm::LazyCorrection* lazy = nullptr) {
   dim3 grid((unsigned)n_tiles, (unsigned)P);
   const double cth = (1.0 - theta) / theta;
+  if (lazy) {
+    if (theta == 0.5)
+      fvm::tile_solve_kernel<TPB, CPT, 1, true><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
+                                                                   cth, w_in, w_out, rs, w_stride, *lazy);
+    else if (theta == 1.0)
+      fvm::tile_solve_kernel<TPB, CPT, 2, true><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
+                                                                   cth, w_in, w_out, rs, w_stride, *lazy);
+    else
+      fvm::tile_solve_kernel<TPB, CPT, 0, true><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
+                                                                   cth, w_in, w_out, rs, w_stride, *lazy);
+    return (int)cudaGetLastError();
+  }
+  const fvm::LazyCorrection none = {nullptr, nullptr, nullptr, 0, 0, 0, 0};
   if (theta == 0.5)
-    fvm::tile_solve_kernel<TPB, CPT, 1><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last, cth, w_in,
-                                                            w_out, rs, w_stride);
+    fvm::tile_solve_kernel<TPB, CPT, 1, false><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
+                                                                   cth, w_in, w_out, rs, w_stride, none);
   else if (theta == 1.0)
-    fvm::tile_solve_kernel<TPB, CPT, 2><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last, cth, w_in,
-                                                            w_out, rs, w_stride);
+    fvm::tile_solve_kernel<TPB, CPT, 2, false><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
+                                                                   cth, w_in, w_out, rs, w_stride, none);
   else
-    fvm::tile_solve_kernel<TPB, CPT, 0><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last, cth, w_in,
-                                                            w_out, rs, w_stride);
+    fvm::tile_solve_kernel<TPB, CPT, 0, false><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
+                                                                   cth, w_in, w_out, rs, w_stride, none);
   return (int)cudaGetLastError();
 }
 
@@ -431,6 +481,62 @@ extern "C" int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, co
   dim3 g((unsigned)((total + 255) / 256), (unsigned)P);
   fvm::correct_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(n_tiles, TPB, CPT, tl, tr, tile_offset, n_tiles_global, Vt,
                                                           Wt, xs, w, w_stride, next_first);
+  return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
+// Lazy correction: fvm_spike_local_lazy + fvm_spike_separators replace fvm_spike_local +
+// fvm_spike_finalize in a time loop.  The state buffer then holds the uncorrected tile solutions
+// between steps (true values at the separators and ghosts); fvm_spike_finalize materialises the true
+// state when it is needed (output, checkpoints).
+static void extent_threads(int config, const int32_t* extents_host, int& tl, int& tr) {
+  const int T = tile_cells(config), TPB = tile_threads(config), CPT = tile_cpt(config);
+  tl = (extents_host[0] + CPT - 1) / CPT;                  // whole threads' chunks from the left edge
+  tr = TPB - (T - 1 - extents_host[1]) / CPT;              // ... and from the right edge
+  if (tl > TPB) tl = TPB;
+  if (tr > TPB - tl) tr = TPB - tl;                        // the two ranges never overlap
+}
+
+extern "C" int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                                    const double* b, const double* sep, const double* bends,
+                                    int32_t has_first_cell, int64_t last_cell_local, double theta,
+                                    const double* w_in, double* w_out, int64_t w_stride, double* rs, double* rr,
+                                    int64_t rr_stride, double* g_first, const double* Vt, const double* Wt,
+                                    const double* xs, int64_t tile_offset, int64_t n_tiles_global,
+                                    const int32_t* extents_host, void* stream) {
+  if (!p || !q || !b || !sep || !bends || !w_in || !w_out || !rs || !rr || !g_first || !Vt || !Wt || !xs ||
+      !extents_host)
+    return FVM_ERR_INVALID_ARG;
+  if (n_tiles < 1 || P < 1 || P > 65535 || !(theta > 0.0 && theta <= 1.0)) return FVM_ERR_INVALID_ARG;
+  if (config < 0 || config >= kTileCfgs || n_tiles > 0x7fffffffLL) return FVM_ERR_INVALID_ARG;
+  const int T = tile_cells(config);
+  if (extents_host[0] < 0 || extents_host[1] < 0 || extents_host[0] > T - 1 || extents_host[1] > T - 1)
+    return FVM_ERR_INVALID_ARG;
+  fvm::LazyCorrection lz;
+  lz.Vt = Vt; lz.Wt = Wt; lz.xs = xs; lz.tile_offset = tile_offset; lz.n_tiles_global = n_tiles_global;
+  extent_threads(config, extents_host, lz.tl, lz.tr);
+  cudaStream_t s = (cudaStream_t)stream;
+  int st = config == 0
+               ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+                                            w_in, w_out, rs, w_stride, s, &lz)
+               : launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+                                          w_in, w_out, rs, w_stride, s, &lz);
+  if (st) return st;
+  dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
+  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,
+                                            rr, rr_stride, g_first);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_spike_separators(int64_t n_tiles, int64_t P, int32_t config, int64_t tile_offset,
+                                    int64_t n_tiles_global, const double* xs, double* w, int64_t w_stride,
+                                    const double* next_first, void* stream) {
+  if (!xs || !w || n_tiles < 1 || P < 1 || P > 65535) return FVM_ERR_INVALID_ARG;
+  if (config < 0 || config >= kTileCfgs) return FVM_ERR_INVALID_ARG;
+  dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
+  fvm::correct_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(n_tiles, tile_threads(config), tile_cpt(config), 0, 0,
+                                                          tile_offset, n_tiles_global, nullptr, nullptr, xs, w, w_stride,
+                                                          next_first);
   return (int)cudaGetLastError();
 }
 

@@ -89,7 +89,7 @@ class PartitionedAdvectionDiffusionModel(object):
     """
 
     def __init__(self, faces, a, d, k, discretisation="central", P=1, reaction=None, strict_bc=False,
-                 J=None, group=None, config=0, spike_tol=1e-30, device=None, hierarchical=True):
+                 J=None, group=None, config=0, spike_tol=1e-30, device=None, hierarchical=True, lazy=True):
         torch = _lib.require_cuda()
         lib = _lib.lib()
         if discretisation not in _lib.SCHEMES:
@@ -109,6 +109,8 @@ class PartitionedAdvectionDiffusionModel(object):
         self.P = int(P)
         self.discretisation, self.strict_bc, self.spike_tol = discretisation, strict_bc, float(spike_tol)
         self.hierarchical = bool(hierarchical)
+        self.lazy = bool(lazy)          # apply the spike correction inside the next step's tile solve
+        self._pending = False           # the current buffer holds uncorrected tile solutions
         plan = plan_partition(self.J, self.T, self.comm.world)
         self.nt = plan["tiles_per_rank"]
         self.nt_global = plan["tiles_global"]
@@ -339,6 +341,7 @@ class PartitionedAdvectionDiffusionModel(object):
             w = w[:, self.j0:self.j1]
         if w.shape[1] != n_real:
             raise ValueError("state has %d cells per problem, expected %d" % (w.shape[1], n_real))
+        self._pending = False
         buf = self._wbuf[0]
         buf.zero_()
         nat = torch.zeros((self.P, self.n_local), dtype=torch.float64, device=self.device)
@@ -357,8 +360,63 @@ class PartitionedAdvectionDiffusionModel(object):
 
     def get_state(self):
         """This rank's cells, (P, j1-j0)."""
+        self._materialise()
         til = self._wbuf[self._cur][:, 1:1 + self.n_local].view(self.P, self.nt, self.CPT, self.TPB)
         return til.transpose(2, 3).reshape(self.P, -1)[:, :self.j1 - self.j0].contiguous()
+
+    def _xs_index(self):
+        """(tensor, tile_offset, n_tiles_global) under which the separator values are addressed."""
+        if self.hier:
+            return self.xs_ext, 1, self.nt + 1
+        return self.xs, self.tile_offset, self.nt_global
+
+    def _materialise(self):
+        """Turn the current buffer into the true state if a lazy correction is pending."""
+        if not self._pending:
+            return
+        torch = _lib.require_cuda()
+        xs, off, ng = self._xs_index()
+        buf = self._wbuf[self._cur]
+        with torch.cuda.device(self.device):
+            # the separators and ghosts are already in place: only the interior correction is left
+            st = _lib.lib().fvm_spike_finalize(self.nt, self.P, self.config, self.extents, off, ng, _lib.ptr(self.Vt),
+                                               _lib.ptr(self.Wt), _lib.ptr(xs), ctypes.c_void_p(buf.data_ptr() + 8),
+                                               self.w_stride, _lib.ptr(self._ghost_right(buf)), _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_finalize")
+        self._pending = False
+
+    def _ghost_right(self, buf):
+        """The right ghost as a (P,) tensor (fvm_spike_finalize rewrites it with what it is given)."""
+        return buf[:, self.n_local + 1].contiguous()
+
+    def _local(self, w_in, w_out, wptr):
+        """Step, part 1 (tile solves + reduced right-hand side), with the pending correction applied on read."""
+        lib, P, nt, cfg, comm = _lib.lib(), self.P, self.nt, self.config, self.comm
+        common = (nt, P, cfg, _lib.ptr(self.p), _lib.ptr(self.q), _lib.ptr(self.b), _lib.ptr(self.sep),
+                  _lib.ptr(self.bends), int(comm.rank == 0), self._last_local, self._theta, wptr(w_in), wptr(w_out),
+                  self.w_stride, _lib.ptr(self.rs), _lib.ptr(self.rr), nt, _lib.ptr(self.g_first))
+        if self._pending:
+            xs, off, ng = self._xs_index()
+            st = lib.fvm_spike_local_lazy(*common, _lib.ptr(self.Vt), _lib.ptr(self.Wt), _lib.ptr(xs), off, ng,
+                                          self.extents, _lib.stream_ptr())
+            _lib.check(st, "fvm_spike_local_lazy")
+        else:
+            st = lib.fvm_spike_local(*common, _lib.stream_ptr())
+            _lib.check(st, "fvm_spike_local")
+
+    def _finalize(self, w_out, wptr, xs, off, ng, next_first):
+        """Step, part 3: separators and ghosts only when the correction is lazy, else the full correction."""
+        lib = _lib.lib()
+        if self.lazy:
+            st = lib.fvm_spike_separators(self.nt, self.P, self.config, off, ng, _lib.ptr(xs), wptr(w_out),
+                                          self.w_stride, _lib.ptr(next_first), _lib.stream_ptr())
+            _lib.check(st, "fvm_spike_separators")
+            self._pending = True
+        else:
+            st = lib.fvm_spike_finalize(self.nt, self.P, self.config, self.extents, off, ng, _lib.ptr(self.Vt),
+                                        _lib.ptr(self.Wt), _lib.ptr(xs), wptr(w_out), self.w_stride,
+                                        _lib.ptr(next_first), _lib.stream_ptr())
+            _lib.check(st, "fvm_spike_finalize")
 
     # ------------------------------------------------------------------ stepping
     def step(self, nsteps=1):
@@ -369,12 +427,7 @@ class PartitionedAdvectionDiffusionModel(object):
         with torch.cuda.device(self.device):
             for _ in range(int(nsteps)):
                 w_in, w_out = self._wbuf[self._cur], self._wbuf[1 - self._cur]
-                st = lib.fvm_spike_local(nt, P, cfg, _lib.ptr(self.p), _lib.ptr(self.q), _lib.ptr(self.b),
-                                         _lib.ptr(self.sep), _lib.ptr(self.bends), int(comm.rank == 0),
-                                         self._last_local, self._theta, wptr(w_in), wptr(w_out), self.w_stride,
-                                         _lib.ptr(self.rs), _lib.ptr(self.rr), nt, _lib.ptr(self.g_first),
-                                         _lib.stream_ptr())
-                _lib.check(st, "fvm_spike_local")
+                self._local(w_in, w_out, wptr)
                 next_first = None
                 if self.hier:
                     self._step_rank_level(w_out, wptr)
@@ -397,10 +450,7 @@ class PartitionedAdvectionDiffusionModel(object):
                     k1 = (comm.rank + 1) * nt                                               # next rank's first tile
                     next_first = (gf[comm.rank + 1] - self.V0_all[:, k1] * self.xs[:, k1 - 1]
                                   - self.W0_all[:, k1] * self.xs[:, k1]).contiguous()
-                st = lib.fvm_spike_finalize(nt, P, cfg, self.extents, self.tile_offset, self.nt_global,
-                                            _lib.ptr(self.Vt), _lib.ptr(self.Wt), _lib.ptr(self.xs), wptr(w_out),
-                                            self.w_stride, _lib.ptr(next_first), _lib.stream_ptr())
-                _lib.check(st, "fvm_spike_finalize")
+                self._finalize(w_out, wptr, self.xs, self.tile_offset, self.nt_global, next_first)
                 self._cur = 1 - self._cur
 
     def _step_rank_level(self, w_out, wptr):
@@ -417,10 +467,7 @@ class PartitionedAdvectionDiffusionModel(object):
                                     _lib.ptr(self.xs_ext), _lib.ptr(self.next_first), _lib.stream_ptr())
         _lib.check(st, "fvm_spike_rank_top")
         nf = self.next_first if comm.rank < comm.world - 1 else None
-        st = lib.fvm_spike_finalize(nt, P, self.config, self.extents, 1, nt + 1, _lib.ptr(self.Vt),
-                                    _lib.ptr(self.Wt), _lib.ptr(self.xs_ext), wptr(w_out), self.w_stride,
-                                    _lib.ptr(nf), _lib.stream_ptr())
-        _lib.check(st, "fvm_spike_finalize")
+        self._finalize(w_out, wptr, self.xs_ext, 1, nt + 1, nf)
 
     def run(self, w, theta, nsteps):
         """set_state + prepare + step; returns this rank's cells of the final state."""

@@ -211,6 +211,25 @@ int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, const int32_t
                        const double* Wt, const double* xs, double* w, int64_t w_stride,
                        const double* next_first, void* stream);
 
+/* Lazy correction for time loops: fvm_spike_local_lazy + fvm_spike_separators in place of
+ * fvm_spike_local + fvm_spike_finalize.  The state then holds the UNCORRECTED tile solutions between
+ * steps (true values only at the separators and in the ghosts, written by fvm_spike_separators), and
+ * the next step's tile solve applies  x = g - Vt xs(k-1) - Wt xs(k)  while it loads the tile (xs = the
+ * previous step's separator values, indexed like in fvm_spike_finalize).  This saves the separate
+ * correction pass: 16 B instead of 32 B of HBM traffic per corrected cell.  The FIRST step after a
+ * true state was stored uses fvm_spike_local; fvm_spike_finalize turns the buffer into the true
+ * state whenever it is needed. */
+int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                         const double* b, const double* sep, const double* bends,
+                         int32_t has_first_cell, int64_t last_cell_local, double theta,
+                         const double* w_in, double* w_out, int64_t w_stride, double* rs, double* rr,
+                         int64_t rr_stride, double* g_first, const double* Vt, const double* Wt,
+                         const double* xs, int64_t tile_offset, int64_t n_tiles_global,
+                         const int32_t* extents_host, void* stream);
+int fvm_spike_separators(int64_t n_tiles, int64_t P, int32_t config, int64_t tile_offset,
+                         int64_t n_tiles_global, const double* xs, double* w, int64_t w_stride,
+                         const double* next_first, void* stream);
+
 /* Rank-level SPIKE over the separator system (cells split over GPUs; no counterpart in the
  * reference, which is single-process).  Each rank solves the block of its own nt tile separators
  * with fvm_spike_reduce_solve (couplings to the neighbouring ranks cut, its last separator
