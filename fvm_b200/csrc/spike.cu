@@ -20,7 +20,11 @@
 //     (host, multi-GPU)       all-gather of rr over the ranks (NCCL), nT doubles per rank
 //     reduced_solve_kernel  : Thomas on the factored separator system, one CTA, affine scans
 //     correct_kernel        : x = g - Vt xs(k-1) - Wt xs(k), only over the extent where a spike
-//                             exceeds `spike_tol` (spikes decay away from the tile edges)
+//                             exceeds `spike_tol` (spikes decay away from the tile edges).  In a
+//                             time loop this pass is skipped: the next step's tile_solve_kernel
+//                             applies the correction while it loads the tile (LAZY), and only the
+//                             separators and ghosts are written between steps.
+//   multi-GPU, rank level   : rank_pack_kernel / rank_top_kernel around ONE all-gather per step
 //
 // All indices are LOCAL to the rank's slab unless they say "global"; the slab starts at global
 // cell j_offset = tile_offset*T.  State arrays carry one ghost cell on each side
