@@ -275,3 +275,35 @@ def test_theta_zero_explicit_euler():
             asm = O.assemble(f, a[p], d[p], "upwind", **bc)
             want = O.theta_run_scipy(asm, k[p], 0.0, w0[p], 40, every=20)
             assert step_error(ck[:, p], want, np.max(np.abs(w0[p]))) < 1e-12
+
+
+@pytest.mark.parametrize("J,variant", [(300, "fused"), (1000, "fused"), (1024, "fused"), (3000, "fused"),
+                                       (8192, "fused"), (777, "thomas")])
+def test_no_stray_writes_around_state_and_checkpoints(J, variant):
+    """compute-sanitizer is closed on this GPU pool, so out-of-bounds WRITES are looked for directly:
+    the state and the checkpoint buffers sit inside larger allocations filled with a sentinel, and the
+    guard bands must be untouched after a run (ragged P so that idle warps / CTAs exist)."""
+    from fvm_b200 import _lib
+    P, G, sentinel = 11, 4096, 12345.678
+    f = W.graded_faces(J, 10.0)
+    h = np.diff(f)
+    rng = np.random.default_rng(J)
+    a = rng.uniform(0.5, 2.0, P); d = a * h.max() / rng.uniform(0.3, 1.5, P); k = rng.uniform(1, 4, P) * h.min()
+    m = BatchedAdvectionDiffusionModel(f, a, d, k, "exponential")
+    m.set_boundary_conditions(left_flux=0.1, right_flux=-0.1)
+    n_ck = 3
+    big_w = torch.full((P * J + 2 * G,), sentinel, dtype=torch.float64, device="cuda")
+    big_c = torch.full((n_ck * P * J + 2 * G,), sentinel, dtype=torch.float64, device="cuda")
+    w = big_w[G:G + P * J].view(P, J)
+    ck = big_c[G:G + n_ck * P * J].view(n_ck, P, J)
+    w.copy_(torch.as_tensor(rng.random((P, J)) + 0.1, device="cuda"))
+    if variant == "fused":
+        m.run_fused_(w, 0.5, 3 * 5, 5, ck)
+        assert bool(torch.isfinite(ck).all()) and bool((ck != sentinel).all())
+    else:
+        w_t = big_w[G:G + P * J].view(J, P)               # interleaved state in the same guarded buffer
+        m.step_thomas_(w_t, 0.5, 15)
+    torch.cuda.synchronize()
+    assert bool(torch.isfinite(w).all())
+    for big, n in ((big_w, P * J), (big_c, n_ck * P * J)):
+        assert bool((big[:G] == sentinel).all()) and bool((big[G + n:] == sentinel).all())
