@@ -254,12 +254,12 @@ def run_partitioned(args):
                "Crank-Nicolson, dt = 4 h_min/a, SPIKE reduced system all-gathered over NCCL each step" % (world, J, world)
     else:
         inner = 10 if args.inner == 1000 else args.inner
-        Pn, J = 256, 1 << 20
+        Pn, J = 512, 1 << 20
         wl = W.stiff_reaction(P=world * Pn, J=J, first=rank * Pn, count=Pn)
         m = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=Pn,
                                                reaction=wl["reaction"], device=dev)
         theta, w0, cells_rank = 1.0, torch.as_tensor(wl["w0"], device=dev), Pn * J
-        desc = "cfg4 stiff reaction-diffusion: %d problems/GPU x 2^20 cells (BASELINE's 4,096 do not fit one GPU), " \
+        desc = "cfg4 stiff reaction-diffusion: %d problems/GPU x 2^20 cells (BASELINE: 4,096 problems = 512 per GPU on 8 GPUs), " \
                "per-problem a/d/reaction, theta = 1, dt = 100 h_min/a" % Pn
     m.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
     m.prepare(theta)
