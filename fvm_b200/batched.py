@@ -126,6 +126,7 @@ class BatchedAdvectionDiffusionModel(object):
         self._asm = None
         self._factors = {}
         self._pr = None
+        self._part_theta = None
 
     def _problem(self):
         if getattr(self, "_pr", None) is not None:
@@ -264,7 +265,9 @@ class BatchedAdvectionDiffusionModel(object):
         """Advance w (P, J) by ``nsteps`` theta steps; returns (w_final, checkpoints or None).
         Equivalent of the loop  d = (I + k*(1-theta)*alpha*M)*w + beta ; w = spsolve(A, d)
         (fvm_classes.py:408-411) for every problem of the batch.
-        variant: 'fused' (on-chip, J <= fused_max_cells), 'thomas' (streaming), or 'auto'."""
+        variant: 'fused' (on-chip, J <= fused_max_cells), 'thomas' (streaming, one thread per
+        system), 'partitioned' (variant 3 on this GPU: few long systems), or 'auto' (fused when
+        it fits, else thomas for batches of at least THOMAS_MIN_PROBLEMS, else partitioned)."""
         torch = _lib.require_cuda()
         w = self._dev(w).reshape(self.P, self.J).clone()
         nsteps = int(nsteps)
@@ -274,9 +277,11 @@ class BatchedAdvectionDiffusionModel(object):
         if float(theta) == 0.0:
             return self._run_explicit(w, nsteps, ce, ckpt), ckpt
         if variant == "auto":
-            variant = "fused" if self.J <= int(_lib.lib().fvm_fused_max_cells()) else "thomas"
+            variant = self._auto_variant()
         if variant == "fused":
             self.run_fused_(w, theta, nsteps, ce, ckpt)
+        elif variant == "partitioned":
+            w = self._run_partitioned(w, theta, nsteps, ce, ckpt)
         elif variant == "thomas":
             w_t = w.t().contiguous()
             if n_ck:
@@ -290,8 +295,47 @@ class BatchedAdvectionDiffusionModel(object):
                 self.step_thomas_(w_t, theta, nsteps)
             w = w_t.t().contiguous()
         else:
-            raise ValueError("variant must be 'auto', 'fused' or 'thomas'")
+            raise ValueError("variant must be 'auto', 'fused', 'thomas' or 'partitioned'")
         return w, ckpt
+
+    # a batch this wide fills the GPU with one thread per system; below it, long systems go to variant 3
+    THOMAS_MIN_PROBLEMS = 16384
+
+    def _auto_variant(self):
+        if self.J <= int(_lib.lib().fvm_fused_max_cells()):
+            return "fused"
+        return "thomas" if self.P >= self.THOMAS_MIN_PROBLEMS else "partitioned"
+
+    def _run_partitioned(self, w, theta, nsteps, ce, ckpt):
+        """Variant 3 on this GPU alone (PartitionedAdvectionDiffusionModel with no process group)."""
+        from .partitioned import PartitionedAdvectionDiffusionModel
+        key = float(theta)
+        m = getattr(self, "_part", None)
+        if m is None:
+            def glob(t, strides):          # back to the shape the constructor classifies
+                if t is None:
+                    return None
+                return t.reshape(()) if strides == (0, 0) else t
+            m = PartitionedAdvectionDiffusionModel(
+                self.faces, glob(self.a, self._a_str), glob(self.d, self._d_str), self.k, self.discretisation,
+                P=self.P, reaction=glob(self.reaction, self._r_str), strict_bc=self.strict_bc, device=self.device)
+            self._part, self._part_theta = m, None
+        if not hasattr(self, "left_flux"):
+            raise AttributeError("boundary conditions are not set: call set_boundary_conditions first")
+        if self._part_theta != key:
+            m.set_boundary_conditions(self.left_flux, self.right_flux, self.left_value, self.right_value)
+            m.prepare(theta)
+            self._part_theta = key
+        m.set_state(w)
+        done = 0
+        if ce > 0 and ckpt is not None:
+            for i in range(ckpt.shape[0]):
+                m.step(ce)
+                ckpt[i].copy_(m.get_state())
+                done += ce
+        if nsteps - done:
+            m.step(nsteps - done)
+        return m.get_state()
 
     def _run_explicit(self, w, nsteps, ce, ckpt):
         """theta = 0: A = I, a step is w <- (I + k*alpha*M) w + beta (fvm_explicit_step)."""
@@ -332,8 +376,13 @@ class BatchedAdvectionDiffusionModel(object):
         elif isinstance(out, np.ndarray):
             out = torch.from_numpy(out)
         if variant == "auto":
-            variant = "fused" if self.J <= int(_lib.lib().fvm_fused_max_cells()) else "thomas"
+            variant = self._auto_variant()
         with torch.cuda.device(self.device):
+            if variant == "partitioned":
+                self._stage.copy_(w_host, non_blocking=True)
+                out.copy_(self._run_partitioned(self._stage, theta, int(nsteps), 0, None), non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                return out
             if variant != "fused":
                 self._stage.copy_(w_host, non_blocking=True)
                 w_t = self._stage.t().contiguous()

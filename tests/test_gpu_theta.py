@@ -307,3 +307,55 @@ def test_no_stray_writes_around_state_and_checkpoints(J, variant):
     assert bool(torch.isfinite(w).all())
     for big, n in ((big_w, P * J), (big_c, n_ck * P * J)):
         assert bool((big[:G] == sentinel).all()) and bool((big[G + n:] == sentinel).all())
+
+
+@pytest.mark.parametrize("scheme", ["central", "exponential"])
+def test_auto_routes_few_long_systems_to_variant3(scheme):
+    """J above the fused maximum with a small batch: 'auto' takes the partitioned solver on
+    this GPU, and it agrees with the thread-per-system kernel and with the oracle -- per-cell
+    coefficients, per-problem time step, checkpoints and the host-buffer call included."""
+    J, P, n = 20000, 3, 12
+    f = W.graded_faces(J)
+    rng = np.random.default_rng(7)
+    a = rng.uniform(0.2, 1.0, (P, J))
+    d = 2e-3 * (1.0 + 0.5 * np.sin(np.linspace(0, 9, J)))
+    k = np.array([0.01, 0.004, 0.02])
+    cells = 0.5 * (f[1:] + f[:-1])
+    w0 = np.stack([np.exp(-((cells - c) / 0.05) ** 2) for c in (0.3, 0.5, 0.7)])
+    bc = dict(left_flux=0.1, right_flux=0.0)
+    m = BatchedAdvectionDiffusionModel(f, a, d, k, scheme)
+    m.set_boundary_conditions(**bc)
+    assert m._auto_variant() == "partitioned"
+    w_auto, ck = m.run(w0, 0.5, n, checkpoint_every=4)
+    w_th, ck_th = m.run(w0, 0.5, n, checkpoint_every=4, variant="thomas")
+    assert ck.shape == (3, P, J)
+    scale = np.max(np.abs(w0))
+    assert step_error(ck.cpu().numpy().reshape(3, -1), ck_th.cpu().numpy().reshape(3, -1), scale) < TOL
+    for p in range(P):
+        asm = O.assemble(f, a[p], d, scheme, **bc)
+        want = O.theta_run_scipy(asm, k[p], 0.5, w0[p], n, every=n)
+        assert step_error(w_auto[p].cpu().numpy()[None], want, scale) < TOL, p
+    out = m.run_host(w0, 0.5, n)
+    assert np.array_equal(out.numpy(), w_auto.cpu().numpy())
+    # a new boundary condition must not reuse the old factors
+    m.set_boundary_conditions(left_value=1.0, right_value=0.0)
+    w2, _ = m.run(w0, 0.5, n)
+    w2_th, _ = m.run(w0, 0.5, n, variant="thomas")
+    assert step_error(w2.cpu().numpy(), w2_th.cpu().numpy(), scale) < TOL
+    assert not np.array_equal(w2.cpu().numpy(), w_auto.cpu().numpy())
+
+
+def test_single_long_model_through_reference_classes():
+    """AdvectionDiffusionModel.theta_run with J = 50,000 (one system: variant 3 on this GPU)."""
+    from fvm_b200 import AdvectionDiffusionModel, CellVariable, Mesh
+    J = 50000
+    mesh = Mesh(W.graded_faces(J))
+    a, d = CellVariable(1.0, mesh=mesh), CellVariable(1e-3, mesh=mesh)
+    model = AdvectionDiffusionModel(mesh.faces, a, d, 0.01, discretisation="upwind")
+    model.set_boundary_conditions(left_value=1.0, right_value=0.0)
+    w0 = W.pulse(mesh.cells)
+    w0[0], w0[-1] = 1.0, 0.0
+    w = model.theta_run(w0, 1.0, 20)
+    asm = O.assemble(mesh.faces, 1.0, 1e-3, "upwind", left_value=1.0, right_value=0.0)
+    want = O.theta_run_scipy(asm, 0.01, 1.0, w0, 20, every=20)
+    assert step_error(np.asarray(w)[None], want, np.max(np.abs(w0))) < TOL
