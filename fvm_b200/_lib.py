@@ -56,6 +56,10 @@ _SIGNATURES = {
                                         c_ptr, c_ptr, c_ptr]),
     "fvm_theta_step_thomas": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_dbl,
                                              c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr]),
+    "fvm_theta_step_thomas_tv": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_dbl,
+                                                c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr]),
+    "fvm_state_compare": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i64, c_i64,
+                                         c_ptr, c_ptr]),
     "fvm_explicit_step": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i32, c_i32,
                                          c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr]),
     "fvm_mesh_check": (ctypes.c_int, [c_ptr, c_i64, c_ptr, c_ptr]),

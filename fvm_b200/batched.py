@@ -127,6 +127,7 @@ class BatchedAdvectionDiffusionModel(object):
         self._factors = {}
         self._pr = None
         self._part_theta = None
+        self._unit = None
 
     def _problem(self):
         if getattr(self, "_pr", None) is not None:
@@ -336,6 +337,99 @@ class BatchedAdvectionDiffusionModel(object):
         if nsteps - done:
             m.step(nsteps - done)
         return m.get_state()
+
+    # ------------------------------------------------------------------ time-varying boundary data
+    def run_time_varying(self, w, theta, left_flux_t=None, right_flux_t=None, checkpoint_every=0):
+        """Theta steps with boundary fluxes that change from step to step: step n uses
+        ``left_flux_t[n]`` / ``right_flux_t[n]`` (shape (nsteps,) or (nsteps, P)) in beta; an end
+        without a history keeps the flux of set_boundary_conditions.  NOT in the reference
+        (constant beta; fvm_classes.py:221,228 only mention the case) -- SURVEY.md 8(f)2.  Runs on
+        variant 1 (fvm_theta_step_thomas_tv).  Returns (w_final, checkpoints or None)."""
+        torch = _lib.require_cuda()
+        if not hasattr(self, "left_flux"):
+            raise AttributeError("boundary conditions are not set: call set_boundary_conditions first")
+        if left_flux_t is None and right_flux_t is None:
+            raise ValueError("give left_flux_t and/or right_flux_t (otherwise use run)")
+        if not (0.0 < float(theta) <= 1.0):
+            raise ValueError("theta must be in (0, 1] for the time-varying run")
+        lk, rk = _bc_kinds(self.left_flux, self.right_flux, self.left_value, self.right_value)
+        if (left_flux_t is not None and lk != _lib.BC_ROBIN) or (right_flux_t is not None and rk != _lib.BC_ROBIN):
+            raise ValueError("a flux history needs a flux (Robin) boundary at that end")
+
+        def hist(x):
+            if x is None:
+                return None
+            t = self._dev(x)
+            if t.ndim == 1:
+                t = t[:, None].expand(t.shape[0], self.P)
+            if t.ndim != 2 or t.shape[1] != self.P:
+                raise ValueError("a flux history must have shape (nsteps,) or (nsteps, P)")
+            return t.contiguous()
+        sl, sr = hist(left_flux_t), hist(right_flux_t)
+        nsteps = int((sl if sl is not None else sr).shape[0])
+        if sl is not None and sr is not None and sl.shape[0] != sr.shape[0]:
+            raise ValueError("the two flux histories must have the same number of steps")
+        # beta is linear in the flux: factor once for a unit flux at the varying ends
+        key = (sl is not None, sr is not None)
+        if getattr(self, "_unit", None) is None or self._unit[0] != key:
+            twin = BatchedAdvectionDiffusionModel.__new__(BatchedAdvectionDiffusionModel)
+            twin.__dict__.update({k_: v for k_, v in self.__dict__.items() if k_ not in ("_unit", "_part", "_stage")})
+            twin.set_boundary_conditions(left_flux=1.0 if sl is not None else self.left_flux,
+                                         right_flux=1.0 if sr is not None else self.right_flux,
+                                         left_value=self.left_value, right_value=self.right_value)
+            self._unit = (key, twin)
+        f = self._unit[1].factor(theta)
+        w_t = self._dev(w).reshape(self.P, self.J).t().contiguous()
+        ce = int(checkpoint_every or 0)
+        n_ck = nsteps // ce if ce > 0 else 0
+        ckpt = torch.empty((n_ck, self.P, self.J), dtype=torch.float64, device=self.device) if n_ck else None
+        segments = [ce] * n_ck + ([nsteps - n_ck * ce] if nsteps - n_ck * ce else [])
+        done = 0
+        with torch.cuda.device(self.device):
+            for i, n in enumerate(segments):
+                off = done * self.P * 8
+                st = _lib.lib().fvm_theta_step_thomas_tv(
+                    self.J, self.P, _lib.ptr(f["fp"]), _lib.ptr(f["fq"]), _lib.ptr(f["fb"]), 1, self.P, float(theta),
+                    _lib.ptr(f["bt_left"]), _lib.ptr(f["bt_right"]),
+                    ctypes.c_void_p(sl.data_ptr() + off) if sl is not None else None,
+                    ctypes.c_void_p(sr.data_ptr() + off) if sr is not None else None,
+                    _lib.ptr(w_t), 1, self.P, int(n), _lib.stream_ptr())
+                _lib.check(st, "fvm_theta_step_thomas_tv")
+                done += n
+                if i < n_ck:
+                    ckpt[i].copy_(w_t.t())
+        return w_t.t().contiguous(), ckpt
+
+    # ------------------------------------------------------------------ distances between states
+    def compare(self, w_a, w_b):
+        """Per problem, on the device (fvm_state_compare): max |a - b|, sum |a - b| h, max |b| and
+        sum b h.  Used for steady-state detection and for the comparison with an analytic
+        solution (fvm_examples.py:71)."""
+        torch = _lib.require_cuda()
+        a = self._dev(w_a).reshape(self.P, self.J).contiguous()
+        b = self._dev(w_b).reshape(self.P, self.J).contiguous()
+        out = torch.empty((self.P, 4), dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            st = _lib.lib().fvm_state_compare(self.J, self.P, _lib.ptr(self.faces), _lib.ptr(a), self.J, 1,
+                                              _lib.ptr(b), self.J, 1, _lib.ptr(out), _lib.stream_ptr())
+        _lib.check(st, "fvm_state_compare")
+        return dict(max_abs_diff=out[:, 0], l1_diff=out[:, 1], max_abs_ref=out[:, 2], area_ref=out[:, 3])
+
+    def run_until_steady(self, w, theta, tol=1e-9, check_every=100, max_steps=1000000, variant="auto"):
+        """Advance in blocks of ``check_every`` steps until, for every problem,
+        max |w_n - w_{n-check_every}| <= tol * max(|w_{n-check_every}|) (or max_steps is reached).
+        Returns (w, steps taken, per-problem relative change of the last block)."""
+        torch = _lib.require_cuda()
+        w = self._dev(w).reshape(self.P, self.J)
+        steps, rel = 0, None
+        while steps < int(max_steps):
+            w_new, _ = self.run(w, theta, int(check_every), variant=variant)
+            c = self.compare(w_new, w)
+            rel = c["max_abs_diff"] / torch.clamp(c["max_abs_ref"], min=1e-300)
+            w, steps = w_new, steps + int(check_every)
+            if bool((rel <= tol).all()):               # one small device->host read per block
+                break
+        return w, steps, rel
 
     def _run_explicit(self, w, nsteps, ce, ckpt):
         """theta = 0: A = I, a step is w <- (I + k*alpha*M) w + beta (fvm_explicit_step)."""

@@ -188,18 +188,39 @@ class AdvectionDiffusionModel(object):
         return dia_matrix(sparse.diags([lo[1:], di, up[:-1]], [-1, 0, 1], shape=(J, J)))
 
     # -------------------------------------------------------------- accelerated time loop
-    def theta_run(self, w_init, theta, nsteps, checkpoint_every=0, variant="auto"):
+    def theta_run(self, w_init, theta, nsteps, checkpoint_every=0, variant="auto", save=None):
         """``nsteps`` steps of  A w_new = B w + beta  (fvm_classes.py:373-377,408-411) on the
         GPU.  Returns the final state (J,), or (final, checkpoints (n, J)) when
-        ``checkpoint_every`` > 0."""
+        ``checkpoint_every`` > 0.  ``save``: path of a .npy file that receives the checkpoints
+        (the final state when there are none) -- the headless stand-in for the demo's movie
+        writer, which grabs a frame per step (fvm_classes.py:406-422)."""
         if not hasattr(self, "left_flux"):
             raise AttributeError("call set_boundary_conditions first")
         w, ck = self._gpu.run(np.asarray(w_init, dtype=float)[None, :], theta, nsteps,
                               checkpoint_every, variant)
         w = w[0].cpu().numpy()
+        snaps = ck[:, 0].cpu().numpy() if checkpoint_every else None
+        if save is not None:
+            np.save(save, snaps if snaps is not None else w[None, :])
         if checkpoint_every:
-            return w, ck[:, 0].cpu().numpy()
+            return w, snaps
         return w
+
+    def theta_run_until_steady(self, w_init, theta, tol=1e-9, check_every=100, max_steps=1000000):
+        """Step until max|w_n - w_{n-check_every}| <= tol max|w| ; returns (w, steps taken)."""
+        if not hasattr(self, "left_flux"):
+            raise AttributeError("call set_boundary_conditions first")
+        w, steps, _ = self._gpu.run_until_steady(np.asarray(w_init, dtype=float)[None, :], theta, tol,
+                                                 check_every, max_steps)
+        return w[0].cpu().numpy(), steps
+
+    def theta_run_time_varying(self, w_init, theta, left_flux_t=None, right_flux_t=None, checkpoint_every=0):
+        """Theta steps with per-step boundary fluxes (not in the reference; see
+        BatchedAdvectionDiffusionModel.run_time_varying)."""
+        w, ck = self._gpu.run_time_varying(np.asarray(w_init, dtype=float)[None, :], theta, left_flux_t,
+                                           right_flux_t, checkpoint_every)
+        w = w[0].cpu().numpy()
+        return (w, ck[:, 0].cpu().numpy()) if checkpoint_every else w
 
 
 class Model(AdvectionDiffusionModel):

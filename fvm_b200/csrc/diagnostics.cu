@@ -85,3 +85,54 @@ extern "C" int fvm_mesh_check(const double* faces, int64_t n_cells, uint64_t* co
                                                                              (unsigned long long*)counts);
   return (int)cudaGetLastError();
 }
+
+// Distance between two states of a batch on the same mesh: the measure behind steady-state
+// detection (w_n against w_{n-m}) and behind the comparison with an analytic solution that the
+// example driver plots (fvm_examples.py:71).  out[p*4 + 0..3] = max_j |a_j - b_j|,
+// sum_j |a_j - b_j| h_j, max_j |b_j|, sum_j b_j h_j.  One warp per problem; the result is
+// deterministic (fixed strided order, shuffle tree).
+namespace fvm {
+__global__ void __launch_bounds__(256) state_compare_kernel(int64_t J, int64_t P, const double* __restrict__ faces,
+                                                            const double* __restrict__ a, int64_t a_ps, int64_t a_cs,
+                                                            const double* __restrict__ b, int64_t b_ps, int64_t b_cs,
+                                                            double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int64_t p = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (p >= P) return;
+  double dmax = 0.0, dl1 = 0.0, bmax = 0.0, bmass = 0.0;
+  bool bad = false;
+  for (int64_t j = lane; j < J; j += 32) {
+    const double h = sub(faces[j + 1], faces[j]);
+    const double av = a[p * a_ps + j * a_cs], bv = b[p * b_ps + j * b_cs];
+    const double e = fabs(sub(av, bv));
+    bad |= !(e == e);                              // fmax would drop a NaN: carry it explicitly
+    dmax = fmax(dmax, e);
+    dl1 = fma(e, h, dl1);
+    bmax = fmax(bmax, fabs(bv));
+    bmass = fma(bv, h, bmass);
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, s));
+    dl1 += __shfl_xor_sync(0xffffffffu, dl1, s);
+    bmax = fmax(bmax, __shfl_xor_sync(0xffffffffu, bmax, s));
+    bmass += __shfl_xor_sync(0xffffffffu, bmass, s);
+  }
+  bad = __any_sync(0xffffffffu, bad);
+  if (lane == 0) {
+    double* o = out + p * 4;
+    o[0] = bad ? NAN : dmax; o[1] = dl1; o[2] = bmax; o[3] = bmass;
+  }
+}
+}  // namespace fvm
+
+extern "C" int fvm_state_compare(int64_t J, int64_t P, const double* faces, const double* a, int64_t a_ps,
+                                 int64_t a_cs, const double* b, int64_t b_ps, int64_t b_cs, double* out,
+                                 void* stream) {
+  if (!faces || !a || !b || !out || J < 1 || P < 1) return FVM_ERR_INVALID_ARG;
+  const int64_t blocks = (P + 7) / 8;
+  if (blocks > 0x7fffffffLL) return FVM_ERR_UNSUPPORTED;
+  fvm::state_compare_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(J, P, faces, a, a_ps, a_cs, b, b_ps,
+                                                                                b_cs, out);
+  return (int)cudaGetLastError();
+}

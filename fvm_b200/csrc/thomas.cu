@@ -12,22 +12,31 @@
 
 namespace fvm {
 
-template <int U>
+// TV: time-varying boundary data.  The boundary term of step s is bt_left[p] * scale_left[s*P + p]
+// (likewise on the right): beta is linear in the boundary flux (fvm_classes.py:244-263), so the
+// caller passes the factors of a unit flux and the flux history as the scales.
+template <int U, bool TV>
 __global__ void __launch_bounds__(128) thomas_steps_kernel(
     int64_t J, int64_t P, const double* __restrict__ fp, const double* __restrict__ fq,
     const double* __restrict__ fb, int64_t f_ps, int64_t f_cs, double cth,
     const double* __restrict__ bt_left, const double* __restrict__ bt_right, double* w,
-    int64_t w_ps, int64_t w_cs, int64_t nsteps) {
+    int64_t w_ps, int64_t w_cs, int64_t nsteps, const double* __restrict__ scale_left,
+    const double* __restrict__ scale_right) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
   const double* P_ = fp + p * f_ps;
   const double* Q_ = fq + p * f_ps;
   const double* B_ = fb + p * f_ps;
   double* W_ = w + p * w_ps;
-  const double bl = bt_left ? bt_left[p] : 0.0;
-  const double br = bt_right ? bt_right[p] : 0.0;
+  const double bl0 = bt_left ? bt_left[p] : 0.0;
+  const double br0 = bt_right ? bt_right[p] : 0.0;
 
   for (int64_t s = 0; s < nsteps; ++s) {
+    double bl = bl0, br = br0;
+    if (TV) {
+      if (scale_left) bl *= scale_left[s * P + p];
+      if (scale_right) br *= scale_right[s * P + p];
+    }
     // forward: r~_j = fb_j w_j - c (fp_j w_{j-1} + fq_j w_{j+1}) ; g_j = r~_j - fp_j g_{j-1}
     double wm = 0.0, w0 = W_[0], g = 0.0;
     int64_t j = 0;
@@ -88,7 +97,24 @@ extern "C" int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, con
   const int64_t blocks = (P + 127) / 128;
   if (blocks > 0x7fffffffLL) return FVM_ERR_UNSUPPORTED;
   const double cth = (1.0 - theta) / theta;
-  fvm::thomas_steps_kernel<8><<<(unsigned)blocks, 128, 0, (cudaStream_t)stream>>>(
-      J, P, fp, fq, fb, f_ps, f_cs, cth, bt_left, bt_right, w, w_ps, w_cs, nsteps);
+  fvm::thomas_steps_kernel<8, false><<<(unsigned)blocks, 128, 0, (cudaStream_t)stream>>>(
+      J, P, fp, fq, fb, f_ps, f_cs, cth, bt_left, bt_right, w, w_ps, w_cs, nsteps, nullptr, nullptr);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_theta_step_thomas_tv(int64_t J, int64_t P, const double* fp, const double* fq,
+                                        const double* fb, int64_t f_ps, int64_t f_cs, double theta,
+                                        const double* bt_left, const double* bt_right,
+                                        const double* scale_left, const double* scale_right, double* w,
+                                        int64_t w_ps, int64_t w_cs, int64_t nsteps, void* stream) {
+  if (!fp || !fq || !fb || !w) return FVM_ERR_INVALID_ARG;
+  if (J < 3 || P < 1 || nsteps < 0 || !(theta > 0.0 && theta <= 1.0)) return FVM_ERR_INVALID_ARG;
+  if ((scale_left && !bt_left) || (scale_right && !bt_right)) return FVM_ERR_INVALID_ARG;
+  if (nsteps == 0) return FVM_OK;
+  const int64_t blocks = (P + 127) / 128;
+  if (blocks > 0x7fffffffLL) return FVM_ERR_UNSUPPORTED;
+  const double cth = (1.0 - theta) / theta;
+  fvm::thomas_steps_kernel<8, true><<<(unsigned)blocks, 128, 0, (cudaStream_t)stream>>>(
+      J, P, fp, fq, fb, f_ps, f_cs, cth, bt_left, bt_right, w, w_ps, w_cs, nsteps, scale_left, scale_right);
   return (int)cudaGetLastError();
 }

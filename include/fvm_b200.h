@@ -111,6 +111,19 @@ int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, const double* 
                           const double* bt_left, const double* bt_right, double* w, int64_t w_ps,
                           int64_t w_cs, int64_t nsteps, void* stream);
 
+/* Variant 1 with TIME-VARYING boundary fluxes.  No counterpart in the reference, whose beta is
+ * constant in time; fvm_classes.py:221,228 ("unless BCs are time varying") only hints at it
+ * (SURVEY.md 8(f)2).  Step s (0-based) uses  beta_left * scale_left[s*P + p]  and
+ * beta_right * scale_right[s*P + p]:  beta is linear in the boundary flux [fvm_classes.py:
+ * 244-263], so with bt_left/bt_right factored for a UNIT flux the scales are the flux values at
+ * step s.  A NULL scale array leaves that end constant (scale 1).  Everything else as in
+ * fvm_theta_step_thomas. */
+int fvm_theta_step_thomas_tv(int64_t J, int64_t P, const double* fp, const double* fq,
+                             const double* fb, int64_t f_ps, int64_t f_cs, double theta,
+                             const double* bt_left, const double* bt_right,
+                             const double* scale_left, const double* scale_right, double* w,
+                             int64_t w_ps, int64_t w_cs, int64_t nsteps, void* stream);
+
 /* theta = 0 (explicit Euler, A = I): one step  w_out = (I + dt*alpha*M) w_in + beta  of the same
  * loop [fvm_classes.py:408-411 with theta = 0 at :376-377].  M diagonals from fvm_assemble
  * (strides m_ps, m_cs); w_in and w_out must be different buffers with strides (w_ps, w_cs);
@@ -134,6 +147,14 @@ int fvm_diagnostics(const fvm_problem* prob, const double* dt, const double* w, 
  * which the reference accepts) among the n_cells cells of faces[0..n_cells].  counts: two device
  * uint64, cleared by the caller. */
 int fvm_mesh_check(const double* faces, int64_t n_cells, uint64_t* counts, void* stream);
+
+/* Distance between two states a and b of a batch on one mesh (steady-state detection: w_n
+ * against an earlier w; comparison with an analytic solution, fvm_examples.py:71).
+ * out[p*4 + 0..3] = max_j |a_j - b_j| (NaN if any difference is NaN), sum_j |a_j - b_j| h_j,
+ * max_j |b_j|, sum_j b_j h_j.  a and b strided like every state array. */
+int fvm_state_compare(int64_t J, int64_t P, const double* faces, const double* a, int64_t a_ps,
+                      int64_t a_cs, const double* b, int64_t b_ps, int64_t b_cs, double* out,
+                      void* stream);
 
 /* Largest J the fused on-chip variant accepts. */
 int64_t fvm_fused_max_cells(void);
