@@ -400,6 +400,46 @@ class BatchedAdvectionDiffusionModel(object):
                     ckpt[i].copy_(w_t.t())
         return w_t.t().contiguous(), ckpt
 
+    def run_variable_dt(self, w, theta, dt_t, checkpoint_every=0):
+        """Theta steps whose time step changes: step n uses ``dt_t[n]`` (shape (nsteps,) or
+        (nsteps, P)) in place of the constructor's k.  NOT in the reference (one k per model,
+        fvm_classes.py:92,351) -- SURVEY.md 8(f)2.  Variant 1: the operators are re-factored
+        (fvm_theta_factor, one pass over the assembled diagonals) whenever the time step differs
+        from the previous step's; runs of equal steps share a factorisation and a launch."""
+        torch = _lib.require_cuda()
+        if not (0.0 < float(theta) <= 1.0):
+            raise ValueError("theta must be in (0, 1] for the variable-step run")
+        dt = self._dev(dt_t)
+        if dt.ndim == 1:
+            dt = dt[:, None].expand(dt.shape[0], self.P)
+        if dt.ndim != 2 or dt.shape[1] != self.P:
+            raise ValueError("the time-step history must have shape (nsteps,) or (nsteps, P)")
+        dt = dt.contiguous()
+        nsteps = int(dt.shape[0])
+        # boundaries of the runs of identical rows, found on the device (one small read back)
+        change = torch.ones(nsteps, dtype=torch.bool, device=self.device)
+        if nsteps > 1:
+            change[1:] = (dt[1:] != dt[:-1]).any(dim=1)
+        starts = [int(i) for i in torch.nonzero(change).flatten().cpu()] + [nsteps]
+        w_t = self._dev(w).reshape(self.P, self.J).t().contiguous()
+        ce = int(checkpoint_every or 0)
+        n_ck = nsteps // ce if ce > 0 else 0
+        ckpt = torch.empty((n_ck, self.P, self.J), dtype=torch.float64, device=self.device) if n_ck else None
+        k_saved, f_saved = self.k, self._factors
+        try:
+            for s0, s1 in zip(starts[:-1], starts[1:]):
+                self.k, self._factors = dt[s0], {}
+                n = s0
+                while n < s1:                         # cut the run at the checkpoints
+                    stop = min(s1, (n // ce + 1) * ce) if ce > 0 else s1
+                    self.step_thomas_(w_t, theta, stop - n)
+                    n = stop
+                    if ce > 0 and n % ce == 0 and n // ce <= n_ck:
+                        ckpt[n // ce - 1].copy_(w_t.t())
+        finally:
+            self.k, self._factors = k_saved, f_saved
+        return w_t.t().contiguous(), ckpt
+
     # ------------------------------------------------------------------ distances between states
     def compare(self, w_a, w_b):
         """Per problem, on the device (fvm_state_compare): max |a - b|, sum |a - b| h, max |b| and

@@ -122,3 +122,34 @@ def test_run_until_steady_reaches_the_analytic_steady_state(tmp_path):
     path = tmp_path / "snaps.npy"
     _, ck = model.theta_run(w0, 1.0, 40, checkpoint_every=10, save=str(path))
     assert np.array_equal(np.load(path), ck) and ck.shape == (4, J)
+
+
+def test_variable_time_step_matches_per_step_oracle():
+    """A time step that changes during the run (per problem, too): re-factored where it changes."""
+    J, P, n = 200, 2, 18
+    f = W.graded_faces(J)
+    a, d = np.array([1.0, 0.6]), np.array([0.02, 0.05])
+    cells = 0.5 * (f[1:] + f[:-1])
+    w0 = np.stack([np.exp(-((cells - 0.4) / 0.1) ** 2)] * P)
+    dt = np.empty((n, P))
+    dt[:6] = [2e-3, 1e-3]; dt[6:7] = [5e-3, 1e-3]; dt[7:] = [1e-3, 4e-3]      # runs of 6, 1 and 11 steps
+    bc = dict(left_flux=0.2, right_flux=0.0)
+    m = BatchedAdvectionDiffusionModel(f, a, d, 1.0, "exponential", P=P)      # the constructor's k is not used
+    m.set_boundary_conditions(**bc)
+    w, ck = m.run_variable_dt(w0, 0.5, dt, checkpoint_every=4)
+    assert ck.shape == (4, P, J)
+    for p in range(P):
+        asm = O.assemble(f, a[p], d[p], "exponential", **bc)
+        x, snaps = w0[p].copy(), []
+        for s in range(n):
+            x = O.theta_run_scipy(asm, dt[s, p], 0.5, x, 1, every=1)[0]
+            snaps.append(x)
+        snaps = np.array(snaps)
+        assert step_error(ck[:, p].cpu().numpy(), snaps[3::4][:4], 1.0) < TOL, p
+        assert step_error(w[p].cpu().numpy()[None], snaps[-1][None], 1.0) < TOL, p
+    # the model's own time step and factors are untouched afterwards
+    assert float(m.k[0]) == 1.0
+    # a constant history is run()
+    w1, _ = m.run_variable_dt(w0, 1.0, np.full(n, 1.0))
+    w2, _ = m.run(w0, 1.0, n, variant="thomas")
+    assert np.array_equal(w1.cpu().numpy(), w2.cpu().numpy())
