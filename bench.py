@@ -7,10 +7,10 @@ Crank-Nicolson, per-problem a/d/dt.
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
     python bench.py --impl reference      # the reference's numpy/scipy loop on the host cores
 
-One bench "step" = one launch of the fused kernel that advances every problem of the batch
-by --inner theta steps (default 1000 = cfg 3's checkpoint interval); the default K=10 steps
-are cfg 3's full 10,000 time steps.  Metric: fp64 cell-updates/s (one cell advanced by one
-theta step), whole job over all ranks.  Prints ONE JSON line on rank 0.
+One bench "step" = cfg 3's whole run for this GPU's problems: ONE launch of the fused kernel
+advances every problem by --inner = 10,000 theta steps and writes the state out every
+--checkpoint-every = 1,000 steps (10 checkpoints of 512 MiB).  Metric: fp64 cell-updates/s (one
+cell advanced by one theta step), whole job over all ranks.  Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -44,7 +44,11 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--problems", type=int, default=65536, help="problems per GPU")
     ap.add_argument("--cells", type=int, default=1024)
-    ap.add_argument("--inner", type=int, default=1000, help="theta steps per bench step (one launch)")
+    ap.add_argument("--inner", type=int, default=None,
+                    help="theta steps per bench step; default: the workload's own run length "
+                         "(cfg 3: 10,000 in one launch; cfg 4: 10; cfg 5: 20)")
+    ap.add_argument("--checkpoint-every", type=int, default=1000,
+                    help="cfg 3: the state is written out every this many steps (0: never)")
     ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg4", "cfg5"],
                     help="cfg3 (default, the headline): batched on-chip; cfg4: batched long systems; "
                          "cfg5: one mesh of 2^27 cells per GPU split over the ranks")
@@ -57,7 +61,8 @@ def config(args, extra=None):
     cfg = {"workload": "cfg3 batched sweep: %d problems/GPU x %d cells, exponential fitting, zero-flux "
                        "Robin, Crank-Nicolson theta=0.5, per-problem a/d/dt" % (args.problems, args.cells),
            "problems_per_gpu": args.problems, "cells": args.cells, "theta": 0.5,
-           "theta_steps_per_bench_step": args.inner, "sharding": "independent problems, no communication",
+           "theta_steps_per_bench_step": args.inner, "checkpoint_every": getattr(args, "checkpoint_every", 0),
+           "sharding": "independent problems, no communication",
            "l2": "state (%.0f MiB/GPU) exceeds the 126 MB L2; no flush needed" %
                  (args.problems * args.cells * 8 / 2 ** 20)}
     if extra:
@@ -109,6 +114,8 @@ def run_reference_arm(args):
     if rank != 0:
         return
     import multiprocessing as mp
+    if args.inner is None:
+        args.inner = 10000
     cores = os.cpu_count() or 1
     nsteps = 200
     jobs = [(i, 1, args.cells, nsteps) for i in range(cores)]
@@ -170,6 +177,9 @@ class ClockSampler:
                     reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "samples": len(sm), "reasons": sorted(reasons)}
+
+
+FUSED_SUMMARY = "r01_fused_cfg3_full.summary.txt"     # ncu --set full of the default command's dominant kernel
 
 
 def ncu_traffic(summary_name):
@@ -241,7 +251,7 @@ def run_partitioned(args):
         dist.init_process_group("nccl", device_id=dev)
     K, Wm = args.steps, max(args.warmup, 3)
     if args.workload == "cfg5":
-        inner = 20 if args.inner == 1000 else args.inner
+        inner = 20 if args.inner is None else args.inner
         J = world << 27
         from fvm_b200.partitioned import plan_partition
         T = 8192
@@ -253,7 +263,7 @@ def run_partitioned(args):
         desc = "cfg5 one graded mesh of %d x 2^27 = %d cells split over %d GPU(s), exponential, zero-flux Robin, " \
                "Crank-Nicolson, dt = 4 h_min/a, SPIKE reduced system all-gathered over NCCL each step" % (world, J, world)
     else:
-        inner = 10 if args.inner == 1000 else args.inner
+        inner = 10 if args.inner is None else args.inner
         Pn, J = 512, 1 << 20
         wl = W.stiff_reaction(P=world * Pn, J=J, first=rank * Pn, count=Pn)
         m = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=Pn,
@@ -350,6 +360,8 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
+    if args.inner is None:
+        args.inner = 10000
     P, J, inner, K, Wm = args.problems, args.cells, args.inner, args.steps, max(args.warmup, 3)
     # weak scaling: every rank owns its own shard of `problems` problems of a (world*P)-problem sweep
     wl = W.batched_sweep(world * P, J, first=rank * P, count=P)
@@ -363,9 +375,14 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident throughput ("value")
+    ce = args.checkpoint_every if 0 < args.checkpoint_every <= inner else 0
+    n_ck = inner // ce if ce else 0
+    ckpt = torch.empty((n_ck, P, J), dtype=torch.float64, device=dev) if n_ck else None
+
+    # ---- device-resident throughput ("value"): one launch = the whole run of `inner` steps,
+    # checkpoints written to HBM on the way
     for _ in range(Wm):
-        model.run_fused_(w, 0.5, inner)
+        model.run_fused_(w, 0.5, inner, ce, ckpt)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     sampler = ClockSampler(local)
     barrier()
@@ -374,7 +391,7 @@ def run_b200(args):
     t_all0.record()
     for i in range(K):
         ev[i][0].record()
-        model.run_fused_(w, 0.5, inner)
+        model.run_fused_(w, 0.5, inner, ce, ckpt)
         ev[i][1].record()
     t_all1.record()
     barrier()
@@ -387,29 +404,33 @@ def run_b200(args):
     ms_total = float(t.item())
     cu_per_step_rank = float(P) * J * inner
     value = world * cu_per_step_rank * K / (ms_total * 1e-3)
-    finite = bool(torch.isfinite(w).all())
+    finite = bool(torch.isfinite(w).all()) and (ckpt is None or bool(torch.isfinite(ckpt[-1]).all()))
+    del ckpt
 
     # ---- end to end through the host-facing call: pinned host state in, pinned host state out
     e2e = None
     if not args.no_e2e:
         h_in = torch.empty((P, J), dtype=torch.float64).pin_memory()
         h_out = torch.empty((P, J), dtype=torch.float64).pin_memory()
+        h_ck = torch.empty((n_ck, P, J), dtype=torch.float64).pin_memory() if n_ck else None
         h_in.copy_(w0)
         for _ in range(2):
-            model.run_host(h_in, 0.5, inner, out=h_out)
+            model.run_host(h_in, 0.5, inner, out=h_out, checkpoint_every=ce, ckpt_out=h_ck)
         barrier()
         t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
         t0.record()
         for _ in range(K):
-            model.run_host(h_in, 0.5, inner, out=h_out)
+            model.run_host(h_in, 0.5, inner, out=h_out, checkpoint_every=ce, ckpt_out=h_ck)
         t1.record()
         barrier()
         te = torch.tensor([t0.elapsed_time(t1)], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         e2e = {"value": world * cu_per_step_rank * K / (float(te.item()) * 1e-3), "unit": UNIT,
-               "h2d_bytes_per_step": P * J * 8, "d2h_bytes_per_step": P * J * 8,
-               "api": "BatchedAdvectionDiffusionModel.run_host (pinned host state in/out every step)"}
+               "h2d_bytes_per_step": P * J * 8, "d2h_bytes_per_step": (1 + n_ck) * P * J * 8,
+               "api": "BatchedAdvectionDiffusionModel.run_host (pinned host state in, final state and every "
+                      "checkpoint out to pinned host memory, every step)"}
+        del h_ck
 
     # ---- streaming variant (HBM roofline evidence), rank 0 only, small step count
     hbm = None
@@ -466,9 +487,10 @@ def run_b200(args):
     onchip = ONCHIP_B_PER_CELL_UPDATE * cu_s_kernel / 1e9
     roofline = {"kernel": "fused_tmem_kernel<CN> (variant 2: state in registers, coefficients in TMEM)",
                 "bound": "fp64", "achieved": fp64_ach, "peak": fp64_peak, "unit": "TFLOP/s",
-                "frac": fp64_ach / fp64_peak, "traffic": ncu_traffic("r01_fused_final.summary.txt"),
-                "traffic_note": "DRAM bytes per launch from profiles/r01_fused_final.summary.txt (ncu --set full, same "
-                                "command); algorithmic HBM bytes per launch = 16 B x %d x %d = %.3e" % (P, J, 16.0 * P * J),
+                "frac": fp64_ach / fp64_peak, "traffic": ncu_traffic(FUSED_SUMMARY),
+                "traffic_note": "DRAM bytes per launch from profiles/%s (ncu --set full, same command); algorithmic "
+                                "HBM bytes per launch = (16 + 8 x %d checkpoints) B x %d x %d = %.3e"
+                                % (FUSED_SUMMARY, n_ck, P, J, (16.0 + 8.0 * n_ck) * P * J),
                 "peak_source": "%d SMs x 64 DFMA/clk x 2 flop x %.0f MHz (max SM clock, %s); the 64 DFMA/clk/SM rate is "
                                "measured (profiles/microbench/r01_fp64_peak_b200.txt)" % (sms, f_max / 1e6, peak_src),
                 "flop_per_cell_update": FLOP_PER_CELL_UPDATE,
@@ -479,8 +501,9 @@ def run_b200(args):
                                                "note": "coefficient reads served by TMEM (tcgen05.ld) and registers; exceeds what "
                                                        "the 128 B/clk/SM shared-memory pipe could deliver when frac > 1",
                                                "frac_of_shared_memory_peak": onchip / smem_peak},
-                "hbm": {"achieved": 16.0 * P * J / (kernel_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                        "note": "state read once + written once per launch of %d steps" % inner},
+                "hbm": {"achieved": (16.0 + 8.0 * n_ck) * P * J / (kernel_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
+                        "unit": "GB/s", "note": "state read once, written once, plus %d checkpoints, per launch of "
+                                                "%d steps" % (n_ck, inner)},
                 "kernel_ms_per_launch": kernel_ms, "cell_updates_per_launch": cu_per_step_rank}
 
     cpu = None if args.no_cpu_baseline else cpu_baseline_single(J)

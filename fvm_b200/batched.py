@@ -488,7 +488,8 @@ class BatchedAdvectionDiffusionModel(object):
                     ckpt[(n + 1) // ce - 1].copy_(dst)
         return bufs[nsteps & 1]
 
-    def run_host(self, w_host, theta, nsteps, out=None, variant="auto", chunks=8):
+    def run_host(self, w_host, theta, nsteps, out=None, variant="auto", chunks=8, checkpoint_every=0,
+                 ckpt_out=None):
         """Host-buffer form of :meth:`run`: ``w_host`` (P, J) lives in host memory (numpy array
         or CPU tensor; pinned memory makes the copies asynchronous and fast).  Copies it to the
         device, advances it ``nsteps`` theta steps, copies the result into ``out`` (allocated
@@ -497,7 +498,11 @@ class BatchedAdvectionDiffusionModel(object):
 
         The batch is cut into ``chunks`` groups of problems that travel on three streams, so
         that the upload of one group, the kernel of another and the download of a third overlap
-        (problems are independent: no group waits for another)."""
+        (problems are independent: no group waits for another).
+
+        ``checkpoint_every`` > 0 (fused variant): the state after every that many steps is
+        copied into ``ckpt_out`` (nsteps // checkpoint_every, P, J) in host memory (allocated
+        pinned if None), group by group on the same streams; returns (out, ckpt_out)."""
         torch = _lib.require_cuda()
         if isinstance(w_host, np.ndarray):
             w_host = torch.from_numpy(np.ascontiguousarray(w_host, dtype=np.float64))
@@ -511,6 +516,17 @@ class BatchedAdvectionDiffusionModel(object):
             out = torch.from_numpy(out)
         if variant == "auto":
             variant = self._auto_variant()
+        ce = int(checkpoint_every or 0)
+        n_ck = int(nsteps) // ce if ce > 0 else 0
+        if n_ck and variant != "fused":
+            raise ValueError("host checkpoints are written by the fused variant only; use run() otherwise")
+        if n_ck:
+            if ckpt_out is None:
+                ckpt_out = torch.empty((n_ck, self.P, self.J), dtype=torch.float64).pin_memory()
+            elif isinstance(ckpt_out, np.ndarray):
+                ckpt_out = torch.from_numpy(ckpt_out)
+            if tuple(ckpt_out.shape) != (n_ck, self.P, self.J) or not ckpt_out.is_contiguous():
+                raise ValueError("ckpt_out must be a contiguous (%d, %d, %d) array" % (n_ck, self.P, self.J))
         with torch.cuda.device(self.device):
             if variant == "partitioned":
                 self._stage.copy_(w_host, non_blocking=True)
@@ -530,6 +546,14 @@ class BatchedAdvectionDiffusionModel(object):
             main = torch.cuda.current_stream()
             for s in self._streams:
                 s.wait_stream(main)
+            ck_stage = None
+            if n_ck:                                   # one device staging buffer per stream
+                width = max(bounds[i + 1] - bounds[i] for i in range(n_chunks))
+                key = (n_ck, width)
+                if getattr(self, "_stage_ck", None) is None or self._stage_ck[0] != key:
+                    self._stage_ck = (key, [torch.empty((n_ck, width, self.J), dtype=torch.float64, device=self.device)
+                                            for _ in self._streams])
+                ck_stage = self._stage_ck[1]
             for i in range(n_chunks):
                 lo, hi = bounds[i], bounds[i + 1]
                 st = self._streams[i % len(self._streams)]
@@ -537,15 +561,20 @@ class BatchedAdvectionDiffusionModel(object):
                     dst = self._stage[lo:hi]
                     dst.copy_(w_host[lo:hi], non_blocking=True)
                     sub = self._chunk_problem(pr, lo, hi)
+                    ck = None
+                    if n_ck:                           # the kernel's layout is (n, hi-lo, J), contiguous
+                        ck = ck_stage[i % len(self._streams)].view(-1)[:n_ck * (hi - lo) * self.J].view(n_ck, hi - lo, self.J)
                     rc = _lib.lib().fvm_theta_run_fused(ctypes.byref(sub), ctypes.c_void_p(self.k.data_ptr() + 8 * lo),
-                                                        float(theta), int(nsteps), 0, _lib.ptr(dst), None,
-                                                        _lib.stream_ptr())
+                                                        float(theta), int(nsteps), ce if n_ck else 0, _lib.ptr(dst),
+                                                        _lib.ptr(ck), _lib.stream_ptr())
                     _lib.check(rc, "fvm_theta_run_fused")
                     out[lo:hi].copy_(dst, non_blocking=True)
+                    for n in range(n_ck):
+                        ckpt_out[n, lo:hi].copy_(ck[n], non_blocking=True)
             for s in self._streams:
                 main.wait_stream(s)
             main.synchronize()
-        return out
+        return (out, ckpt_out) if n_ck else out
 
     def _chunk_problem(self, pr, lo, hi):
         """struct fvm_problem of the problems [lo, hi) of this batch (same mesh, shifted pointers)."""

@@ -412,6 +412,11 @@ template <> struct TmemChunk<4> {
   static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[32]) { tmem_ld_x32(t, r); }
   static __device__ __forceinline__ void wait(uint32_t (&r)[32]) { tmem_wait_ld_x32(r); }
 };
+template <> struct TmemChunk<1> {
+  static constexpr int REGS = 8;
+  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[8]) { tmem_ld_x8(t, r); }
+  static __device__ __forceinline__ void wait(uint32_t (&r)[8]) { tmem_wait_ld_x8(r); }
+};
 template <> struct TmemChunk<2> {
   static constexpr int REGS = 16;
   static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[16]) { tmem_ld_x16(t, r); }
@@ -885,6 +890,11 @@ static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, 
       return launch_fused_tmem<0, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
     }
     const char* its = getenv("FVM_TMEM_IT");     // 4: .x32 loads (experiments); default 2: .x16
+    if (its && its[0] == '1') {
+      if (theta == 0.5) return launch_fused_tmem<1, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      if (theta == 1.0) return launch_fused_tmem<2, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      return launch_fused_tmem<0, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    }
     if (its && its[0] == '4') {
       if (theta == 0.5) return launch_fused_tmem<1, 4, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
       if (theta == 1.0) return launch_fused_tmem<2, 4, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);

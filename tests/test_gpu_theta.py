@@ -257,6 +257,13 @@ def test_run_host_pipelined_chunks_equal_device_run():
     assert torch.equal(out, w_dev.cpu())
     out1 = m.run_host(wl["w0"], 0.5, 30, chunks=1)         # numpy input, single chunk
     assert torch.equal(out1, w_dev.cpu())
+    # checkpoints delivered to host memory, group by group (uneven groups: 8192 = 2730 + 2731 + 2731)
+    w_ck, ck_dev = m.run(wl["w0"], 0.5, 30, checkpoint_every=8, variant="fused")
+    out2, ck_host = m.run_host(h_in, 0.5, 30, chunks=3, checkpoint_every=8)
+    assert ck_host.shape == (3, 8192, 1024) and ck_host.is_pinned()
+    assert torch.equal(ck_host, ck_dev.cpu()) and torch.equal(out2, w_ck.cpu())
+    with pytest.raises(ValueError):
+        m.run_host(h_in, 0.5, 30, variant="thomas", checkpoint_every=8)
 
 
 def test_theta_zero_explicit_euler():
