@@ -284,9 +284,15 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
 // M = 16): assembles this lane's rows of A, factors the interior block from both ends (e, b ->
 // tensor memory at t_eb; s -> sS and the registers sr), computes both spikes (sv = V, su = U in
 // shared memory, natural cell order), the separator system and its PCR factors.
+//
+// LK (the 4-operation Crank-Nicolson sweep of fused_tmem_pipe_kernel<3, IT>): tensor memory gets
+// (l, kappa) instead of (e, b) -- l = the un-normalised elimination factor A_c,prev / pivot_prev,
+// kappa = 1 / (theta pivot_c) -- R.bfirst = theta beta_0 (un-normalised), and om_l / om_r return
+// (1 - theta) times the coupling of the block's end cells to the two separators.
+template <bool LK>
 __device__ __forceinline__ void tmem_setup_common(const fvm_problem& pr, int64_t p, int lane, double dt_p, double theta,
                                                   uint32_t t_eb, double* sS, double* sv, double* su, Reduced& R,
-                                                  double (&sr)[31], double& delta) {
+                                                  double (&sr)[31], double& delta, double& om_l, double& om_r) {
   constexpr int C = 32, N = 31, M = 16;
   const int64_t J = pr.J;
   const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
@@ -323,6 +329,8 @@ __device__ __forceinline__ void tmem_setup_common(const fvm_problem& pr, int64_t
         rFR = F; rD0 = Dm;
       }
       double sl_prev = 0.0, sr_prev = 0.0, gv_prev = 0.0, gu_prev = 0.0;
+      double invl_prev = 0.0, invr_prev = 0.0;
+      om_l = 0.0; om_r = 0.0;
 #pragma unroll 1
       for (int i = 0; i < M; ++i) {
         {                                            // left cell i: top-down elimination
@@ -335,8 +343,15 @@ __device__ __forceinline__ void tmem_setup_common(const fvm_problem& pr, int64_t
           sl_prev = a.up * inv;
           gv_prev = (i == 0) ? e : -e * gv_prev;     // elimination sweep of the left spike
           sS[i * 32] = sl_prev; sv[i * 32] = gv_prev; su[i * 32] = 0.0;
-          tmem_st_2d(t_eb + 8 * i, e, inv * (rth - cth * a.di));
-          if ((int64_t)lane * C + i == 0) R.bfirst = beta_l * inv;
+          if (LK) {
+            tmem_st_2d(t_eb + 8 * i, a.lo * invl_prev, inv * rth);
+            if (i == 0) om_l = (1.0 - theta) * a.lo;
+            if ((int64_t)lane * C + i == 0) R.bfirst = theta * beta_l;
+            invl_prev = inv;
+          } else {
+            tmem_st_2d(t_eb + 8 * i, e, inv * (rth - cth * a.di));
+            if ((int64_t)lane * C + i == 0) R.bfirst = beta_l * inv;
+          }
         }
         if (i < N - M) {                             // right cell 30-i: bottom-up elimination
           const int c = N - 1 - i;
@@ -349,7 +364,13 @@ __device__ __forceinline__ void tmem_setup_common(const fvm_problem& pr, int64_t
           sr_prev = a.lo * inv;
           gu_prev = (i == 0) ? e : -e * gu_prev;     // elimination sweep of the right spike
           sS[c * 32] = sr_prev; su[c * 32] = gu_prev; sv[c * 32] = 0.0;
-          tmem_st_2d(t_eb + 8 * i + 4, e, inv * (rth - cth * a.di));
+          if (LK) {
+            tmem_st_2d(t_eb + 8 * i + 4, a.up * invr_prev, inv * rth);
+            if (i == 0) om_r = (1.0 - theta) * a.up;
+            invr_prev = inv;
+          } else {
+            tmem_st_2d(t_eb + 8 * i + 4, e, inv * (rth - cth * a.di));
+          }
         }
       }
       R.slo = asep.lo; sdi = asep.di; R.sup = asep.up;
@@ -423,6 +444,16 @@ template <> struct TmemChunk<2> {
   static __device__ __forceinline__ void wait(uint32_t (&r)[16]) { tmem_wait_ld_x16(r); }
 };
 
+// Issue a chunk load and thread a value through an empty volatile asm behind it: whatever is
+// computed from `dep` afterwards is ordered after the ISSUE of the load.  This pins a prefetch
+// ahead of the arithmetic it is meant to overlap; the compiler otherwise sinks the load down to
+// its wait to save registers, and every chunk then pays the tensor-memory latency.
+template <class TC, int REGS>
+__device__ __forceinline__ void chunk_ld_after(uint32_t t, uint32_t (&r)[REGS], double& dep) {
+  TC::ld(t, r);
+  asm volatile("" : "+d"(dep));
+}
+
 // k-th double of a chunk (two 32-bit columns each)
 __device__ __forceinline__ double chunk_dbl(const uint32_t* r, int k) { return __hiloint2double((int)r[2 * k + 1], (int)r[2 * k]); }
 
@@ -457,7 +488,8 @@ fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, i
     Reduced R;
     double delta;
     double sr[N];                                    // s for the whole launch
-    tmem_setup_common(pr, p, lane, dt[p], theta, t_eb, sS, sv, su, R, sr, delta);
+    double om_unused_l, om_unused_r;
+    tmem_setup_common<false>(pr, p, lane, dt[p], theta, t_eb, sS, sv, su, R, sr, delta, om_unused_l, om_unused_r);
     {
 #pragma unroll 1
       for (int i = 0; i < M; ++i) {
@@ -610,9 +642,68 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
     Reduced R;
     double delta;
     double sr[N];
-    tmem_setup_common(pr, p, lane, dt[p], theta, t_eb, sS, sv, su, R, sr, delta);
+    constexpr bool CN4 = (MODE == 3);
+    double om_l, om_r;
+    tmem_setup_common<CN4>(pr, p, lane, dt[p], theta, t_eb, sS, sv, su, R, sr, delta, om_l, om_r);
     const double V0 = sv[0], U0 = su[0], VL = sv[(N - 1) * 32], UL = su[(N - 1) * 32];
-    {
+    if (CN4) {
+      // P1 = -(1/theta) T^-1 V, P2 = -(1/theta) T^-1 U  (T^-1 b_left = -c V cancels the -c V of
+      // B~_ii V = V/theta - c T V): twisted solve with right-hand sides -V, -U, in tensor memory
+      auto tcol = [&](int c) { return (uint32_t)(c < M ? 8 * c : 8 * (N - 1 - c) + 4); };
+      tmem_wait_st();
+      double l, kap, h1 = -sv[0], h2 = -su[0];
+      tmem_st_2d(t_pp + tcol(0), h1, h2);
+#pragma unroll 1
+      for (int c = 1; c < M; ++c) {
+        tmem_ld_2d(t_eb + tcol(c), l, kap);
+        h1 = fma(-l, h1, -sv[c * 32]); h2 = fma(-l, h2, -su[c * 32]);
+        tmem_st_2d(t_pp + tcol(c), h1, h2);
+      }
+      const double hl1 = h1, hl2 = h2;               // eliminated values at cell M-1
+      h1 = -sv[(N - 1) * 32]; h2 = -su[(N - 1) * 32];
+      tmem_st_2d(t_pp + tcol(N - 1), h1, h2);
+#pragma unroll 1
+      for (int c = N - 2; c >= M; --c) {
+        tmem_ld_2d(t_eb + tcol(c), l, kap);
+        h1 = fma(-l, h1, -sv[c * 32]); h2 = fma(-l, h2, -su[c * 32]);
+        tmem_st_2d(t_pp + tcol(c), h1, h2);
+      }
+      double kap_l, kap_r;
+      tmem_ld_2d(t_eb + tcol(M - 1), l, kap_l);
+      tmem_ld_2d(t_eb + tcol(M), l, kap_r);
+      const double m1 = fma(-sS[M * 32], hl1 * kap_l, h1 * kap_r) * delta;
+      const double m2 = fma(-sS[M * 32], hl2 * kap_l, h2 * kap_r) * delta;
+      tmem_wait_st();
+      double p1 = m1, p2 = m2, x1, x2;
+#pragma unroll 1
+      for (int c = M - 1; c >= 0; --c) {
+        tmem_ld_2d(t_pp + tcol(c), x1, x2);
+        tmem_ld_2d(t_eb + tcol(c), l, kap);
+        const double sc = sS[c * 32];
+        p1 = fma(-sc, p1, x1 * kap); p2 = fma(-sc, p2, x2 * kap);
+        tmem_st_2d(t_pp + tcol(c), p1, p2);
+      }
+      tmem_st_2d(t_pp + tcol(M), m1, m2);
+      p1 = m1; p2 = m2;
+#pragma unroll 1
+      for (int c = M + 1; c < N; ++c) {
+        tmem_ld_2d(t_pp + tcol(c), x1, x2);
+        tmem_ld_2d(t_eb + tcol(c), l, kap);
+        const double sc = sS[c * 32];
+        p1 = fma(-sc, p1, x1 * kap); p2 = fma(-sc, p2, x2 * kap);
+        tmem_st_2d(t_pp + tcol(c), p1, p2);
+      }
+      tmem_wait_st();
+      __syncwarp();
+      // s is in registers now: its shared-memory slots take the per-lane constants of a step, so
+      // that the registers they would occupy can hold the second tensor-memory chunk buffer
+      sS[0] = om_l; sS[32] = om_r;
+#pragma unroll
+      for (int l = 0; l < 5; ++l) { sS[(2 + l) * 32] = R.al[l]; sS[(7 + l) * 32] = R.ga[l]; }
+      sS[12 * 32] = R.invD; sS[13 * 32] = R.slo; sS[14 * 32] = R.sup; sS[15 * 32] = R.sblo;
+      sS[16 * 32] = R.sbdi; sS[17 * 32] = R.sbup; sS[18 * 32] = R.bsep; sS[19 * 32] = V0; sS[20 * 32] = U0;
+      sS[21 * 32] = VL; sS[22 * 32] = UL; sS[23 * 32] = R.bfirst;
+    } else {
       auto tcol = [&](int c) { return (uint32_t)(c < M ? 8 * c : 8 * (N - 1 - c) + 4); };
       tmem_wait_st();
       // right-hand sides of P1, P2: b_left - B~_ii V and b_right - B~_ii U, into tensor memory
@@ -684,33 +775,87 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
 
     // ------------------------------------------------------------------ time loop
     uint32_t ra[TC::REGS], rb[TC::REGS];
+    auto K = [&](int slot, double in_register) { return CN4 ? sS[slot * 32] : in_register; };
     // Elimination and substitution, in place on w[0..N-1]; the cells outside the block that the
     // end cells couple to contribute oldL0 / oldR0.  With PIPE the five PCR levels of the previous
     // step's separator system (rr in, xs out) are issued between the elimination chunks.
-    auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double& rr) {
+    // With PIPE the step-end chain of the PREVIOUS step (xs -> shuffle -> true end values -> shuffle
+    // -> rs) is issued inside the elimination as soon as the last PCR level is done (EARLY): its
+    // ~100 cycles of shuffle and FMA latency then hide behind the chunks' arithmetic.
+    auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double& rr,
+                      double g0_old, double gl_old, double& xsl, double& rs) {
       constexpr bool PIPE = decltype(pipe_tag)::value;
+      constexpr bool EARLY = PIPE && NCH >= 8;
+      double x_first = 0.0, x_last = 0.0, x_first_next = 0.0;
       const double w_m_old = w[M];
       double oldL = oldL0, gL = 0.0, oldR = oldR0, gR = 0.0;
+      double hk_l = 0.0, hk_r = 0.0;                  // CN4: h*kappa of the two cells at the meeting point
       int level = 0;
 #pragma unroll
       for (int k = 0; k < NCH; ++k) {
         uint32_t* cur = (k & 1) ? rb : ra;
-        if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, ra); }
-        else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, rb); }
+        if (CN4 && IT == 2 && k > 0) {
+          if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, ra, gL); }
+          else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, rb, gL); }
+        } else {
+          if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, ra); }
+          else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, rb); }
+        }
         // One PCR level per chunk.  Warps issue in order, so the level's shuffles are issued HERE and
         // their consumer sits after the chunk's cell work: the ~26-cycle shuffle latency is covered.
         double rm = 0.0, rp = 0.0;
         const bool lvl = PIPE && k < 5;
         if (lvl) { rm = shfl_up(rr, 1 << k); rp = shfl_dn(rr, 1 << k); }
+        if (EARLY && k == 5) { rr *= K(12, R.invD); xsl = shfl_up(rr, 1); }      // rr now holds xs
+        if (EARLY && k == 6) {
+          x_last = fma(-K(22, UL), rr, fma(-K(21, VL), xsl, gl_old));            // true values of the finished step
+          x_first = fma(-K(20, U0), rr, fma(-K(19, V0), xsl, g0_old));
+          x_first_next = shfl_dn(x_first, 1);
+        }
+        if (EARLY && k == 7) {
+          if (lane == 31) x_first_next = 0.0;
+          rs = fma(K(17, R.sbup), x_first_next, fma(K(16, R.sbdi), rr, fma(K(15, R.sblo), x_last, K(18, R.bsep))));
+        }
 #pragma unroll
         for (int ii = 0; ii < IT; ++ii) {
           const int i = k * IT + ii;
+          if (CN4) {
+            // h = g - l h_prev ; t = h kappa - g - s g_next : w <- t, so that the substitution
+            // z = t - s z_next below yields (1/theta) T^-1 g - g directly (4 operations per cell)
+            {
+              const int c = i;
+              const double l = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1);
+              const double gc = w[c];
+              const double gn = (c == M - 1) ? w_m_old : w[c + 1];
+              if (i == 0) {
+                gL = gc + K(23, R.bfirst);
+                if (!PIPE) gL = fma(-sS[0], oldL0, gL);
+              } else {
+                gL = fma(-l, gL, gc);
+              }
+              if (c == M - 1) { hk_l = gL * kap; w[c] = fma(-sr[c], gn, hk_l - gc); }
+              else w[c] = fma(-sr[c], gn, fma(gL, kap, -gc));
+            }
+            if (i < N - M) {
+              const int c = N - 1 - i;
+              const double l = chunk_dbl(cur, 4 * ii + 2), kap = chunk_dbl(cur, 4 * ii + 3);
+              const double gc = w[c];
+              if (i == 0) {
+                gR = gc;
+                if (!PIPE) gR = fma(-sS[32], oldR0, gR);
+              } else {
+                gR = fma(-l, gR, gc);
+              }
+              if (c == M) { hk_r = gR * kap; w[c] = fma(-sr[c], w[c - 1], hk_r - gc); }
+              else w[c] = fma(-sr[c], w[c - 1], fma(gR, kap, -gc));
+            }
+          } else {
           {
             const int c = i;
             const double e = chunk_dbl(cur, 4 * ii), b = chunk_dbl(cur, 4 * ii + 1);
             const double wc = w[c];
             const double wn = (c == M - 1) ? w_m_old : w[c + 1];
-            double r = rhs_cell<MODE>(e, sr[c], b, oldL, wc, wn, cth);
+            double r = rhs_cell<(MODE == 3 ? 1 : MODE)>(e, sr[c], b, oldL, wc, wn, cth);
             if (c == 0) r += R.bfirst;
             gL = (i == 0) ? r : fma(-e, gL, r);
             w[c] = gL;
@@ -720,13 +865,14 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
             const int c = N - 1 - i;
             const double e = chunk_dbl(cur, 4 * ii + 2), b = chunk_dbl(cur, 4 * ii + 3);
             const double wc = w[c];
-            double r = rhs_cell<MODE>(e, sr[c], b, oldR, wc, w[c - 1], cth);
+            double r = rhs_cell<(MODE == 3 ? 1 : MODE)>(e, sr[c], b, oldR, wc, w[c - 1], cth);
             gR = (i == 0) ? r : fma(-e, gR, r);
             w[c] = gR;
             oldR = wc;
           }
+          }
         }
-        if (lvl) { rr = fma(R.ga[k], rp, fma(R.al[k], rm, rr)); level = k + 1; }
+        if (lvl) { rr = fma(K(7 + k, R.ga[k]), rp, fma(K(2 + k, R.al[k]), rm, rr)); level = k + 1; }
       }
       if (PIPE) {
 #pragma unroll
@@ -734,12 +880,21 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
           if (l >= level) {
             const int s = 1 << l;
             const double rm = shfl_up(rr, s), rp = shfl_dn(rr, s);
-            rr = fma(R.ga[l], rp, fma(R.al[l], rm, rr));
+            rr = fma(K(7 + l, R.ga[l]), rp, fma(K(2 + l, R.al[l]), rm, rr));
           }
         }
-        rr *= R.invD;                                // rr now holds xs
+        if (!EARLY) {
+          rr *= K(12, R.invD);                       // rr now holds xs
+          xsl = shfl_up(rr, 1);
+          x_last = fma(-K(22, UL), rr, fma(-K(21, VL), xsl, gl_old));
+          x_first = fma(-K(20, U0), rr, fma(-K(19, V0), xsl, g0_old));
+          x_first_next = shfl_dn(x_first, 1);
+          if (lane == 31) x_first_next = 0.0;
+          rs = fma(K(17, R.sbup), x_first_next, fma(K(16, R.sbdi), rr, fma(K(15, R.sblo), x_last, K(18, R.bsep))));
+        }
       }
-      w[M] = fma(-sr[M], w[M - 1], w[M]) * delta;
+      if (CN4) w[M] = fma(fma(-sr[M], hk_l, hk_r), delta, -w_m_old);
+      else w[M] = fma(-sr[M], w[M - 1], w[M]) * delta;
 #pragma unroll
       for (int j = 0; j < M; ++j) {
         const int cl = M - 1 - j, cr = M + 1 + j;
@@ -758,26 +913,25 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       double wr = shfl_dn(w[0], 1);
       if (lane == 0) wl = 0.0;
       if (lane == 31) wr = 0.0;
-      double rs = fma(R.sbup, wr, fma(R.sbdi, w[C - 1], fma(R.sblo, w[N - 1], R.bsep)));
-      double rr = 0.0;
-      sweeps(std::false_type{}, wl, w[C - 1], t_eb, rr);
-      rr = fma(-R.sup, shfl_dn(w[0], 1), fma(-R.slo, w[N - 1], rs));
+      double rs = fma(K(17, R.sbup), wr, fma(K(16, R.sbdi), w[C - 1], fma(K(15, R.sblo), w[N - 1], K(18, R.bsep))));
+      double rr = 0.0, xsl = 0.0;
+      sweeps(std::false_type{}, wl, w[C - 1], t_eb, rr, 0.0, 0.0, xsl, rs);
+      rr = fma(-K(14, R.sup), shfl_dn(w[0], 1), fma(-K(13, R.slo), w[N - 1], rs));
       // -------- pipelined steps: PCR of step n overlaps the sweeps of step n+1
       for (int64_t i = 1; i < L; ++i) {
-        const double g0_old = w[0], gl_old = w[N - 1];
-        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr);
-        const double xs = rr;
-        const double xsl = shfl_up(xs, 1);          // lane 0: V == P1 == 0, value unused
-        const double x_last = fma(-UL, xs, fma(-VL, xsl, gl_old));      // true values of the finished step
-        const double x_first = fma(-U0, xs, fma(-V0, xsl, g0_old));
-        double x_first_next = shfl_dn(x_first, 1);
-        if (lane == 31) x_first_next = 0.0;
-        rs = fma(R.sbup, x_first_next, fma(R.sbdi, xs, fma(R.sblo, x_last, R.bsep)));
+        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, w[0], w[N - 1], xsl, rs);
+        double xs = rr;                             // lane 0: V == P1 == 0, its xsl is unused
+        double g0n = 0.0;
 #pragma unroll
         for (int k = 0; k < NCH; ++k) {             // g' = G + P1 xsl + P2 xs
           uint32_t* cur = (k & 1) ? rb : ra;
-          if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra); }
-          else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb); }
+          if (CN4 && IT == 2) {
+            if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra, xs); }
+            else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb, xs); }
+          } else {
+            if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra); }
+            else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb); }
+          }
 #pragma unroll
           for (int ii = 0; ii < IT; ++ii) {
             const int i2 = k * IT + ii;
@@ -787,12 +941,23 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
               w[c] = fma(chunk_dbl(cur, 4 * ii + 3), xs, fma(chunk_dbl(cur, 4 * ii + 2), xsl, w[c]));
             }
           }
+          if (k == 0) g0n = shfl_dn(w[0], 1);       // cells 0 and N-1 are final: start the exchange now
         }
-        rr = fma(-R.sup, shfl_dn(w[0], 1), fma(-R.slo, w[N - 1], rs));
+        rr = fma(-K(14, R.sup), g0n, fma(-K(13, R.slo), w[N - 1], rs));
       }
       // -------- end of the segment: finish the last step and materialise the true state
       {
-        const double xs = pcr_solve(rr, R);
+        double xs = rr;
+        if (CN4) {
+#pragma unroll
+          for (int l = 0; l < 5; ++l) {
+            const double rm = shfl_up(xs, 1 << l), rp = shfl_dn(xs, 1 << l);
+            xs = fma(sS[(7 + l) * 32], rp, fma(sS[(2 + l) * 32], rm, xs));
+          }
+          xs *= sS[12 * 32];
+        } else {
+          xs = pcr_solve(rr, R);
+        }
         const double xsl = shfl_up(xs, 1);
 #pragma unroll
         for (int c = 0; c < N; ++c) w[c] = fma(-su[c * 32], xs, fma(-sv[c * 32], xsl, w[c]));
@@ -864,7 +1029,10 @@ static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double the
   if (e != cudaSuccess) return (int)e;
   int64_t blocks = (pr.P + warps - 1) / warps;
   if (blocks > sms) blocks = sms;                // one CTA per SM: it holds the SM's whole TMEM
-  kern<<<(unsigned)blocks, warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
+  int launch_warps = warps;
+  const char* lw = getenv("FVM_FUSED_WARPS");    // experiment: 4 = one warp per scheduler
+  if (lw && lw[0] == '4') launch_warps = 4;
+  kern<<<(unsigned)blocks, launch_warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
   return (int)cudaGetLastError();
 }
 
@@ -888,6 +1056,13 @@ static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, 
       if (theta == 0.5) return launch_fused_tmem<1, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
       if (theta == 1.0) return launch_fused_tmem<2, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
       return launch_fused_tmem<0, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    }
+    // Crank-Nicolson: the 4-operation sweep (MODE 3); FVM_CN4=0 keeps the 5-operation one (A/B runs)
+    const char* c4 = getenv("FVM_CN4");
+    const char* it4 = getenv("FVM_TMEM_IT");
+    if (theta == 0.5 && !(c4 && c4[0] == '0')) {
+      if (it4 && it4[0] == '1') return launch_fused_tmem<3, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+      return launch_fused_tmem<3, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
     }
     const char* its = getenv("FVM_TMEM_IT");     // 4: .x32 loads (experiments); default 2: .x16
     if (its && its[0] == '1') {
