@@ -30,7 +30,7 @@ METRIC = "fp64 cell-updates/sec (theta-step)"
 UNIT = "cell-updates/s"
 # algorithmic work per cell-update of the fused on-chip variant
 FLOP_PER_CELL_UPDATE = 11.0          # RHS 3 FMA, forward 1 FMA, backward 1 FMA + 1 MUL
-FP64_INSTR_PER_CELL_UPDATE = 7.0     # what the partitioned on-chip solver issues: + 2 spike-correction FMAs
+FP64_INSTR_PER_CELL_UPDATE = 6.0     # what the on-chip Crank-Nicolson solver issues: 4 for the sweeps + 2 spike-correction FMAs
 ONCHIP_B_PER_CELL_UPDATE = 40.0      # five factored coefficients read once per step (32 B TMEM + 8 B registers)
 HBM_B_PER_CELL_UPDATE_THOMAS = 64.0  # variant 1: w, fp, fq, fb in; g out; g, fq in; w out
 HBM_B_PER_CELL_UPDATE_SPIKE = 40.0   # variant 3: w, p, q, b in; g out (three per-cell arrays streamed)
@@ -485,7 +485,7 @@ def run_b200(args):
     issue_frac = FP64_INSTR_PER_CELL_UPDATE * cu_s_kernel / (sms * 64.0 * f_clk)   # thread-level DFMAs issued / (64 lanes per clk per SM)
     smem_peak = sms * 128.0 * f_max / 1e9
     onchip = ONCHIP_B_PER_CELL_UPDATE * cu_s_kernel / 1e9
-    roofline = {"kernel": "fused_tmem_kernel<CN> (variant 2: state in registers, coefficients in TMEM)",
+    roofline = {"kernel": "fused_tmem_pipe_kernel<3, 2> (variant 2, Crank-Nicolson: state in registers, coefficients in TMEM)",
                 "bound": "fp64", "achieved": fp64_ach, "peak": fp64_peak, "unit": "TFLOP/s",
                 "frac": fp64_ach / fp64_peak, "traffic": ncu_traffic(FUSED_SUMMARY),
                 "traffic_note": "DRAM bytes per launch from profiles/%s (ncu --set full, same command); algorithmic "

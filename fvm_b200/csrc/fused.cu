@@ -794,7 +794,9 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
 #pragma unroll
       for (int k = 0; k < NCH; ++k) {
         uint32_t* cur = (k & 1) ? rb : ra;
-        if (CN4 && IT == 2 && k > 0) {
+        if (CN4 && IT <= 2 && k == 0) {
+          TC::wait(ra); chunk_ld_after<TC>(t_eb + 8 * IT, rb, w[0]);
+        } else if (CN4 && IT <= 2) {
           if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, ra, gL); }
           else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, rb, gL); }
         } else {
@@ -925,7 +927,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
 #pragma unroll
         for (int k = 0; k < NCH; ++k) {             // g' = G + P1 xsl + P2 xs
           uint32_t* cur = (k & 1) ? rb : ra;
-          if (CN4 && IT == 2) {
+          if (CN4 && IT <= 2) {
             if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra, xs); }
             else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb, xs); }
           } else {
