@@ -650,23 +650,27 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       // P1 = -(1/theta) T^-1 V, P2 = -(1/theta) T^-1 U  (T^-1 b_left = -c V cancels the -c V of
       // B~_ii V = V/theta - c T V): twisted solve with right-hand sides -V, -U, in tensor memory
       auto tcol = [&](int c) { return (uint32_t)(c < M ? 8 * c : 8 * (N - 1 - c) + 4); };
+      // P1, P2 are stored in the order the substitution visits the cells (from the meeting point
+      // outwards): slot j = (left cell M-1-j, right cell M+j), so that the correction of a cell can
+      // ride on its substitution link
+      auto tpp = [&](int c) { return (uint32_t)(c < M ? 8 * (M - 1 - c) : 8 * (c - M) + 4); };
       tmem_wait_st();
       double l, kap, h1 = -sv[0], h2 = -su[0];
-      tmem_st_2d(t_pp + tcol(0), h1, h2);
+      tmem_st_2d(t_pp + tpp(0), h1, h2);
 #pragma unroll 1
       for (int c = 1; c < M; ++c) {
         tmem_ld_2d(t_eb + tcol(c), l, kap);
         h1 = fma(-l, h1, -sv[c * 32]); h2 = fma(-l, h2, -su[c * 32]);
-        tmem_st_2d(t_pp + tcol(c), h1, h2);
+        tmem_st_2d(t_pp + tpp(c), h1, h2);
       }
       const double hl1 = h1, hl2 = h2;               // eliminated values at cell M-1
       h1 = -sv[(N - 1) * 32]; h2 = -su[(N - 1) * 32];
-      tmem_st_2d(t_pp + tcol(N - 1), h1, h2);
+      tmem_st_2d(t_pp + tpp(N - 1), h1, h2);
 #pragma unroll 1
       for (int c = N - 2; c >= M; --c) {
         tmem_ld_2d(t_eb + tcol(c), l, kap);
         h1 = fma(-l, h1, -sv[c * 32]); h2 = fma(-l, h2, -su[c * 32]);
-        tmem_st_2d(t_pp + tcol(c), h1, h2);
+        tmem_st_2d(t_pp + tpp(c), h1, h2);
       }
       double kap_l, kap_r;
       tmem_ld_2d(t_eb + tcol(M - 1), l, kap_l);
@@ -677,21 +681,21 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       double p1 = m1, p2 = m2, x1, x2;
 #pragma unroll 1
       for (int c = M - 1; c >= 0; --c) {
-        tmem_ld_2d(t_pp + tcol(c), x1, x2);
+        tmem_ld_2d(t_pp + tpp(c), x1, x2);
         tmem_ld_2d(t_eb + tcol(c), l, kap);
         const double sc = sS[c * 32];
         p1 = fma(-sc, p1, x1 * kap); p2 = fma(-sc, p2, x2 * kap);
-        tmem_st_2d(t_pp + tcol(c), p1, p2);
+        tmem_st_2d(t_pp + tpp(c), p1, p2);
       }
-      tmem_st_2d(t_pp + tcol(M), m1, m2);
+      tmem_st_2d(t_pp + tpp(M), m1, m2);
       p1 = m1; p2 = m2;
 #pragma unroll 1
       for (int c = M + 1; c < N; ++c) {
-        tmem_ld_2d(t_pp + tcol(c), x1, x2);
+        tmem_ld_2d(t_pp + tpp(c), x1, x2);
         tmem_ld_2d(t_eb + tcol(c), l, kap);
         const double sc = sS[c * 32];
         p1 = fma(-sc, p1, x1 * kap); p2 = fma(-sc, p2, x2 * kap);
-        tmem_st_2d(t_pp + tcol(c), p1, p2);
+        tmem_st_2d(t_pp + tpp(c), p1, p2);
       }
       tmem_wait_st();
       __syncwarp();
@@ -786,6 +790,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
                       double g0_old, double gl_old, double& xsl, double& rs) {
       constexpr bool PIPE = decltype(pipe_tag)::value;
       constexpr bool EARLY = PIPE && NCH >= 8;
+      constexpr bool FSC = CN4;                       // fused substitution + correction
       double x_first = 0.0, x_last = 0.0, x_first_next = 0.0;
       const double w_m_old = w[M];
       double oldL = oldL0, gL = 0.0, oldR = oldR0, gR = 0.0;
@@ -895,13 +900,41 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
           rs = fma(K(17, R.sbup), x_first_next, fma(K(16, R.sbdi), rr, fma(K(15, R.sblo), x_last, K(18, R.bsep))));
         }
       }
-      if (CN4) w[M] = fma(fma(-sr[M], hk_l, hk_r), delta, -w_m_old);
-      else w[M] = fma(-sr[M], w[M - 1], w[M]) * delta;
+      if (PIPE && FSC) {
+        // substitution outwards from the meeting point with the delayed correction riding on every
+        // link: the chain runs on the uncorrected values zL / zR, the corrected ones go to w
+        const double zM = fma(fma(-sr[M], hk_l, hk_r), delta, -w_m_old);
+        const double xs = rr;
+        double zL = zM, zR = zM;
 #pragma unroll
-      for (int j = 0; j < M; ++j) {
-        const int cl = M - 1 - j, cr = M + 1 + j;
-        w[cl] = fma(-sr[cl], w[cl + 1], w[cl]);
-        if (cr < N) w[cr] = fma(-sr[cr], w[cr - 1], w[cr]);
+        for (int k = 0; k < NCH; ++k) {
+          uint32_t* cur = (k & 1) ? rb : ra;
+          if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra, zL); }
+          else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb, zL); }
+#pragma unroll
+          for (int ii = 0; ii < IT; ++ii) {
+            const int j = k * IT + ii;
+            {
+              const int cl = M - 1 - j;
+              zL = fma(-sr[cl], zL, w[cl]);
+              w[cl] = fma(chunk_dbl(cur, 4 * ii + 1), xs, fma(chunk_dbl(cur, 4 * ii), xsl, zL));
+            }
+            if (j < N - M) {
+              const int cr = M + j;
+              if (j > 0) zR = fma(-sr[cr], zR, w[cr]);
+              w[cr] = fma(chunk_dbl(cur, 4 * ii + 3), xs, fma(chunk_dbl(cur, 4 * ii + 2), xsl, zR));
+            }
+          }
+        }
+      } else {
+        if (CN4) w[M] = fma(fma(-sr[M], hk_l, hk_r), delta, -w_m_old);
+        else w[M] = fma(-sr[M], w[M - 1], w[M]) * delta;
+#pragma unroll
+        for (int j = 0; j < M; ++j) {
+          const int cl = M - 1 - j, cr = M + 1 + j;
+          w[cl] = fma(-sr[cl], w[cl + 1], w[cl]);
+          if (cr < N) w[cr] = fma(-sr[cr], w[cr - 1], w[cr]);
+        }
       }
     };
 
@@ -924,8 +957,9 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
         sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, w[0], w[N - 1], xsl, rs);
         double xs = rr;                             // lane 0: V == P1 == 0, its xsl is unused
         double g0n = 0.0;
+        if (CN4) g0n = shfl_dn(w[0], 1);            // the correction was applied inside the substitution
 #pragma unroll
-        for (int k = 0; k < NCH; ++k) {             // g' = G + P1 xsl + P2 xs
+        for (int k = 0; k < (CN4 ? 0 : NCH); ++k) { // g' = G + P1 xsl + P2 xs
           uint32_t* cur = (k & 1) ? rb : ra;
           if (CN4 && IT <= 2) {
             if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra, xs); }
