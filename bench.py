@@ -31,6 +31,7 @@ UNIT = "cell-updates/s"
 # algorithmic work per cell-update of the fused on-chip variant
 FLOP_PER_CELL_UPDATE = 11.0          # RHS 3 FMA, forward 1 FMA, backward 1 FMA + 1 MUL
 FP64_INSTR_PER_CELL_UPDATE = 6.0     # what the on-chip Crank-Nicolson solver issues: 4 for the sweeps + 2 spike-correction FMAs
+DFMA_DISTINCT_OPERANDS_PER_CLK_SM = 44.0   # measured: profiles/microbench/r01_fp64_operands_b200.txt
 ONCHIP_B_PER_CELL_UPDATE = 40.0      # five factored coefficients read once per step (32 B TMEM + 8 B registers)
 HBM_B_PER_CELL_UPDATE_THOMAS = 64.0  # variant 1: w, fp, fq, fb in; g out; g, fq in; w out
 HBM_B_PER_CELL_UPDATE_SPIKE = 40.0   # variant 3: w, p, q, b in; g out (three per-cell arrays streamed)
@@ -493,6 +494,14 @@ def run_b200(args):
                                 % (FUSED_SUMMARY, n_ck, P, J, (16.0 + 8.0 * n_ck) * P * J),
                 "peak_source": "%d SMs x 64 DFMA/clk x 2 flop x %.0f MHz (max SM clock, %s); the 64 DFMA/clk/SM rate is "
                                "measured (profiles/microbench/r01_fp64_peak_b200.txt)" % (sms, f_max / 1e6, peak_src),
+                "register_operand_ceiling": {
+                    "dfma_per_clk_per_sm": DFMA_DISTINCT_OPERANDS_PER_CLK_SM,
+                    "issued_dfma_per_clk_per_sm": issue_frac * 64.0,
+                    "frac": issue_frac * 64.0 / DFMA_DISTINCT_OPERANDS_PER_CLK_SM,
+                    "note": "a DFMA whose three operands are distinct registers (every FMA of the sweeps) sustains "
+                            "42-45 per clk per SM on this GPU, not 64: register-file operand bandwidth "
+                            "(profiles/microbench/fp64_operands.cu, r01_fp64_operands_b200.txt); roofline.frac above is "
+                            "still quoted against the 64/clk/SM pipe peak"},
                 "flop_per_cell_update": FLOP_PER_CELL_UPDATE,
                 "fp64_pipe_issue_frac": issue_frac,
                 "fp64_instr_per_cell_update": FP64_INSTR_PER_CELL_UPDATE,

@@ -911,19 +911,32 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
           uint32_t* cur = (k & 1) ? rb : ra;
           if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra, zL); }
           else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb, zL); }
+          // links first, then the xsl products of the whole chunk, then the xs products: consecutive
+          // FMAs that share an operand can take it from the operand-reuse cache instead of the
+          // register file, whose bandwidth is what bounds these loops (fp64_operands.cu)
+          double zl[IT], zr[IT];
 #pragma unroll
           for (int ii = 0; ii < IT; ++ii) {
             const int j = k * IT + ii;
-            {
-              const int cl = M - 1 - j;
-              zL = fma(-sr[cl], zL, w[cl]);
-              w[cl] = fma(chunk_dbl(cur, 4 * ii + 1), xs, fma(chunk_dbl(cur, 4 * ii), xsl, zL));
-            }
+            const int cl = M - 1 - j, cr = M + j;
+            zL = fma(-sr[cl], zL, w[cl]);
+            zl[ii] = zL;
             if (j < N - M) {
-              const int cr = M + j;
               if (j > 0) zR = fma(-sr[cr], zR, w[cr]);
-              w[cr] = fma(chunk_dbl(cur, 4 * ii + 3), xs, fma(chunk_dbl(cur, 4 * ii + 2), xsl, zR));
+              zr[ii] = zR;
             }
+          }
+#pragma unroll
+          for (int ii = 0; ii < IT; ++ii) {
+            const int j = k * IT + ii;
+            zl[ii] = fma(chunk_dbl(cur, 4 * ii), xsl, zl[ii]);
+            if (j < N - M) zr[ii] = fma(chunk_dbl(cur, 4 * ii + 2), xsl, zr[ii]);
+          }
+#pragma unroll
+          for (int ii = 0; ii < IT; ++ii) {
+            const int j = k * IT + ii;
+            w[M - 1 - j] = fma(chunk_dbl(cur, 4 * ii + 1), xs, zl[ii]);
+            if (j < N - M) w[M + j] = fma(chunk_dbl(cur, 4 * ii + 3), xs, zr[ii]);
           }
         }
       } else {
