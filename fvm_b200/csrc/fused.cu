@@ -598,19 +598,31 @@ fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, i
 // Tensor-memory variant with a DELAYED CORRECTION, the default for 512 < J <= 1024.
 //
 // In fused_tmem_kernel a step is  sweeps -> separator PCR -> correction, and the PCR (five
-// levels of shuffle + FMA, ~25 % of the step, a pure latency chain that leaves the fp64 pipe
-// idle) cannot overlap anything, because the next sweeps need the corrected state.  But the whole
-// step is linear with constant coefficients.  Keep, between steps, the UNCORRECTED block
-// solutions g and the reduced right-hand side rr; the true state is x = g - V xsl - U xs with the
-// separator values xs = R^-1 rr still to come.  Then
-//     g' = T^-1 (B~ x)_interior = T^-1 B~_ii g  +  P1 xsl  +  P2 xs ,
-//     P1 = T^-1 (b_left  - B~_ii V) ,  P2 = T^-1 (b_right - B~_ii U)      (computed once, in TMEM),
-// where b_left / b_right carry the coupling of the block's end cells to the two separators.  The
-// sweeps T^-1 B~_ii g do not need xs, so they run while the PCR of the PREVIOUS step is in
-// flight: its levels are interleaved with the elimination chunks.  P1, P2 take the place of V, U
-// in tensor memory (same traffic, same flops); V and U stay in shared memory for the points where
-// the true state is needed (checkpoints, the end of the launch), which cut the run into
-// pipelined segments.  Algebraically identical to the plain scheme (scratch/proto_pipe.py).
+// levels of shuffle + FMA, a pure latency chain that leaves the fp64 pipe idle) cannot overlap
+// anything, because the next sweeps need the corrected state.  But the whole step is linear with
+// constant coefficients.  Keep, between steps, the UNCORRECTED block solutions g and the reduced
+// right-hand side rr; the true state is x = g - V xsl - U xs with the separator values
+// xs = R^-1 rr still to come.  Then
+//     g' = T^-1 (B x)_interior = T^-1 B_ii g  +  P1 xsl  +  P2 xs ,
+// and the sweeps T^-1 B_ii g do not need xs: they run while the PCR of the PREVIOUS step is in
+// flight, its levels interleaved with the elimination chunks.  V and U stay in shared memory for
+// the points where the true state is needed (checkpoints, the end of the launch), which cut the
+// run into pipelined segments (scratch/proto_pipe.py).
+//
+// The sweeps use  B = I/theta - c A  once more:  A^-1 B = (1/theta) A^-1 - c I, so on the block
+// interior  T^-1 B_ii g = (1/theta) T^-1 g - c g  -- there is no right-hand side to build -- and
+//     P1 = -(1/theta) T^-1 V ,   P2 = -(1/theta) T^-1 U
+// (T^-1 b_left = -c V cancels the -c V of T^-1 B_ii V).  With the un-normalised factors
+// l_c = A_c,prev / pivot_prev, kappa_c = 1 / (theta pivot_c) and z = y - c g:
+//     elimination   h_c = g_c - l_c h_prev                          (1 FMA, the chain)
+//                   t_c = h_c kappa_c - c g_c - c s_c g_next        (off the chain, written over g_c)
+//     substitution  z_c = t_c - s_c z_next                          (1 FMA, the chain)
+// which is 4 operations per cell for Crank-Nicolson (c = 1), 3 for implicit Euler (c = 0) and 5
+// in general (scratch/proto_cn4.py).  The correction rides on the substitution links: P1, P2 are
+// stored in the order the substitution visits the cells (slot j = left cell M-1-j, right cell M+j),
+// the chain runs on the uncorrected values and each link is followed by its two correction FMAs.
+//
+// MODE 0: any theta in (0,1];  1: Crank-Nicolson;  2: implicit Euler.
 template <int MODE, int IT>
 __global__ void __launch_bounds__(kFusedThreads, 1)
 fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
@@ -618,12 +630,15 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
   constexpr int C = 32, N = 31, M = 16;
   constexpr int NCH = M / IT;
   using TC = TmemChunk<IT>;
+  // shared-memory slots (per lane) of the constants of a step, in the place s occupied during set-up
+  enum { K_OML = 0, K_OMR = 1, K_AL = 2, K_GA = 7, K_INVD = 12, K_SLO = 13, K_SUP = 14, K_SBLO = 15, K_SBDI = 16,
+         K_SBUP = 17, K_BSEP = 18, K_V0 = 19, K_U0 = 20, K_VL = 21, K_UL = 22, K_BFIRST = 23 };
   extern __shared__ double smem[];
   __shared__ uint32_t tmem_base_slot;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps = blockDim.x >> 5;
-  double* sS = smem + (size_t)warp * (3 * N * 32) + lane;        // s (set-up only), V, U
+  double* sS = smem + (size_t)warp * (3 * N * 32) + lane;        // s during set-up, then the constants; V; U
   double* sv = sS + N * 32;
   double* su = sv + N * 32;
   const int64_t J = pr.J;
@@ -634,32 +649,26 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
   __syncthreads();
   tmem_fence_after_sync();
   const uint32_t tmem_base = tmem_base_slot;
-  const uint32_t t_eb = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
-  const uint32_t t_pp = t_eb + 128;                  // (P1, P2) pairs, same slot order as (e, b)
+  const uint32_t t_lk = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
+  const uint32_t t_pp = t_lk + 128;                  // (P1, P2) pairs in substitution order
 
   for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
     // ------------------------------------------------------------------ set-up (once)
-    Reduced R;
     double delta;
     double sr[N];
-    constexpr bool CN4 = (MODE == 3);
-    double om_l, om_r;
-    tmem_setup_common<CN4>(pr, p, lane, dt[p], theta, t_eb, sS, sv, su, R, sr, delta, om_l, om_r);
-    const double V0 = sv[0], U0 = su[0], VL = sv[(N - 1) * 32], UL = su[(N - 1) * 32];
-    if (CN4) {
-      // P1 = -(1/theta) T^-1 V, P2 = -(1/theta) T^-1 U  (T^-1 b_left = -c V cancels the -c V of
-      // B~_ii V = V/theta - c T V): twisted solve with right-hand sides -V, -U, in tensor memory
+    {
+      Reduced R;
+      double om_l, om_r;
+      tmem_setup_common<true>(pr, p, lane, dt[p], theta, t_lk, sS, sv, su, R, sr, delta, om_l, om_r);
+      // P1, P2: twisted solve with right-hand sides -V, -U, in place in tensor memory
       auto tcol = [&](int c) { return (uint32_t)(c < M ? 8 * c : 8 * (N - 1 - c) + 4); };
-      // P1, P2 are stored in the order the substitution visits the cells (from the meeting point
-      // outwards): slot j = (left cell M-1-j, right cell M+j), so that the correction of a cell can
-      // ride on its substitution link
       auto tpp = [&](int c) { return (uint32_t)(c < M ? 8 * (M - 1 - c) : 8 * (c - M) + 4); };
       tmem_wait_st();
       double l, kap, h1 = -sv[0], h2 = -su[0];
       tmem_st_2d(t_pp + tpp(0), h1, h2);
 #pragma unroll 1
-      for (int c = 1; c < M; ++c) {
-        tmem_ld_2d(t_eb + tcol(c), l, kap);
+      for (int c = 1; c < M; ++c) {                  // eliminate downwards
+        tmem_ld_2d(t_lk + tcol(c), l, kap);
         h1 = fma(-l, h1, -sv[c * 32]); h2 = fma(-l, h2, -su[c * 32]);
         tmem_st_2d(t_pp + tpp(c), h1, h2);
       }
@@ -667,22 +676,22 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       h1 = -sv[(N - 1) * 32]; h2 = -su[(N - 1) * 32];
       tmem_st_2d(t_pp + tpp(N - 1), h1, h2);
 #pragma unroll 1
-      for (int c = N - 2; c >= M; --c) {
-        tmem_ld_2d(t_eb + tcol(c), l, kap);
+      for (int c = N - 2; c >= M; --c) {             // eliminate upwards
+        tmem_ld_2d(t_lk + tcol(c), l, kap);
         h1 = fma(-l, h1, -sv[c * 32]); h2 = fma(-l, h2, -su[c * 32]);
         tmem_st_2d(t_pp + tpp(c), h1, h2);
       }
-      double kap_l, kap_r;
-      tmem_ld_2d(t_eb + tcol(M - 1), l, kap_l);
-      tmem_ld_2d(t_eb + tcol(M), l, kap_r);
+      double kap_l, kap_r;                           // meet between cells M-1 and M
+      tmem_ld_2d(t_lk + tcol(M - 1), l, kap_l);
+      tmem_ld_2d(t_lk + tcol(M), l, kap_r);
       const double m1 = fma(-sS[M * 32], hl1 * kap_l, h1 * kap_r) * delta;
       const double m2 = fma(-sS[M * 32], hl2 * kap_l, h2 * kap_r) * delta;
       tmem_wait_st();
       double p1 = m1, p2 = m2, x1, x2;
 #pragma unroll 1
-      for (int c = M - 1; c >= 0; --c) {
+      for (int c = M - 1; c >= 0; --c) {             // substitute outwards
         tmem_ld_2d(t_pp + tpp(c), x1, x2);
-        tmem_ld_2d(t_eb + tcol(c), l, kap);
+        tmem_ld_2d(t_lk + tcol(c), l, kap);
         const double sc = sS[c * 32];
         p1 = fma(-sc, p1, x1 * kap); p2 = fma(-sc, p2, x2 * kap);
         tmem_st_2d(t_pp + tpp(c), p1, p2);
@@ -692,7 +701,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
 #pragma unroll 1
       for (int c = M + 1; c < N; ++c) {
         tmem_ld_2d(t_pp + tpp(c), x1, x2);
-        tmem_ld_2d(t_eb + tcol(c), l, kap);
+        tmem_ld_2d(t_lk + tcol(c), l, kap);
         const double sc = sS[c * 32];
         p1 = fma(-sc, p1, x1 * kap); p2 = fma(-sc, p2, x2 * kap);
         tmem_st_2d(t_pp + tpp(c), p1, p2);
@@ -701,185 +710,101 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       __syncwarp();
       // s is in registers now: its shared-memory slots take the per-lane constants of a step, so
       // that the registers they would occupy can hold the second tensor-memory chunk buffer
-      sS[0] = om_l; sS[32] = om_r;
+      const double V0 = sv[0], U0 = su[0], VL = sv[(N - 1) * 32], UL = su[(N - 1) * 32];
+      sS[K_OML * 32] = om_l; sS[K_OMR * 32] = om_r;
 #pragma unroll
-      for (int l = 0; l < 5; ++l) { sS[(2 + l) * 32] = R.al[l]; sS[(7 + l) * 32] = R.ga[l]; }
-      sS[12 * 32] = R.invD; sS[13 * 32] = R.slo; sS[14 * 32] = R.sup; sS[15 * 32] = R.sblo;
-      sS[16 * 32] = R.sbdi; sS[17 * 32] = R.sbup; sS[18 * 32] = R.bsep; sS[19 * 32] = V0; sS[20 * 32] = U0;
-      sS[21 * 32] = VL; sS[22 * 32] = UL; sS[23 * 32] = R.bfirst;
-    } else {
-      auto tcol = [&](int c) { return (uint32_t)(c < M ? 8 * c : 8 * (N - 1 - c) + 4); };
-      tmem_wait_st();
-      // right-hand sides of P1, P2: b_left - B~_ii V and b_right - B~_ii U, into tensor memory
-#pragma unroll 1
-      for (int c = 0; c < N; ++c) {
-        double e, b;
-        tmem_ld_2d(t_eb + tcol(c), e, b);
-        const bool left = c < M;
-        const int cn_e = left ? c - 1 : c + 1, cn_s = left ? c + 1 : c - 1;
-        const bool has_e = left ? (c > 0) : (c < N - 1);
-        const double Ve = has_e ? sv[cn_e * 32] : 0.0, Ue = has_e ? su[cn_e * 32] : 0.0;
-        const double Vs = sv[cn_s * 32], Us = su[cn_s * 32];
-        const double sc = sS[c * 32];
-        double tv = b * sv[c * 32], tu = b * su[c * 32];
-        if (MODE != 2) {
-          tv = fma(-cth, fma(sc, Vs, e * Ve), tv);
-          tu = fma(-cth, fma(sc, Us, e * Ue), tu);
-        }
-        const double r1 = ((c == 0 && MODE != 2) ? -cth * e : 0.0) - tv;
-        const double r2 = ((c == N - 1 && MODE != 2) ? -cth * e : 0.0) - tu;
-        tmem_st_2d(t_pp + tcol(c), r1, r2);
-      }
-      tmem_wait_st();
-      // twisted solve of both right-hand sides, in place in tensor memory
-      double x1, x2, p1, p2, e, b;
-      tmem_ld_2d(t_pp + tcol(0), p1, p2);
-#pragma unroll 1
-      for (int c = 1; c < M; ++c) {                  // eliminate downwards
-        tmem_ld_2d(t_eb + tcol(c), e, b);
-        tmem_ld_2d(t_pp + tcol(c), x1, x2);
-        p1 = fma(-e, p1, x1); p2 = fma(-e, p2, x2);
-        tmem_st_2d(t_pp + tcol(c), p1, p2);
-      }
-      double l1 = p1, l2 = p2;                        // eliminated values at cell M-1
-      tmem_ld_2d(t_pp + tcol(N - 1), p1, p2);
-#pragma unroll 1
-      for (int c = N - 2; c >= M; --c) {             // eliminate upwards
-        tmem_ld_2d(t_eb + tcol(c), e, b);
-        tmem_ld_2d(t_pp + tcol(c), x1, x2);
-        p1 = fma(-e, p1, x1); p2 = fma(-e, p2, x2);
-        tmem_st_2d(t_pp + tcol(c), p1, p2);
-      }
-      // meet between cells M-1 and M, then substitute outwards
-      const double m1 = fma(-sS[M * 32], l1, p1) * delta, m2 = fma(-sS[M * 32], l2, p2) * delta;
-      tmem_st_2d(t_pp + tcol(M), m1, m2);
-      tmem_wait_st();
-      p1 = m1; p2 = m2;
-#pragma unroll 1
-      for (int c = M - 1; c >= 0; --c) {
-        tmem_ld_2d(t_pp + tcol(c), x1, x2);
-        const double sc = sS[c * 32];
-        p1 = fma(-sc, p1, x1); p2 = fma(-sc, p2, x2);
-        tmem_st_2d(t_pp + tcol(c), p1, p2);
-      }
-      p1 = m1; p2 = m2;
-#pragma unroll 1
-      for (int c = M + 1; c < N; ++c) {
-        tmem_ld_2d(t_pp + tcol(c), x1, x2);
-        const double sc = sS[c * 32];
-        p1 = fma(-sc, p1, x1); p2 = fma(-sc, p2, x2);
-        tmem_st_2d(t_pp + tcol(c), p1, p2);
-      }
+      for (int l2 = 0; l2 < 5; ++l2) { sS[(K_AL + l2) * 32] = R.al[l2]; sS[(K_GA + l2) * 32] = R.ga[l2]; }
+      sS[K_INVD * 32] = R.invD; sS[K_SLO * 32] = R.slo; sS[K_SUP * 32] = R.sup; sS[K_SBLO * 32] = R.sblo;
+      sS[K_SBDI * 32] = R.sbdi; sS[K_SBUP * 32] = R.sbup; sS[K_BSEP * 32] = R.bsep; sS[K_V0 * 32] = V0;
+      sS[K_U0 * 32] = U0; sS[K_VL * 32] = VL; sS[K_UL * 32] = UL; sS[K_BFIRST * 32] = R.bfirst;
     }
-    tmem_wait_st();
-    __syncwarp();
+    auto K = [&](int slot) { return sS[slot * 32]; };
 
     double w[C];
     load_state<C>(w_io + p * J, J, lane, w);
 
     // ------------------------------------------------------------------ time loop
     uint32_t ra[TC::REGS], rb[TC::REGS];
-    auto K = [&](int slot, double in_register) { return CN4 ? sS[slot * 32] : in_register; };
-    // Elimination and substitution, in place on w[0..N-1]; the cells outside the block that the
-    // end cells couple to contribute oldL0 / oldR0.  With PIPE the five PCR levels of the previous
-    // step's separator system (rr in, xs out) are issued between the elimination chunks.
-    // With PIPE the step-end chain of the PREVIOUS step (xs -> shuffle -> true end values -> shuffle
-    // -> rs) is issued inside the elimination as soon as the last PCR level is done (EARLY): its
-    // ~100 cycles of shuffle and FMA latency then hide behind the chunks' arithmetic.
+    // t_c of one cell (see the header): MODE 1 takes g, g_next as they are, MODE 0 their c-multiples
+    auto tval = [&](double hk_minus, double s, double cg_next) {
+      return (MODE == 2) ? hk_minus : fma(-s, cg_next, hk_minus);
+    };
+    // One step on w[0..N-1] in place; the cells outside the block that the end cells couple to
+    // contribute oldL0 / oldR0 (first step of a segment only).  With PIPE the five PCR levels of
+    // the previous step's separator system (rr in, xs out) are issued between the elimination
+    // chunks, the step-end chain of the PREVIOUS step (xs -> shuffle -> true end values -> shuffle
+    // -> rs) follows as soon as the last level is done (EARLY), and the substitution applies the
+    // delayed correction link by link.
     auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double& rr,
                       double g0_old, double gl_old, double& xsl, double& rs) {
       constexpr bool PIPE = decltype(pipe_tag)::value;
       constexpr bool EARLY = PIPE && NCH >= 8;
-      constexpr bool FSC = CN4;                       // fused substitution + correction
       double x_first = 0.0, x_last = 0.0, x_first_next = 0.0;
       const double w_m_old = w[M];
-      double oldL = oldL0, gL = 0.0, oldR = oldR0, gR = 0.0;
-      double hk_l = 0.0, hk_r = 0.0;                  // CN4: h*kappa of the two cells at the meeting point
+      double hL = 0.0, hR = 0.0, hk_l = 0.0, hk_r = 0.0;
+      double cgL = 0.0, cgR = 0.0;                    // MODE 0: c * g of the cell the chain is at
       int level = 0;
 #pragma unroll
       for (int k = 0; k < NCH; ++k) {
         uint32_t* cur = (k & 1) ? rb : ra;
-        if (CN4 && IT <= 2 && k == 0) {
-          TC::wait(ra); chunk_ld_after<TC>(t_eb + 8 * IT, rb, w[0]);
-        } else if (CN4 && IT <= 2) {
-          if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, ra, gL); }
-          else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, rb, gL); }
-        } else {
-          if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, ra); }
-          else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : next_region, rb); }
-        }
+        // prefetch of the next chunk, pinned ahead of this chunk's arithmetic (chunk_ld_after)
+        if (k == 0) { TC::wait(ra); chunk_ld_after<TC>(t_lk + 8 * IT, rb, w[0]); }
+        else if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_lk + 8 * IT * (k + 1) : next_region, ra, hL); }
+        else            { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_lk + 8 * IT * (k + 1) : next_region, rb, hL); }
         // One PCR level per chunk.  Warps issue in order, so the level's shuffles are issued HERE and
         // their consumer sits after the chunk's cell work: the ~26-cycle shuffle latency is covered.
-        double rm = 0.0, rp = 0.0;
+        double rm = 0.0, rp = 0.0, fa = 0.0, fg = 0.0;
         const bool lvl = PIPE && k < 5;
-        if (lvl) { rm = shfl_up(rr, 1 << k); rp = shfl_dn(rr, 1 << k); }
-        if (EARLY && k == 5) { rr *= K(12, R.invD); xsl = shfl_up(rr, 1); }      // rr now holds xs
+        if (lvl) { rm = shfl_up(rr, 1 << k); rp = shfl_dn(rr, 1 << k); fa = K(K_AL + k); fg = K(K_GA + k); }
+        if (EARLY && k == 5) { rr *= K(K_INVD); xsl = shfl_up(rr, 1); }      // rr now holds xs
         if (EARLY && k == 6) {
-          x_last = fma(-K(22, UL), rr, fma(-K(21, VL), xsl, gl_old));            // true values of the finished step
-          x_first = fma(-K(20, U0), rr, fma(-K(19, V0), xsl, g0_old));
+          x_last = fma(-K(K_UL), rr, fma(-K(K_VL), xsl, gl_old));            // true values of the finished step
+          x_first = fma(-K(K_U0), rr, fma(-K(K_V0), xsl, g0_old));
           x_first_next = shfl_dn(x_first, 1);
         }
         if (EARLY && k == 7) {
           if (lane == 31) x_first_next = 0.0;
-          rs = fma(K(17, R.sbup), x_first_next, fma(K(16, R.sbdi), rr, fma(K(15, R.sblo), x_last, K(18, R.bsep))));
+          rs = fma(K(K_SBUP), x_first_next, fma(K(K_SBDI), rr, fma(K(K_SBLO), x_last, K(K_BSEP))));
         }
 #pragma unroll
         for (int ii = 0; ii < IT; ++ii) {
           const int i = k * IT + ii;
-          if (CN4) {
-            // h = g - l h_prev ; t = h kappa - g - s g_next : w <- t, so that the substitution
-            // z = t - s z_next below yields (1/theta) T^-1 g - g directly (4 operations per cell)
-            {
-              const int c = i;
-              const double l = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1);
-              const double gc = w[c];
-              const double gn = (c == M - 1) ? w_m_old : w[c + 1];
-              if (i == 0) {
-                gL = gc + K(23, R.bfirst);
-                if (!PIPE) gL = fma(-sS[0], oldL0, gL);
-              } else {
-                gL = fma(-l, gL, gc);
-              }
-              if (c == M - 1) { hk_l = gL * kap; w[c] = fma(-sr[c], gn, hk_l - gc); }
-              else w[c] = fma(-sr[c], gn, fma(gL, kap, -gc));
-            }
-            if (i < N - M) {
-              const int c = N - 1 - i;
-              const double l = chunk_dbl(cur, 4 * ii + 2), kap = chunk_dbl(cur, 4 * ii + 3);
-              const double gc = w[c];
-              if (i == 0) {
-                gR = gc;
-                if (!PIPE) gR = fma(-sS[32], oldR0, gR);
-              } else {
-                gR = fma(-l, gR, gc);
-              }
-              if (c == M) { hk_r = gR * kap; w[c] = fma(-sr[c], w[c - 1], hk_r - gc); }
-              else w[c] = fma(-sr[c], w[c - 1], fma(gR, kap, -gc));
-            }
-          } else {
           {
-            const int c = i;
-            const double e = chunk_dbl(cur, 4 * ii), b = chunk_dbl(cur, 4 * ii + 1);
-            const double wc = w[c];
-            const double wn = (c == M - 1) ? w_m_old : w[c + 1];
-            double r = rhs_cell<(MODE == 3 ? 1 : MODE)>(e, sr[c], b, oldL, wc, wn, cth);
-            if (c == 0) r += R.bfirst;
-            gL = (i == 0) ? r : fma(-e, gL, r);
-            w[c] = gL;
-            oldL = wc;
+            const int c = i;                          // left cell, eliminated top-down
+            const double l = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1);
+            const double gc = w[c];
+            const double gn = (c == M - 1) ? w_m_old : w[c + 1];
+            if (i == 0) {
+              hL = gc + K(K_BFIRST);
+              if (!PIPE) hL = fma(-K(K_OML), oldL0, hL);
+              if (MODE == 0) cgL = cth * gc;
+            } else {
+              hL = fma(-l, hL, gc);
+            }
+            const double cg = (MODE == 0) ? cgL : gc, cgn = (MODE == 0) ? cth * gn : gn;
+            if (c == M - 1) { hk_l = hL * kap; w[c] = tval(MODE == 2 ? hk_l : hk_l - cg, sr[c], cgn); }
+            else w[c] = tval(MODE == 2 ? hL * kap : fma(hL, kap, -cg), sr[c], cgn);
+            cgL = cgn;
           }
           if (i < N - M) {
-            const int c = N - 1 - i;
-            const double e = chunk_dbl(cur, 4 * ii + 2), b = chunk_dbl(cur, 4 * ii + 3);
-            const double wc = w[c];
-            double r = rhs_cell<(MODE == 3 ? 1 : MODE)>(e, sr[c], b, oldR, wc, w[c - 1], cth);
-            gR = (i == 0) ? r : fma(-e, gR, r);
-            w[c] = gR;
-            oldR = wc;
-          }
+            const int c = N - 1 - i;                  // right cell, eliminated bottom-up
+            const double l = chunk_dbl(cur, 4 * ii + 2), kap = chunk_dbl(cur, 4 * ii + 3);
+            const double gc = w[c];
+            const double gp = w[c - 1];
+            if (i == 0) {
+              hR = gc;
+              if (!PIPE) hR = fma(-K(K_OMR), oldR0, hR);
+              if (MODE == 0) cgR = cth * gc;
+            } else {
+              hR = fma(-l, hR, gc);
+            }
+            const double cg = (MODE == 0) ? cgR : gc, cgp = (MODE == 0) ? cth * gp : gp;
+            if (c == M) { hk_r = hR * kap; w[c] = tval(MODE == 2 ? hk_r : hk_r - cg, sr[c], cgp); }
+            else w[c] = tval(MODE == 2 ? hR * kap : fma(hR, kap, -cg), sr[c], cgp);
+            cgR = cgp;
           }
         }
-        if (lvl) { rr = fma(K(7 + k, R.ga[k]), rp, fma(K(2 + k, R.al[k]), rm, rr)); level = k + 1; }
+        if (lvl) { rr = fma(fg, rp, fma(fa, rm, rr)); level = k + 1; }
       }
       if (PIPE) {
 #pragma unroll
@@ -887,30 +812,33 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
           if (l >= level) {
             const int s = 1 << l;
             const double rm = shfl_up(rr, s), rp = shfl_dn(rr, s);
-            rr = fma(K(7 + l, R.ga[l]), rp, fma(K(2 + l, R.al[l]), rm, rr));
+            rr = fma(K(K_GA + l), rp, fma(K(K_AL + l), rm, rr));
           }
         }
         if (!EARLY) {
-          rr *= K(12, R.invD);                       // rr now holds xs
+          rr *= K(K_INVD);                           // rr now holds xs
           xsl = shfl_up(rr, 1);
-          x_last = fma(-K(22, UL), rr, fma(-K(21, VL), xsl, gl_old));
-          x_first = fma(-K(20, U0), rr, fma(-K(19, V0), xsl, g0_old));
+          x_last = fma(-K(K_UL), rr, fma(-K(K_VL), xsl, gl_old));
+          x_first = fma(-K(K_U0), rr, fma(-K(K_V0), xsl, g0_old));
           x_first_next = shfl_dn(x_first, 1);
           if (lane == 31) x_first_next = 0.0;
-          rs = fma(K(17, R.sbup), x_first_next, fma(K(16, R.sbdi), rr, fma(K(15, R.sblo), x_last, K(18, R.bsep))));
+          rs = fma(K(K_SBUP), x_first_next, fma(K(K_SBDI), rr, fma(K(K_SBLO), x_last, K(K_BSEP))));
         }
       }
-      if (PIPE && FSC) {
-        // substitution outwards from the meeting point with the delayed correction riding on every
-        // link: the chain runs on the uncorrected values zL / zR, the corrected ones go to w
-        const double zM = fma(fma(-sr[M], hk_l, hk_r), delta, -w_m_old);
+      // meeting point: z_M = (hk_r - s_M hk_l) delta - c g_M
+      double zM = fma(-sr[M], hk_l, hk_r) * delta;
+      if (MODE == 1) zM -= w_m_old;
+      if (MODE == 0) zM = fma(-cth, w_m_old, zM);
+      if (PIPE) {
+        // substitution outwards with the delayed correction riding on every link: the chain runs on
+        // the uncorrected values zL / zR, the corrected ones go to w
         const double xs = rr;
         double zL = zM, zR = zM;
 #pragma unroll
         for (int k = 0; k < NCH; ++k) {
           uint32_t* cur = (k & 1) ? rb : ra;
-          if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra, zL); }
-          else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb, zL); }
+          if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_lk, ra, zL); }
+          else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_lk, rb, zL); }
           // links first, then the xsl products of the whole chunk, then the xs products: consecutive
           // FMAs that share an operand can take it from the operand-reuse cache instead of the
           // register file, whose bandwidth is what bounds these loops (fp64_operands.cu)
@@ -940,8 +868,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
           }
         }
       } else {
-        if (CN4) w[M] = fma(fma(-sr[M], hk_l, hk_r), delta, -w_m_old);
-        else w[M] = fma(-sr[M], w[M - 1], w[M]) * delta;
+        w[M] = zM;
 #pragma unroll
         for (int j = 0; j < M; ++j) {
           const int cl = M - 1 - j, cr = M + 1 + j;
@@ -952,7 +879,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
     };
 
     int64_t remaining = nsteps, n_ckpt = 0;
-    TC::ld(t_eb, ra);                               // first (e, b) chunk
+    TC::ld(t_lk, ra);                               // first (l, kappa) chunk
     while (remaining > 0) {
       const bool ck = ckpt != nullptr && ckpt_every > 0 && remaining >= ckpt_every;
       const int64_t L = ck ? ckpt_every : remaining; // steps until the true state is needed again
@@ -961,55 +888,28 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       double wr = shfl_dn(w[0], 1);
       if (lane == 0) wl = 0.0;
       if (lane == 31) wr = 0.0;
-      double rs = fma(K(17, R.sbup), wr, fma(K(16, R.sbdi), w[C - 1], fma(K(15, R.sblo), w[N - 1], K(18, R.bsep))));
+      double rs = fma(K(K_SBUP), wr, fma(K(K_SBDI), w[C - 1], fma(K(K_SBLO), w[N - 1], K(K_BSEP))));
       double rr = 0.0, xsl = 0.0;
-      sweeps(std::false_type{}, wl, w[C - 1], t_eb, rr, 0.0, 0.0, xsl, rs);
-      rr = fma(-K(14, R.sup), shfl_dn(w[0], 1), fma(-K(13, R.slo), w[N - 1], rs));
+      sweeps(std::false_type{}, wl, w[C - 1], t_lk, rr, 0.0, 0.0, xsl, rs);
+      rr = fma(-K(K_SUP), shfl_dn(w[0], 1), fma(-K(K_SLO), w[N - 1], rs));
       // -------- pipelined steps: PCR of step n overlaps the sweeps of step n+1
       for (int64_t i = 1; i < L; ++i) {
         sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, w[0], w[N - 1], xsl, rs);
-        double xs = rr;                             // lane 0: V == P1 == 0, its xsl is unused
-        double g0n = 0.0;
-        if (CN4) g0n = shfl_dn(w[0], 1);            // the correction was applied inside the substitution
-#pragma unroll
-        for (int k = 0; k < (CN4 ? 0 : NCH); ++k) { // g' = G + P1 xsl + P2 xs
-          uint32_t* cur = (k & 1) ? rb : ra;
-          if (CN4 && IT <= 2) {
-            if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra, xs); }
-            else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb, xs); }
-          } else {
-            if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, ra); }
-            else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_eb, rb); }
-          }
-#pragma unroll
-          for (int ii = 0; ii < IT; ++ii) {
-            const int i2 = k * IT + ii;
-            w[i2] = fma(chunk_dbl(cur, 4 * ii + 1), xs, fma(chunk_dbl(cur, 4 * ii), xsl, w[i2]));
-            if (i2 < N - M) {
-              const int c = N - 1 - i2;
-              w[c] = fma(chunk_dbl(cur, 4 * ii + 3), xs, fma(chunk_dbl(cur, 4 * ii + 2), xsl, w[c]));
-            }
-          }
-          if (k == 0) g0n = shfl_dn(w[0], 1);       // cells 0 and N-1 are final: start the exchange now
-        }
-        rr = fma(-K(14, R.sup), g0n, fma(-K(13, R.slo), w[N - 1], rs));
+        const double g0n = shfl_dn(w[0], 1);        // lane 31: sup == 0
+        rr = fma(-K(K_SUP), g0n, fma(-K(K_SLO), w[N - 1], rs));
       }
       // -------- end of the segment: finish the last step and materialise the true state
       {
         double xs = rr;
-        if (CN4) {
 #pragma unroll
-          for (int l = 0; l < 5; ++l) {
-            const double rm = shfl_up(xs, 1 << l), rp = shfl_dn(xs, 1 << l);
-            xs = fma(sS[(7 + l) * 32], rp, fma(sS[(2 + l) * 32], rm, xs));
-          }
-          xs *= sS[12 * 32];
-        } else {
-          xs = pcr_solve(rr, R);
+        for (int l = 0; l < 5; ++l) {
+          const double rm = shfl_up(xs, 1 << l), rp = shfl_dn(xs, 1 << l);
+          xs = fma(K(K_GA + l), rp, fma(K(K_AL + l), rm, xs));
         }
-        const double xsl = shfl_up(xs, 1);
+        xs *= K(K_INVD);
+        const double xsl_end = shfl_up(xs, 1);      // lane 0: V == 0, value unused
 #pragma unroll
-        for (int c = 0; c < N; ++c) w[c] = fma(-su[c * 32], xs, fma(-sv[c * 32], xsl, w[c]));
+        for (int c = 0; c < N; ++c) w[c] = fma(-su[c * 32], xs, fma(-sv[c * 32], xsl_end, w[c]));
         w[C - 1] = xs;
       }
       remaining -= L;
@@ -1073,15 +973,23 @@ static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double the
   int sms = 0, max_smem = 0;
   int st = device_limits(sms, max_smem);
   if (st) return st;
-  auto kern = PIPE ? fused_tmem_pipe_kernel<MODE, IT> : fused_tmem_kernel<MODE, IT>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return (int)e;
   int64_t blocks = (pr.P + warps - 1) / warps;
   if (blocks > sms) blocks = sms;                // one CTA per SM: it holds the SM's whole TMEM
   int launch_warps = warps;
   const char* lw = getenv("FVM_FUSED_WARPS");    // experiment: 4 = one warp per scheduler
   if (lw && lw[0] == '4') launch_warps = 4;
-  kern<<<(unsigned)blocks, launch_warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
+  cudaError_t e;
+  if constexpr (PIPE) {
+    auto kern = fused_tmem_pipe_kernel<MODE, IT>;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<(unsigned)blocks, launch_warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
+  } else {
+    auto kern = fused_tmem_kernel<MODE, IT>;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<(unsigned)blocks, launch_warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
+  }
   return (int)cudaGetLastError();
 }
 
@@ -1106,23 +1014,11 @@ static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, 
       if (theta == 1.0) return launch_fused_tmem<2, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
       return launch_fused_tmem<0, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
     }
-    // Crank-Nicolson: the 4-operation sweep (MODE 3); FVM_CN4=0 keeps the 5-operation one (A/B runs)
-    const char* c4 = getenv("FVM_CN4");
-    const char* it4 = getenv("FVM_TMEM_IT");
-    if (theta == 0.5 && !(c4 && c4[0] == '0')) {
-      if (it4 && it4[0] == '1') return launch_fused_tmem<3, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      return launch_fused_tmem<3, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    }
-    const char* its = getenv("FVM_TMEM_IT");     // 4: .x32 loads (experiments); default 2: .x16
+    const char* its = getenv("FVM_TMEM_IT");     // 1: .x8 chunks (experiments); default 2: .x16
     if (its && its[0] == '1') {
       if (theta == 0.5) return launch_fused_tmem<1, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
       if (theta == 1.0) return launch_fused_tmem<2, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
       return launch_fused_tmem<0, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    }
-    if (its && its[0] == '4') {
-      if (theta == 0.5) return launch_fused_tmem<1, 4, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      if (theta == 1.0) return launch_fused_tmem<2, 4, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      return launch_fused_tmem<0, 4, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
     }
     if (theta == 0.5) return launch_fused_tmem<1, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
     if (theta == 1.0) return launch_fused_tmem<2, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
