@@ -1,7 +1,7 @@
 """Parity over cfg 3's FULL run length (10,000 Crank-Nicolson steps) on the stiffest problems of the
 sweep (smallest Peclet number: largest dt*d/h^2, where round-off survives longest), against the
 reference's scipy loop (oracle) and against the longdouble Thomas arbiter.
-    python profiles/microbench/long_run_parity.py > gpurun_out/long_run_parity.txt"""
+    python profiles/microbench/long_run_parity.py [fused|thomas] > gpurun_out/long_run_parity.txt"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np
@@ -15,7 +15,9 @@ pe = wl["a"] / wl["d"]
 idx = np.concatenate([np.argsort(pe)[:pick - 2], np.argsort(pe)[-2:]])     # the stiffest, and two advective ones
 m = BatchedAdvectionDiffusionModel(wl["faces"], wl["a"][idx], wl["d"][idx], wl["k"][idx], "exponential")
 m.set_boundary_conditions(**wl["bc"])
-w, _ = m.run(wl["w0"][idx], 0.5, ns, variant="fused")
+variant = sys.argv[1] if len(sys.argv) > 1 else "fused"
+print("variant", variant)
+w, _ = m.run(wl["w0"][idx], 0.5, ns, variant=variant)
 w = w.cpu().numpy()
 As, Bs, betas = [], [], []
 for n, p in enumerate(idx):
