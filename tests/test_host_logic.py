@@ -107,3 +107,31 @@ def test_workloads_are_shard_invariant():
     f = W.graded_faces(1024)
     h = np.diff(f)
     assert f[0] == 0 and abs(f[-1] - 1) < 1e-15 and abs(h[0] / h[-1] - 100) < 1e-9
+
+
+def test_bench_contract_pieces():
+    """bench.py without a GPU: argument defaults, the workload description, and the committed ncu
+    capture that `roofline.traffic` is read from (within 5 % of the algorithmic bytes of a launch)."""
+    import importlib.util
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_under_test", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    argv, sys.argv = sys.argv, ["bench.py"]
+    try:
+        spec.loader.exec_module(bench)
+        args = bench.parse()
+    finally:
+        sys.argv = argv
+    assert (args.gpus, args.impl, args.workload, args.problems, args.cells) == (1, "b200", "cfg3", 65536, 1024)
+    assert args.warmup >= 3 and args.steps >= 1 and args.checkpoint_every == 1000 and args.inner is None
+    args.inner = 10000
+    cfg = bench.config(args)
+    assert "workload" in cfg and "model" not in cfg and cfg["theta_steps_per_bench_step"] == 10000
+    assert bench.METRIC == "fp64 cell-updates/sec (theta-step)" and bench.UNIT == "cell-updates/s"
+    traffic = bench.ncu_traffic(bench.FUSED_SUMMARY)
+    algorithmic = (16.0 + 8.0 * 10) * 65536 * 1024
+    assert traffic is not None and abs(traffic / algorithmic - 1.0) < 0.05
+    assert bench.ncu_traffic("no_such_capture.txt") is None
+    peaks, src = bench.measured_peaks()
+    assert peaks["hbm_gbs"] > 1000 and "sm_max_mhz" in peaks and src
