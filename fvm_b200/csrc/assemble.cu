@@ -1,5 +1,6 @@
 // fvm_assemble + fvm_theta_factor: once-per-model work (not on the per-step path).
 #include "fvm_device.cuh"
+#include "dd.cuh"
 
 namespace fvm {
 
@@ -48,22 +49,27 @@ __global__ void __launch_bounds__(128) theta_factor_kernel(
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
   const double dt_theta = mul(dt[p], theta);
-  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
-  double q_prev = 0.0, inv = 1.0;
+  const double rth = 1.0 / theta;
+  // The pivot recurrence runs in double-double and every factor is rounded ONCE: the step
+  // kernel applies the same factors at every step, so a chain's correlated rounding error would
+  // grow linearly with the step count (dd.cuh).
+  dd s_prev = dd_make(0.0), inv_prev = dd_make(0.0);
   for (int64_t j = 0; j < J; ++j) {
     Row m;
     const int64_t o = p * m_ps + j * m_cs;
     m.lo = lo[o]; m.di = di[o]; m.up = up[o];
     Row a = theta_lhs_row(m, dt_theta, alpha_of(j, J, alpha_left, alpha_right));
-    inv = 1.0 / (a.di - a.lo * q_prev);
-    q_prev = a.up * inv;
+    const dd inv = dd_recip(dd_add_d(dd_neg(dd_mul_d(s_prev, a.lo)), a.di));
     const int64_t f = p * f_ps + j * f_cs;
-    fp[f] = a.lo * inv;
-    fq[f] = q_prev;
-    fb[f] = inv * (rth - cth * a.di);
-    if (j == 0 && bt_left) bt_left[p] = beta_left ? beta_left[p] * inv : 0.0;
+    fp[f] = dd_round(dd_mul_d(inv_prev, a.lo));      // l_j     = A_j,j-1 / pivot_{j-1}
+    fb[f] = dd_round(dd_mul_d(inv, rth));            // kappa_j = 1 / (theta pivot_j)
+    s_prev = dd_mul_d(inv, a.up);
+    fq[f] = dd_round(s_prev);                        // s_j     = A_j,j+1 / pivot_j
+    inv_prev = inv;
   }
-  if (bt_right) bt_right[p] = beta_right ? beta_right[p] * inv : 0.0;
+  // beta enters the elimination un-normalised: A yhat = w/theta + beta, h = theta * (that)
+  if (bt_left) bt_left[p] = beta_left ? theta * beta_left[p] : 0.0;
+  if (bt_right) bt_right[p] = beta_right ? theta * beta_right[p] : 0.0;
 }
 
 static int check_problem(const fvm_problem* pr) {

@@ -26,7 +26,7 @@
 // owned cell, so a launch needs only the mesh, the per-problem scalars and the state.
 #include "fvm_device.cuh"
 #include "tmem.cuh"
-#include <cstdlib>
+#include "dd.cuh"
 #include <type_traits>
 
 namespace fvm {
@@ -280,165 +280,53 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
   }
 }
 
-// Set-up shared by the tensor-memory kernels (C = 32, N = 31 interior cells per lane, twisted at
-// M = 16): assembles this lane's rows of A, factors the interior block from both ends (e, b ->
-// tensor memory at t_eb; s -> sS and the registers sr), computes both spikes (sv = V, su = U in
-// shared memory, natural cell order), the separator system and its PCR factors.
-//
-// LK (the 4-operation Crank-Nicolson sweep of fused_tmem_pipe_kernel<3, IT>): tensor memory gets
-// (l, kappa) instead of (e, b) -- l = the un-normalised elimination factor A_c,prev / pivot_prev,
-// kappa = 1 / (theta pivot_c) -- R.bfirst = theta beta_0 (un-normalised), and om_l / om_r return
-// (1 - theta) times the coupling of the block's end cells to the two separators.
-template <bool LK>
-__device__ __forceinline__ void tmem_setup_common(const fvm_problem& pr, int64_t p, int lane, double dt_p, double theta,
-                                                  uint32_t t_eb, double* sS, double* sv, double* su, Reduced& R,
-                                                  double (&sr)[31], double& delta, double& om_l, double& om_r) {
-  constexpr int C = 32, N = 31, M = 16;
-  const int64_t J = pr.J;
-  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
-    double sdi = 1.0;
-    {
-      const double dt_theta = mul(dt_p, theta);
-      double beta_l = 0.0, beta_r = 0.0;
-      if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
-        beta_l = dvd(pr.left_flux[p], sub(pr.faces[1], pr.faces[0]));
-      if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
-        beta_r = dvd(-pr.right_flux[p], sub(pr.faces[J], pr.faces[J - 1]));
-      R.bfirst = 0.0; R.bint = 0.0; R.bsep = 0.0; R.rb_c = -1;
-      const int64_t j0 = (int64_t)lane * C;
-      Row asep;
-      auto row_of = [&](int c, const Face& FL, const Face& FR) {
-        const int64_t j = j0 + c;
-        Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;    // padding rows (j >= J) are identity
-        if (j < J) {
-          Row m = problem_row(pr, p, j, FL, FR);
-          a = theta_lhs_row(m, dt_theta, alpha_of(j, J, pr.alpha_left, pr.alpha_right));
-        }
-        return a;
-      };
-      // sliding windows over faces, one per sweep direction: one expm1 and one face (5 divisions)
-      // per row instead of three and two
-      double lD0 = cell_D(pr, p, j0);
-      Face lFL = problem_face(pr, p, j0 - 1, cell_D(pr, p, j0 - 1), lD0);
-      double rD0 = cell_D(pr, p, j0 + C - 1);                                 // the separator's cell
-      Face rFR = problem_face(pr, p, j0 + C - 1, rD0, cell_D(pr, p, j0 + C));
-      {
-        const double Dm = cell_D(pr, p, j0 + C - 2);
-        const Face F = problem_face(pr, p, j0 + C - 2, Dm, rD0);
-        asep = row_of(C - 1, F, rFR);                                         // the separator's row
-        rFR = F; rD0 = Dm;
-      }
-      double sl_prev = 0.0, sr_prev = 0.0, gv_prev = 0.0, gu_prev = 0.0;
-      double invl_prev = 0.0, invr_prev = 0.0;
-      om_l = 0.0; om_r = 0.0;
-#pragma unroll 1
-      for (int i = 0; i < M; ++i) {
-        {                                            // left cell i: top-down elimination
-          const double lDp = cell_D(pr, p, j0 + i + 1);
-          const Face lFR = problem_face(pr, p, j0 + i, lD0, lDp);
-          const Row a = row_of(i, lFL, lFR);
-          lD0 = lDp; lFL = lFR;
-          const double inv = 1.0 / (a.di - a.lo * sl_prev);
-          const double e = a.lo * inv;
-          sl_prev = a.up * inv;
-          gv_prev = (i == 0) ? e : -e * gv_prev;     // elimination sweep of the left spike
-          sS[i * 32] = sl_prev; sv[i * 32] = gv_prev; su[i * 32] = 0.0;
-          if (LK) {
-            tmem_st_2d(t_eb + 8 * i, a.lo * invl_prev, inv * rth);
-            if (i == 0) om_l = (1.0 - theta) * a.lo;
-            if ((int64_t)lane * C + i == 0) R.bfirst = theta * beta_l;
-            invl_prev = inv;
-          } else {
-            tmem_st_2d(t_eb + 8 * i, e, inv * (rth - cth * a.di));
-            if ((int64_t)lane * C + i == 0) R.bfirst = beta_l * inv;
-          }
-        }
-        if (i < N - M) {                             // right cell 30-i: bottom-up elimination
-          const int c = N - 1 - i;
-          const double rDm = cell_D(pr, p, j0 + c - 1);
-          const Face rFL = problem_face(pr, p, j0 + c - 1, rDm, rD0);
-          const Row a = row_of(c, rFL, rFR);
-          rD0 = rDm; rFR = rFL;
-          const double inv = 1.0 / (a.di - a.up * sr_prev);
-          const double e = a.up * inv;
-          sr_prev = a.lo * inv;
-          gu_prev = (i == 0) ? e : -e * gu_prev;     // elimination sweep of the right spike
-          sS[c * 32] = sr_prev; su[c * 32] = gu_prev; sv[c * 32] = 0.0;
-          if (LK) {
-            tmem_st_2d(t_eb + 8 * i + 4, a.up * invr_prev, inv * rth);
-            if (i == 0) om_r = (1.0 - theta) * a.up;
-            invr_prev = inv;
-          } else {
-            tmem_st_2d(t_eb + 8 * i + 4, e, inv * (rth - cth * a.di));
-          }
-        }
-      }
-      R.slo = asep.lo; sdi = asep.di; R.sup = asep.up;
-      const int64_t js = (int64_t)lane * C + C - 1;
-      if (js == J - 1) R.bsep += beta_r;
-      R.sblo = -cth * R.slo; R.sbdi = rth - cth * sdi; R.sbup = -cth * R.sup;
-    }
-#pragma unroll
-    for (int c = 0; c < N; ++c) sr[c] = sS[c * 32];
-    delta = 1.0 / (1.0 - sr[M] * sr[M - 1]);
-    {
-      // substitution sweeps of both spikes, outwards from the meeting point
-      double xv = (sv[M * 32] - sr[M] * sv[(M - 1) * 32]) * delta;
-      double xu = (su[M * 32] - sr[M] * su[(M - 1) * 32]) * delta;
-      sv[M * 32] = xv; su[M * 32] = xu;
-      double lv = xv, lu = xu;
-#pragma unroll 1
-      for (int c = M - 1; c >= 0; --c) {
-        const double sc = sS[c * 32];
-        lv = sv[c * 32] - sc * lv; lu = su[c * 32] - sc * lu;
-        sv[c * 32] = lv; su[c * 32] = lu;
-      }
-      double rv = xv, ru = xu;
-#pragma unroll 1
-      for (int c = M + 1; c < N; ++c) {
-        const double sc = sS[c * 32];
-        rv = sv[c * 32] - sc * rv; ru = su[c * 32] - sc * ru;
-        sv[c * 32] = rv; su[c * 32] = ru;
-      }
-      // lv, lu = spikes at cell 0; rv, ru = spikes at cell N-1
-      const double v0n = shfl_dn(lv, 1), u0n = shfl_dn(lu, 1);
-      const double RL = -R.slo * rv;
-      const double RD = sdi - R.slo * ru - R.sup * v0n;          // sup == 0 on lane 31
-      const double RU = -R.sup * u0n;
-      pcr_factor(lane, RL, RD, RU, R);
-    }
-}
-
 // ------------------------------------------------------------------------------------------
-// Tensor-memory variant, C = 32 (512 < J <= 1024), 8 warps per CTA, one CTA per SM.
+// Tensor-memory kernel, C = 32 (512 < J <= 1024), 8 warps per CTA, one CTA per SM: the default
+// for cfg 3.  Coefficients live in TENSOR MEMORY: TMEM (256 KB/SM) is idle in this workload --
+// there is no MMA -- and its tcgen05.ld path is separate from, and wider than, the 128 B/clk
+// shared-memory pipe (profiles/microbench/r01_tmem_bw_b200.txt).
 //
-// A step of the shared-memory kernel is bound by the latency of its dependent-FMA chains
-// (31 links forward, 30 backward, ~9 cycles each; profiles/r01_fused_v3_tmem.summary.txt), not
-// by the fp64 pipe.  This kernel therefore factors each lane's interior block T with a TWISTED
-// factorisation: cells 0..15 are eliminated top-down, cells 30..16 bottom-up, the two sweeps
-// meet between cells 15 and 16, and substitution runs outwards from there.  Same flops, same
-// five coefficients per cell, but two independent chains of half the length: 16 + 1 + 16
-// dependent links per step instead of 61.  Per cell:  e = elimination coefficient (times the
-// neighbour the sweep comes from), s = substitution coefficient (times the neighbour the
-// sweep moves towards), b = diagonal of inv*B; inv*B's off-diagonals are -c*e and -c*s.
+// 1. TWISTED factorisation of each lane's interior block T: cells 0..14 are eliminated top-down,
+//    cells 30..16 bottom-up, the sweeps meet AT cell 15 (its pivot takes a term from either side)
+//    and substitution runs outwards from there: two independent chains of half the length.
+// 2. NO RIGHT-HAND SIDE.  B = I/theta - c A (c = (1-theta)/theta) gives A^-1 B = (1/theta) A^-1 - c I.
+//    With the un-normalised factors l_c = A_c,prev / pivot_prev, kappa_c = 1 / (theta pivot_c),
+//    s_c = A_c,next / pivot_c and z = yhat - c g, where yhat = (1/theta) T^-1 g:
+//        elimination   h_c = g_c - l_c h_prev                          (1 FMA, the chain)
+//                      t_c = h_c kappa_c - c g_c - c s_c g_next        (off the chain, written over g_c)
+//        substitution  z_c = t_c - s_c z_next                          (1 FMA, the chain)
+//    4 operations per cell for Crank-Nicolson, 3 for implicit Euler, 5 in general.
+// 3. DELAYED CORRECTION.  The separator PCR is a pure latency chain.  The step is linear with
+//    constant coefficients, so the kernel keeps, between steps, the UNCORRECTED block solutions g
+//    (true state x = g - V xsl - U xs) and advances
+//        g' = (1/theta) T^-1 g - c g  +  P1 xsl  +  P2 xs ,   P1 = -(1/theta) T^-1 V,  P2 = -(1/theta) T^-1 U ,
+//    so the PCR of step n runs interleaved with the elimination chunks of step n+1 and the
+//    correction rides on the substitution links.  V and U stay in shared memory for the points
+//    where the true state is needed (checkpoints, end of the launch).
+// 4. SEPARATOR ROWS in yhat as well:  A yhat = x/theta + beta,  x' = yhat - c x.  Row of separator s:
+//        R yhat_s = xs/theta + beta_s - slo ghat_last - sup ghat_first(next lane),   ghat = g' + c g_old
+//    (ghat = (1/theta) T^-1 x_int is the uncorrected block solution of yhat), then x'_s = yhat_s - c xs.
+//    Nothing of size dt*d/h^2 is multiplied by a state value and cancelled, and the true end values
+//    of the blocks are not needed.
+// 5. SET-UP IN DOUBLE-DOUBLE (dd.cuh).  The loop applies the same rounded constants 10^4 times, so
+//    their errors are systematic.  (a) The pivot chain runs in dd and l, kappa, s, delta are
+//    rounded ONCE.  (b) The spikes V, U, the separator system built from their ends and its PCR
+//    factors come from the UNROUNDED factors, chains and intermediates in dd, and are rounded once
+//    at the end: the spikes carry the separator values (the large part of the solution of a stiff
+//    block) into the interior, so they have to be those of the exact block.  Spikes "consistent"
+//    with the rounded factors were tried and are 100x worse (3.5e-11 against 2e-13 after 10,000
+//    steps on cfg 3's stiffest problems): the rounding of l, kappa, s then acts on terms of size
+//    (dt d/h^2) x instead of on the small uncorrected block solutions.  (c) P1, P2 = -Lhat(V, U)
+//    use the loop's own rounded factors with dd chains.
 //
 // TMEM layout per warp (256 columns of its lane quadrant), in the order the loop consumes it:
-//   columns [0,128)  : slot i = (e, b) of left cell i, then (e, b) of right cell 30-i   (8 columns)
-//   columns [128,256): slot i = (v, u) of left cell i, then (v, u) of right cell 30-i
-// s lives in registers (it is read twice per step).  IT = slots per tcgen05.ld (2 -> .x16,
-// 4 -> .x32); loads are double-buffered so the next chunk is in flight while one is consumed.
-template <int IT> struct TmemChunk;
-template <> struct TmemChunk<4> {
-  static constexpr int REGS = 32;
-  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[32]) { tmem_ld_x32(t, r); }
-  static __device__ __forceinline__ void wait(uint32_t (&r)[32]) { tmem_wait_ld_x32(r); }
-};
-template <> struct TmemChunk<1> {
-  static constexpr int REGS = 8;
-  static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[8]) { tmem_ld_x8(t, r); }
-  static __device__ __forceinline__ void wait(uint32_t (&r)[8]) { tmem_wait_ld_x8(r); }
-};
-template <> struct TmemChunk<2> {
+//   columns [0,128)  : slot i < 15 = (l, kappa) of left cell i, then of right cell 30-i  (8 columns);
+//                      slot 15 = (l_down, kappa) and (l_up, -) of the middle cell
+//   columns [128,256): slot 0 = (P1, P2) of the middle cell; slot j = (P1, P2) of left cell 15-j,
+//                      then of right cell 15+j                                         (substitution order)
+// s lives in registers (it is read twice per step); loads are .x16 chunks, double-buffered.
+// MODE 0: any theta in (0,1];  1: Crank-Nicolson;  2: implicit Euler.
+struct TmemChunk {
   static constexpr int REGS = 16;
   static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[16]) { tmem_ld_x16(t, r); }
   static __device__ __forceinline__ void wait(uint32_t (&r)[16]) { tmem_wait_ld_x16(r); }
@@ -448,191 +336,246 @@ template <> struct TmemChunk<2> {
 // computed from `dep` afterwards is ordered after the ISSUE of the load.  This pins a prefetch
 // ahead of the arithmetic it is meant to overlap; the compiler otherwise sinks the load down to
 // its wait to save registers, and every chunk then pays the tensor-memory latency.
-template <class TC, int REGS>
-__device__ __forceinline__ void chunk_ld_after(uint32_t t, uint32_t (&r)[REGS], double& dep) {
-  TC::ld(t, r);
+__device__ __forceinline__ void chunk_ld_after(uint32_t t, uint32_t (&r)[16], double& dep) {
+  TmemChunk::ld(t, r);
   asm volatile("" : "+d"(dep));
 }
 
 // k-th double of a chunk (two 32-bit columns each)
 __device__ __forceinline__ double chunk_dbl(const uint32_t* r, int k) { return __hiloint2double((int)r[2 * k + 1], (int)r[2 * k]); }
 
-template <int MODE, int IT>
-__global__ void __launch_bounds__(kFusedThreads, 1)
-fused_tmem_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
-                  int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
-  constexpr int C = 32, N = 31, M = 16;              // left cells 0..M-1, right cells N-1..M
-  constexpr int NCH = M / IT;                        // chunks per region
-  using TC = TmemChunk<IT>;
-  extern __shared__ double smem[];
-  __shared__ uint32_t tmem_base_slot;
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int warps = blockDim.x >> 5;
-  double* sS = smem + (size_t)warp * (3 * N * 32) + lane;        // set-up staging: s, v, u
-  double* sv = sS + N * 32;
-  double* su = sv + N * 32;
-  const int64_t J = pr.J;
-  const double cth = (1.0 - theta) / theta;
-
-  if (warp == 0) tmem_alloc_512(&tmem_base_slot);
-  tmem_fence_before_sync();
-  __syncthreads();
-  tmem_fence_after_sync();
-  const uint32_t tmem_base = tmem_base_slot;
-  const uint32_t t_eb = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
-  const uint32_t t_vu = t_eb + 128;
-
-  for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
-    // ------------------------------------------------------------------ set-up (once)
-    Reduced R;
-    double delta;
-    double sr[N];                                    // s for the whole launch
-    double om_unused_l, om_unused_r;
-    tmem_setup_common<false>(pr, p, lane, dt[p], theta, t_eb, sS, sv, su, R, sr, delta, om_unused_l, om_unused_r);
-    {
-#pragma unroll 1
-      for (int i = 0; i < M; ++i) {
-        tmem_st_2d(t_vu + 8 * i, sv[i * 32], su[i * 32]);
-        if (i < N - M) tmem_st_2d(t_vu + 8 * i + 4, sv[(N - 1 - i) * 32], su[(N - 1 - i) * 32]);
-      }
-    }
-    tmem_wait_st();
-    __syncwarp();
-
-    double w[C];
-    load_state<C>(w_io + p * J, J, lane, w);
-
-    // ------------------------------------------------------------------ time loop
-    uint32_t ra[TC::REGS], rb[TC::REGS];
-    int64_t until_ckpt = ckpt_every, n_ckpt = 0;
-    TC::ld(t_eb, ra);                               // first (e, b) chunk of the first step
-    for (int64_t n = 0; n < nsteps; ++n) {
-      double wl = shfl_up(w[C - 1], 1);
-      double wr = shfl_dn(w[0], 1);
-      if (lane == 0) wl = 0.0;
-      if (lane == 31) wr = 0.0;
-      const double w_m_old = w[M], w_last_old = w[N - 1], w_sep = w[C - 1];
-      double oldL = wl, gL = 0.0;                   // left sweep comes from cell -1 (previous separator)
-      double oldR = w_sep, gR = 0.0;                // right sweep comes from cell 31 (own separator)
-      // elimination: chunk k is consumed from one buffer while chunk k+1 (or the first (v, u)
-      // chunk of the correction) is already on its way into the other
-#pragma unroll
-      for (int k = 0; k < NCH; ++k) {
-        uint32_t* cur = (k & 1) ? rb : ra;
-        if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : t_vu, ra); }
-        else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_eb + 8 * IT * (k + 1) : t_vu, rb); }
-#pragma unroll
-        for (int ii = 0; ii < IT; ++ii) {
-          const int i = k * IT + ii;
-          {
-            const int c = i;
-            const double e = chunk_dbl(cur, 4 * ii), b = chunk_dbl(cur, 4 * ii + 1);
-            const double wc = w[c];
-            const double wn = (c == M - 1) ? w_m_old : w[c + 1];
-            double r = rhs_cell<MODE>(e, sr[c], b, oldL, wc, wn, cth);
-            if (c == 0) r += R.bfirst;
-            gL = (i == 0) ? r : fma(-e, gL, r);
-            w[c] = gL;
-            oldL = wc;
-          }
-          if (i < N - M) {
-            const int c = N - 1 - i;
-            const double e = chunk_dbl(cur, 4 * ii + 2), b = chunk_dbl(cur, 4 * ii + 3);
-            const double wc = w[c];
-            double r = rhs_cell<MODE>(e, sr[c], b, oldR, wc, w[c - 1], cth);
-            gR = (i == 0) ? r : fma(-e, gR, r);
-            w[c] = gR;
-            oldR = wc;
-          }
-        }
-      }
-      const double rs = fma(R.sbup, wr, fma(R.sbdi, w_sep, fma(R.sblo, w_last_old, R.bsep)));
-      // the sweeps meet between cells M-1 and M; substitute outwards
-      w[M] = fma(-sr[M], w[M - 1], w[M]) * delta;
-#pragma unroll
-      for (int j = 0; j < M; ++j) {
-        const int cl = M - 1 - j, cr = M + 1 + j;
-        w[cl] = fma(-sr[cl], w[cl + 1], w[cl]);
-        if (cr < N) w[cr] = fma(-sr[cr], w[cr - 1], w[cr]);
-      }
-      const double g0n = shfl_dn(w[0], 1);
-      const double rr = fma(-R.sup, g0n, fma(-R.slo, w[N - 1], rs));
-      const double xs = pcr_solve(rr, R);
-      const double xsl = shfl_up(xs, 1);            // lane 0: v == 0, value unused
-      // correction; NCH is even, so the first (v, u) chunk sits in ra again
-#pragma unroll
-      for (int k = 0; k < NCH; ++k) {
-        uint32_t* cur = (k & 1) ? rb : ra;
-        if (k & 1) { TC::wait(rb); TC::ld(k + 1 < NCH ? t_vu + 8 * IT * (k + 1) : t_eb, ra); }
-        else       { TC::wait(ra); TC::ld(k + 1 < NCH ? t_vu + 8 * IT * (k + 1) : t_eb, rb); }
-#pragma unroll
-        for (int ii = 0; ii < IT; ++ii) {
-          const int i = k * IT + ii;
-          w[i] = fma(-chunk_dbl(cur, 4 * ii + 1), xs, fma(-chunk_dbl(cur, 4 * ii), xsl, w[i]));
-          if (i < N - M) {
-            const int c = N - 1 - i;
-            w[c] = fma(-chunk_dbl(cur, 4 * ii + 3), xs, fma(-chunk_dbl(cur, 4 * ii + 2), xsl, w[c]));
-          }
-        }
-      }
-      w[C - 1] = xs;
-
-      if (ckpt != nullptr && ckpt_every > 0 && --until_ckpt == 0) {
-        until_ckpt = ckpt_every;
-        store_state<C>(ckpt + (n_ckpt * pr.P + p) * J, J, lane, w);
-        ++n_ckpt;
-      }
-    }
-    TC::wait(ra);                                   // drain the prefetch of the step that never comes
-    store_state<C>(w_io + p * J, J, lane, w);
-    __syncwarp();
-  }
-
-  tmem_fence_before_sync();
-  __syncthreads();
-  if (warp == 0) tmem_dealloc_512(tmem_base);
+constexpr int kPipeN = 31, kPipeMid = 15;           // interior cells per lane; the cell the two sweeps meet at
+// column offsets of cell c inside the (l, kappa) region and inside the (P1, P2) region
+__device__ __forceinline__ uint32_t pipe_col_lk(int c) {
+  return (uint32_t)(c <= kPipeMid ? 8 * c : 8 * (kPipeN - 1 - c) + 4);
+}
+__device__ __forceinline__ uint32_t pipe_col_pp(int c) {
+  return (uint32_t)(c <= kPipeMid ? 8 * (kPipeMid - c) : 8 * (c - kPipeMid) + 4);
 }
 
-// ------------------------------------------------------------------------------------------
-// Tensor-memory variant with a DELAYED CORRECTION, the default for 512 < J <= 1024.
-//
-// In fused_tmem_kernel a step is  sweeps -> separator PCR -> correction, and the PCR (five
-// levels of shuffle + FMA, a pure latency chain that leaves the fp64 pipe idle) cannot overlap
-// anything, because the next sweeps need the corrected state.  But the whole step is linear with
-// constant coefficients.  Keep, between steps, the UNCORRECTED block solutions g and the reduced
-// right-hand side rr; the true state is x = g - V xsl - U xs with the separator values
-// xs = R^-1 rr still to come.  Then
-//     g' = T^-1 (B x)_interior = T^-1 B_ii g  +  P1 xsl  +  P2 xs ,
-// and the sweeps T^-1 B_ii g do not need xs: they run while the PCR of the PREVIOUS step is in
-// flight, its levels interleaved with the elimination chunks.  V and U stay in shared memory for
-// the points where the true state is needed (checkpoints, the end of the launch), which cut the
-// run into pipelined segments (scratch/proto_pipe.py).
-//
-// The sweeps use  B = I/theta - c A  once more:  A^-1 B = (1/theta) A^-1 - c I, so on the block
-// interior  T^-1 B_ii g = (1/theta) T^-1 g - c g  -- there is no right-hand side to build -- and
-//     P1 = -(1/theta) T^-1 V ,   P2 = -(1/theta) T^-1 U
-// (T^-1 b_left = -c V cancels the -c V of T^-1 B_ii V).  With the un-normalised factors
-// l_c = A_c,prev / pivot_prev, kappa_c = 1 / (theta pivot_c) and z = y - c g:
-//     elimination   h_c = g_c - l_c h_prev                          (1 FMA, the chain)
-//                   t_c = h_c kappa_c - c g_c - c s_c g_next        (off the chain, written over g_c)
-//     substitution  z_c = t_c - s_c z_next                          (1 FMA, the chain)
-// which is 4 operations per cell for Crank-Nicolson (c = 1), 3 for implicit Euler (c = 0) and 5
-// in general (scratch/proto_cn4.py).  The correction rides on the substitution links: P1, P2 are
-// stored in the order the substitution visits the cells (slot j = left cell M-1-j, right cell M+j),
-// the chain runs on the uncorrected values and each link is followed by its two correction FMAs.
-//
-// MODE 0: any theta in (0,1];  1: Crank-Nicolson;  2: implicit Euler.
-template <int MODE, int IT>
+// Per-lane constants of a step (kept in the shared-memory slots that s occupies during set-up).
+struct PipeConsts {
+  double al[5], ga[5], invD;     // PCR factors of the separator system
+  double slo, sup;               // separator's row of A (off-diagonals)
+  double bsep, bfirst;           // beta at the separator; theta * beta at global cell 0
+  double om_l, om_r;             // (1 - theta) * coupling of the block's end cells to the separators
+};
+
+// PCR factorisation of the 32-unknown separator system in dd; the factors are rounded once.
+__device__ __forceinline__ void pcr_factor_dd(int lane, dd RL, dd RD, dd RU, PipeConsts& K) {
+#pragma unroll 1
+  for (int l = 0; l < 5; ++l) {
+    const int s = 1 << l;
+    const bool hm = lane >= s, hp = lane + s < 32;
+    const dd Dm = dd_shfl_up(RD, s), Dp = dd_shfl_dn(RD, s);
+    const dd Lm = dd_shfl_up(RL, s), Um = dd_shfl_up(RU, s);
+    const dd Lp = dd_shfl_dn(RL, s), Up = dd_shfl_dn(RU, s);
+    dd a_ = dd_make(0.0), g_ = dd_make(0.0);
+    if (hm) a_ = dd_neg(dd_div(RL, Dm));
+    if (hp) g_ = dd_neg(dd_div(RU, Dp));
+    K.al[l] = dd_round(a_); K.ga[l] = dd_round(g_);
+    RD = dd_add(RD, dd_add(dd_mul(a_, Um), dd_mul(g_, Lp)));
+    RL = dd_mul(a_, Lm);
+    RU = dd_mul(g_, Up);
+  }
+  K.invD = dd_round(dd_recip(RD));
+}
+
+// Set-up of one system (see 5. above).  On return: (l, kappa) and (P1, P2) are in tensor memory,
+// s in sS, V and U in sv / su (natural cell order), the step constants in K.
+__device__ __forceinline__ void pipe_setup(const fvm_problem& pr, int64_t p, int lane, double dt_p, double theta,
+                                           uint32_t t_lk, uint32_t t_pp, double* sS, double* sv, double* su,
+                                           PipeConsts& K) {
+  constexpr int C = 32, N = kPipeN, MID = kPipeMid;
+  const int64_t J = pr.J;
+  const double rth = 1.0 / theta;
+  double sdi = 1.0;
+  dd vm, um;                                      // yhat-units spikes at the middle cell
+  double l_dn, l_up, kap_m;                       // the middle cell's factors
+  {
+    const double dt_theta = mul(dt_p, theta);
+    double beta_l = 0.0, beta_r = 0.0;
+    if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
+      beta_l = dvd(pr.left_flux[p], sub(pr.faces[1], pr.faces[0]));
+    if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
+      beta_r = dvd(-pr.right_flux[p], sub(pr.faces[J], pr.faces[J - 1]));
+    K.bfirst = 0.0; K.bsep = 0.0; K.om_l = 0.0; K.om_r = 0.0;
+    const int64_t j0 = (int64_t)lane * C;
+    Row asep;
+    auto row_of = [&](int c, const Face& FL, const Face& FR) {
+      const int64_t j = j0 + c;
+      Row a; a.lo = 0.0; a.di = 1.0; a.up = 0.0;    // padding rows (j >= J) are identity
+      if (j < J) {
+        Row m = problem_row(pr, p, j, FL, FR);
+        a = theta_lhs_row(m, dt_theta, alpha_of(j, J, pr.alpha_left, pr.alpha_right));
+      }
+      return a;
+    };
+    // sliding windows over faces, one per sweep direction: one expm1 and one face (5 divisions)
+    // per row instead of three and two
+    double lD0 = cell_D(pr, p, j0);
+    Face lFL = problem_face(pr, p, j0 - 1, cell_D(pr, p, j0 - 1), lD0);
+    double rD0 = cell_D(pr, p, j0 + C - 1);                                 // the separator's cell
+    Face rFR = problem_face(pr, p, j0 + C - 1, rD0, cell_D(pr, p, j0 + C));
+    {
+      const double Dm = cell_D(pr, p, j0 + C - 2);
+      const Face F = problem_face(pr, p, j0 + C - 2, Dm, rD0);
+      asep = row_of(C - 1, F, rFR);                                         // the separator's row
+      rFR = F; rD0 = Dm;
+    }
+    dd sl_prev = dd_make(0.0), sr_prev = dd_make(0.0), invl_prev = dd_make(0.0), invr_prev = dd_make(0.0);
+    dd hv = dd_make(0.0), hu = dd_make(0.0);
+#pragma unroll 1
+    for (int i = 0; i < MID; ++i) {
+      {                                            // left cell i: top-down elimination
+        const double lDp = cell_D(pr, p, j0 + i + 1);
+        const Face lFR = problem_face(pr, p, j0 + i, lD0, lDp);
+        const Row a = row_of(i, lFL, lFR);
+        lD0 = lDp; lFL = lFR;
+        const dd inv = dd_recip(dd_add_d(dd_neg(dd_mul_d(sl_prev, a.lo)), a.di));
+        const dd l = dd_mul_d(invl_prev, a.lo);
+        const dd kap = dd_mul_d(inv, rth);
+        sl_prev = dd_mul_d(inv, a.up);
+        invl_prev = inv;
+        // left spike with the UNROUNDED factors: h_0 = A_0,-1, h_i = -l_i h_{i-1}, g_i = h_i kappa_i
+        hv = (i == 0) ? dd_make(a.lo) : dd_neg(dd_mul(hv, l));
+        const dd g = dd_mul(hv, kap);
+        sS[i * 32] = dd_round(sl_prev); sv[i * 32] = g.hi; su[i * 32] = 0.0;
+        tmem_st_2d(t_lk + pipe_col_lk(i), dd_round(l), dd_round(kap));
+        tmem_st_2d(t_pp + pipe_col_pp(i), g.lo, sl_prev.lo);   // staging: low words of the dd values g, s
+        if (i == 0) K.om_l = (1.0 - theta) * a.lo;
+        if (j0 + i == 0) K.bfirst = theta * beta_l;
+      }
+      {                                            // right cell 30-i: bottom-up elimination
+        const int c = N - 1 - i;
+        const double rDm = cell_D(pr, p, j0 + c - 1);
+        const Face rFL = problem_face(pr, p, j0 + c - 1, rDm, rD0);
+        const Row a = row_of(c, rFL, rFR);
+        rD0 = rDm; rFR = rFL;
+        const dd inv = dd_recip(dd_add_d(dd_neg(dd_mul_d(sr_prev, a.up)), a.di));
+        const dd l = dd_mul_d(invr_prev, a.up);
+        const dd kap = dd_mul_d(inv, rth);
+        sr_prev = dd_mul_d(inv, a.lo);
+        invr_prev = inv;
+        hu = (i == 0) ? dd_make(a.up) : dd_neg(dd_mul(hu, l));
+        const dd g = dd_mul(hu, kap);
+        sS[c * 32] = dd_round(sr_prev); su[c * 32] = g.hi; sv[c * 32] = 0.0;
+        tmem_st_2d(t_lk + pipe_col_lk(c), dd_round(l), dd_round(kap));
+        tmem_st_2d(t_pp + pipe_col_pp(c), g.lo, sr_prev.lo);
+        if (i == 0) K.om_r = (1.0 - theta) * a.up;
+      }
+    }
+    {
+      // the middle cell takes both sweeps: pivot = A_mm - A_m,m-1 s_{m-1} - A_m,m+1 s_{m+1}.  (A 2x2 solve
+      // between the last cells of the two chains would divide by 1 - s s', which is ~2/sqrt(dt d/h^2) for
+      // stiff cells and amplifies the rounding of the factors by its inverse at every step.)
+      const Row a = row_of(MID, lFL, rFR);
+      const dd piv = dd_sub(dd_add_d(dd_neg(dd_mul_d(sl_prev, a.lo)), a.di), dd_mul_d(sr_prev, a.up));
+      const dd inv = dd_recip(piv);
+      const dd ld = dd_mul_d(invl_prev, a.lo), lu = dd_mul_d(invr_prev, a.up), km = dd_mul_d(inv, rth);
+      l_dn = dd_round(ld); l_up = dd_round(lu); kap_m = dd_round(km);
+      vm = dd_mul(dd_neg(dd_mul(hv, ld)), km);
+      um = dd_mul(dd_neg(dd_mul(hu, lu)), km);
+      sS[MID * 32] = 0.0;
+      tmem_st_2d(t_lk + pipe_col_lk(MID), l_dn, kap_m);
+      tmem_st_2d(t_lk + pipe_col_lk(MID) + 4, l_up, 0.0);
+    }
+    K.slo = asep.lo; sdi = asep.di; K.sup = asep.up;
+    if (j0 + C - 1 == J - 1) K.bsep += beta_r;
+  }
+  tmem_wait_st();
+  // ---- spikes of the exact block:  Vhat = (1/theta) T^-1 (A_0,-1 e_0), Uhat likewise;  V = theta Vhat
+  dd V0, U0, VL, UL;
+  {
+    sv[MID * 32] = dd_round(dd_mul_d(vm, theta)); su[MID * 32] = dd_round(dd_mul_d(um, theta));
+    dd lv = vm, lu = um;
+    double glo, slo_;
+#pragma unroll 1
+    for (int c = MID - 1; c >= 0; --c) {
+      tmem_ld_2d(t_pp + pipe_col_pp(c), glo, slo_);
+      const dd sc = dd_make(sS[c * 32], slo_);
+      lv = dd_sub(dd_make(sv[c * 32], glo), dd_mul(lv, sc));
+      lu = dd_neg(dd_mul(lu, sc));
+      sv[c * 32] = dd_round(dd_mul_d(lv, theta)); su[c * 32] = dd_round(dd_mul_d(lu, theta));
+    }
+    dd rv = vm, ru = um;
+#pragma unroll 1
+    for (int c = MID + 1; c < N; ++c) {
+      tmem_ld_2d(t_pp + pipe_col_pp(c), glo, slo_);
+      const dd sc = dd_make(sS[c * 32], slo_);
+      rv = dd_neg(dd_mul(rv, sc));
+      ru = dd_sub(dd_make(su[c * 32], glo), dd_mul(ru, sc));
+      sv[c * 32] = dd_round(dd_mul_d(rv, theta)); su[c * 32] = dd_round(dd_mul_d(ru, theta));
+    }
+    V0 = dd_mul_d(lv, theta); U0 = dd_mul_d(lu, theta); VL = dd_mul_d(rv, theta); UL = dd_mul_d(ru, theta);
+  }
+  // ---- separator system  R = A_ss - A_si (spike ends)  and its PCR factors
+  {
+    const dd v0n = dd_shfl_dn(V0, 1), u0n = dd_shfl_dn(U0, 1);        // next lane's first interior cell
+    const dd RL = dd_neg(dd_mul_d(VL, K.slo));
+    const dd RD = dd_sub(dd_add_d(dd_neg(dd_mul_d(UL, K.slo)), sdi), dd_mul_d(v0n, K.sup));   // sup == 0 on lane 31
+    const dd RU = dd_neg(dd_mul_d(u0n, K.sup));
+    pcr_factor_dd(lane, RL, RD, RU, K);
+  }
+  // ---- P1 = -Lhat(V), P2 = -Lhat(U): the loop's own sweeps with right-hand sides -V, -U, chains in dd,
+  //      in place in tensor memory
+  {
+    double l, kap;
+    dd h1 = dd_make(-sv[0]), h2 = dd_make(-su[0]);
+    tmem_st_2d(t_pp + pipe_col_pp(0), h1.hi, h2.hi);
+#pragma unroll 1
+    for (int c = 1; c < MID; ++c) {                // eliminate downwards
+      tmem_ld_2d(t_lk + pipe_col_lk(c), l, kap);
+      h1 = dd_add_d(dd_neg(dd_mul_d(h1, l)), -sv[c * 32]); h2 = dd_add_d(dd_neg(dd_mul_d(h2, l)), -su[c * 32]);
+      tmem_st_2d(t_pp + pipe_col_pp(c), h1.hi, h2.hi);
+    }
+    const dd hl1 = h1, hl2 = h2;                   // eliminated values at cell MID-1
+    h1 = dd_make(-sv[(N - 1) * 32]); h2 = dd_make(-su[(N - 1) * 32]);
+    tmem_st_2d(t_pp + pipe_col_pp(N - 1), h1.hi, h2.hi);
+#pragma unroll 1
+    for (int c = N - 2; c > MID; --c) {            // eliminate upwards
+      tmem_ld_2d(t_lk + pipe_col_lk(c), l, kap);
+      h1 = dd_add_d(dd_neg(dd_mul_d(h1, l)), -sv[c * 32]); h2 = dd_add_d(dd_neg(dd_mul_d(h2, l)), -su[c * 32]);
+      tmem_st_2d(t_pp + pipe_col_pp(c), h1.hi, h2.hi);
+    }
+    // the middle cell
+    const dd m1 = dd_mul_d(dd_sub(dd_add_d(dd_neg(dd_mul_d(hl1, l_dn)), -sv[MID * 32]), dd_mul_d(h1, l_up)), kap_m);
+    const dd m2 = dd_mul_d(dd_sub(dd_add_d(dd_neg(dd_mul_d(hl2, l_dn)), -su[MID * 32]), dd_mul_d(h2, l_up)), kap_m);
+    tmem_wait_st();
+    dd p1 = m1, p2 = m2;
+    double x1, x2;
+#pragma unroll 1
+    for (int c = MID - 1; c >= 0; --c) {           // substitute outwards
+      tmem_ld_2d(t_pp + pipe_col_pp(c), x1, x2);
+      tmem_ld_2d(t_lk + pipe_col_lk(c), l, kap);
+      const double sc = sS[c * 32];
+      p1 = dd_sub(two_prod(x1, kap), dd_mul_d(p1, sc)); p2 = dd_sub(two_prod(x2, kap), dd_mul_d(p2, sc));
+      tmem_st_2d(t_pp + pipe_col_pp(c), dd_round(p1), dd_round(p2));
+    }
+    tmem_st_2d(t_pp + pipe_col_pp(MID), dd_round(m1), dd_round(m2));
+    p1 = m1; p2 = m2;
+#pragma unroll 1
+    for (int c = MID + 1; c < N; ++c) {
+      tmem_ld_2d(t_pp + pipe_col_pp(c), x1, x2);
+      tmem_ld_2d(t_lk + pipe_col_lk(c), l, kap);
+      const double sc = sS[c * 32];
+      p1 = dd_sub(two_prod(x1, kap), dd_mul_d(p1, sc)); p2 = dd_sub(two_prod(x2, kap), dd_mul_d(p2, sc));
+      tmem_st_2d(t_pp + pipe_col_pp(c), dd_round(p1), dd_round(p2));
+    }
+    tmem_wait_st();
+  }
+}
+
+template <int MODE>
 __global__ void __launch_bounds__(kFusedThreads, 1)
 fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
                        int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
-  constexpr int C = 32, N = 31, M = 16;
-  constexpr int NCH = M / IT;
-  using TC = TmemChunk<IT>;
+  constexpr int C = 32, N = kPipeN, MID = kPipeMid;
+  constexpr int IT = 2;                              // slots per chunk (.x16): a slot = a left and a right cell
+  constexpr int NCH = (MID + 1) / IT;                // 16 slots: 15 cell pairs and the middle cell
+  using TC = TmemChunk;
   // shared-memory slots (per lane) of the constants of a step, in the place s occupied during set-up
-  enum { K_OML = 0, K_OMR = 1, K_AL = 2, K_GA = 7, K_INVD = 12, K_SLO = 13, K_SUP = 14, K_SBLO = 15, K_SBDI = 16,
-         K_SBUP = 17, K_BSEP = 18, K_V0 = 19, K_U0 = 20, K_VL = 21, K_UL = 22, K_BFIRST = 23 };
+  enum { K_OML = 0, K_OMR = 1, K_AL = 2, K_GA = 7, K_INVD = 12, K_SLO = 13, K_SUP = 14, K_BSEP = 15, K_BFIRST = 16 };
   extern __shared__ double smem[];
   __shared__ uint32_t tmem_base_slot;
   const int lane = threadIdx.x & 31;
@@ -642,7 +585,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
   double* sv = sS + N * 32;
   double* su = sv + N * 32;
   const int64_t J = pr.J;
-  const double cth = (1.0 - theta) / theta;
+  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
 
   if (warp == 0) tmem_alloc_512(&tmem_base_slot);
   tmem_fence_before_sync();
@@ -654,71 +597,30 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
 
   for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
     // ------------------------------------------------------------------ set-up (once)
-    double delta;
-    double sr[N];
+    double sr[N];                                    // sr[MID] is unused (the middle cell has no substitution link)
     {
-      Reduced R;
-      double om_l, om_r;
-      tmem_setup_common<true>(pr, p, lane, dt[p], theta, t_lk, sS, sv, su, R, sr, delta, om_l, om_r);
-      // P1, P2: twisted solve with right-hand sides -V, -U, in place in tensor memory
-      auto tcol = [&](int c) { return (uint32_t)(c < M ? 8 * c : 8 * (N - 1 - c) + 4); };
-      auto tpp = [&](int c) { return (uint32_t)(c < M ? 8 * (M - 1 - c) : 8 * (c - M) + 4); };
-      tmem_wait_st();
-      double l, kap, h1 = -sv[0], h2 = -su[0];
-      tmem_st_2d(t_pp + tpp(0), h1, h2);
-#pragma unroll 1
-      for (int c = 1; c < M; ++c) {                  // eliminate downwards
-        tmem_ld_2d(t_lk + tcol(c), l, kap);
-        h1 = fma(-l, h1, -sv[c * 32]); h2 = fma(-l, h2, -su[c * 32]);
-        tmem_st_2d(t_pp + tpp(c), h1, h2);
-      }
-      const double hl1 = h1, hl2 = h2;               // eliminated values at cell M-1
-      h1 = -sv[(N - 1) * 32]; h2 = -su[(N - 1) * 32];
-      tmem_st_2d(t_pp + tpp(N - 1), h1, h2);
-#pragma unroll 1
-      for (int c = N - 2; c >= M; --c) {             // eliminate upwards
-        tmem_ld_2d(t_lk + tcol(c), l, kap);
-        h1 = fma(-l, h1, -sv[c * 32]); h2 = fma(-l, h2, -su[c * 32]);
-        tmem_st_2d(t_pp + tpp(c), h1, h2);
-      }
-      double kap_l, kap_r;                           // meet between cells M-1 and M
-      tmem_ld_2d(t_lk + tcol(M - 1), l, kap_l);
-      tmem_ld_2d(t_lk + tcol(M), l, kap_r);
-      const double m1 = fma(-sS[M * 32], hl1 * kap_l, h1 * kap_r) * delta;
-      const double m2 = fma(-sS[M * 32], hl2 * kap_l, h2 * kap_r) * delta;
-      tmem_wait_st();
-      double p1 = m1, p2 = m2, x1, x2;
-#pragma unroll 1
-      for (int c = M - 1; c >= 0; --c) {             // substitute outwards
-        tmem_ld_2d(t_pp + tpp(c), x1, x2);
-        tmem_ld_2d(t_lk + tcol(c), l, kap);
-        const double sc = sS[c * 32];
-        p1 = fma(-sc, p1, x1 * kap); p2 = fma(-sc, p2, x2 * kap);
-        tmem_st_2d(t_pp + tpp(c), p1, p2);
-      }
-      tmem_st_2d(t_pp + tpp(M), m1, m2);
-      p1 = m1; p2 = m2;
-#pragma unroll 1
-      for (int c = M + 1; c < N; ++c) {
-        tmem_ld_2d(t_pp + tpp(c), x1, x2);
-        tmem_ld_2d(t_lk + tcol(c), l, kap);
-        const double sc = sS[c * 32];
-        p1 = fma(-sc, p1, x1 * kap); p2 = fma(-sc, p2, x2 * kap);
-        tmem_st_2d(t_pp + tpp(c), p1, p2);
-      }
-      tmem_wait_st();
+      PipeConsts Kc;
+      pipe_setup(pr, p, lane, dt[p], theta, t_lk, t_pp, sS, sv, su, Kc);
+#pragma unroll
+      for (int c = 0; c < N; ++c) sr[c] = sS[c * 32];
       __syncwarp();
       // s is in registers now: its shared-memory slots take the per-lane constants of a step, so
       // that the registers they would occupy can hold the second tensor-memory chunk buffer
-      const double V0 = sv[0], U0 = su[0], VL = sv[(N - 1) * 32], UL = su[(N - 1) * 32];
-      sS[K_OML * 32] = om_l; sS[K_OMR * 32] = om_r;
+      sS[K_OML * 32] = Kc.om_l; sS[K_OMR * 32] = Kc.om_r;
 #pragma unroll
-      for (int l2 = 0; l2 < 5; ++l2) { sS[(K_AL + l2) * 32] = R.al[l2]; sS[(K_GA + l2) * 32] = R.ga[l2]; }
-      sS[K_INVD * 32] = R.invD; sS[K_SLO * 32] = R.slo; sS[K_SUP * 32] = R.sup; sS[K_SBLO * 32] = R.sblo;
-      sS[K_SBDI * 32] = R.sbdi; sS[K_SBUP * 32] = R.sbup; sS[K_BSEP * 32] = R.bsep; sS[K_V0 * 32] = V0;
-      sS[K_U0 * 32] = U0; sS[K_VL * 32] = VL; sS[K_UL * 32] = UL; sS[K_BFIRST * 32] = R.bfirst;
+      for (int l2 = 0; l2 < 5; ++l2) { sS[(K_AL + l2) * 32] = Kc.al[l2]; sS[(K_GA + l2) * 32] = Kc.ga[l2]; }
+      sS[K_INVD * 32] = Kc.invD; sS[K_SLO * 32] = Kc.slo; sS[K_SUP * 32] = Kc.sup;
+      sS[K_BSEP * 32] = Kc.bsep; sS[K_BFIRST * 32] = Kc.bfirst;
     }
     auto K = [&](int slot) { return sS[slot * 32]; };
+    // x' = yhat - c x at a separator
+    auto from_yhat = [&](double ys, double x_old) {
+      return (MODE == 2) ? ys : ((MODE == 1) ? ys - x_old : fma(-cth, x_old, ys));
+    };
+    // g + c g_old: the uncorrected block solution of yhat
+    auto ghat = [&](double g_new, double g_old) {
+      return (MODE == 2) ? g_new : ((MODE == 1) ? g_new + g_old : fma(cth, g_old, g_new));
+    };
 
     double w[C];
     load_state<C>(w_io + p * J, J, lane, w);
@@ -731,114 +633,83 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
     };
     // One step on w[0..N-1] in place; the cells outside the block that the end cells couple to
     // contribute oldL0 / oldR0 (first step of a segment only).  With PIPE the five PCR levels of
-    // the previous step's separator system (rr in, xs out) are issued between the elimination
-    // chunks, the step-end chain of the PREVIOUS step (xs -> shuffle -> true end values -> shuffle
-    // -> rs) follows as soon as the last level is done (EARLY), and the substitution applies the
-    // delayed correction link by link.
-    auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double& rr,
-                      double g0_old, double gl_old, double& xsl, double& rs) {
+    // the previous step's separator system (rr in) are issued between the elimination chunks, the
+    // new separator values xs (and xsl = the left neighbour's) follow as soon as the last level is
+    // done, and the substitution applies the delayed correction link by link.  base returns the
+    // part of the next reduced right-hand side that does not depend on this step's sweeps.
+    auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double rr,
+                      double& xs, double& base) {
       constexpr bool PIPE = decltype(pipe_tag)::value;
-      constexpr bool EARLY = PIPE && NCH >= 8;
-      double x_first = 0.0, x_last = 0.0, x_first_next = 0.0;
-      const double w_m_old = w[M];
-      double hL = 0.0, hR = 0.0, hk_l = 0.0, hk_r = 0.0;
+      double hL = 0.0, hR = 0.0, zM = 0.0;
       double cgL = 0.0, cgR = 0.0;                    // MODE 0: c * g of the cell the chain is at
-      int level = 0;
+      double xsl = 0.0;
 #pragma unroll
       for (int k = 0; k < NCH; ++k) {
         uint32_t* cur = (k & 1) ? rb : ra;
         // prefetch of the next chunk, pinned ahead of this chunk's arithmetic (chunk_ld_after)
-        if (k == 0) { TC::wait(ra); chunk_ld_after<TC>(t_lk + 8 * IT, rb, w[0]); }
-        else if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_lk + 8 * IT * (k + 1) : next_region, ra, hL); }
-        else            { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_lk + 8 * IT * (k + 1) : next_region, rb, hL); }
+        if (k == 0) { TC::wait(ra); chunk_ld_after(t_lk + 8 * IT, rb, w[0]); }
+        else if (k & 1) { TC::wait(rb); chunk_ld_after(k + 1 < NCH ? t_lk + 8 * IT * (k + 1) : next_region, ra, hL); }
+        else            { TC::wait(ra); chunk_ld_after(k + 1 < NCH ? t_lk + 8 * IT * (k + 1) : next_region, rb, hL); }
         // One PCR level per chunk.  Warps issue in order, so the level's shuffles are issued HERE and
         // their consumer sits after the chunk's cell work: the ~26-cycle shuffle latency is covered.
         double rm = 0.0, rp = 0.0, fa = 0.0, fg = 0.0;
         const bool lvl = PIPE && k < 5;
         if (lvl) { rm = shfl_up(rr, 1 << k); rp = shfl_dn(rr, 1 << k); fa = K(K_AL + k); fg = K(K_GA + k); }
-        if (EARLY && k == 5) { rr *= K(K_INVD); xsl = shfl_up(rr, 1); }      // rr now holds xs
-        if (EARLY && k == 6) {
-          x_last = fma(-K(K_UL), rr, fma(-K(K_VL), xsl, gl_old));            // true values of the finished step
-          x_first = fma(-K(K_U0), rr, fma(-K(K_V0), xsl, g0_old));
-          x_first_next = shfl_dn(x_first, 1);
-        }
-        if (EARLY && k == 7) {
-          if (lane == 31) x_first_next = 0.0;
-          rs = fma(K(K_SBUP), x_first_next, fma(K(K_SBDI), rr, fma(K(K_SBLO), x_last, K(K_BSEP))));
-        }
+        if (PIPE && k == 5) { xs = from_yhat(rr * K(K_INVD), xs); xsl = shfl_up(xs, 1); }
+        if (PIPE && k == 6) base = fma(xs, rth, K(K_BSEP));
 #pragma unroll
         for (int ii = 0; ii < IT; ++ii) {
           const int i = k * IT + ii;
-          {
-            const int c = i;                          // left cell, eliminated top-down
-            const double l = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1);
-            const double gc = w[c];
-            const double gn = (c == M - 1) ? w_m_old : w[c + 1];
-            if (i == 0) {
-              hL = gc + K(K_BFIRST);
-              if (!PIPE) hL = fma(-K(K_OML), oldL0, hL);
-              if (MODE == 0) cgL = cth * gc;
-            } else {
-              hL = fma(-l, hL, gc);
+          if (i < MID) {
+            {
+              const int c = i;                        // left cell, eliminated top-down
+              const double l = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1);
+              const double gc = w[c], gn = w[c + 1];
+              if (i == 0) {
+                hL = gc + K(K_BFIRST);
+                if (!PIPE) hL = fma(-K(K_OML), oldL0, hL);
+                if (MODE == 0) cgL = cth * gc;
+              } else {
+                hL = fma(-l, hL, gc);
+              }
+              const double cg = (MODE == 0) ? cgL : gc, cgn = (MODE == 0) ? cth * gn : gn;
+              w[c] = tval(MODE == 2 ? hL * kap : fma(hL, kap, -cg), sr[c], cgn);
+              cgL = cgn;
             }
-            const double cg = (MODE == 0) ? cgL : gc, cgn = (MODE == 0) ? cth * gn : gn;
-            if (c == M - 1) { hk_l = hL * kap; w[c] = tval(MODE == 2 ? hk_l : hk_l - cg, sr[c], cgn); }
-            else w[c] = tval(MODE == 2 ? hL * kap : fma(hL, kap, -cg), sr[c], cgn);
-            cgL = cgn;
-          }
-          if (i < N - M) {
-            const int c = N - 1 - i;                  // right cell, eliminated bottom-up
-            const double l = chunk_dbl(cur, 4 * ii + 2), kap = chunk_dbl(cur, 4 * ii + 3);
-            const double gc = w[c];
-            const double gp = w[c - 1];
-            if (i == 0) {
-              hR = gc;
-              if (!PIPE) hR = fma(-K(K_OMR), oldR0, hR);
-              if (MODE == 0) cgR = cth * gc;
-            } else {
-              hR = fma(-l, hR, gc);
+            {
+              const int c = N - 1 - i;                // right cell, eliminated bottom-up
+              const double l = chunk_dbl(cur, 4 * ii + 2), kap = chunk_dbl(cur, 4 * ii + 3);
+              const double gc = w[c], gp = w[c - 1];
+              if (i == 0) {
+                hR = gc;
+                if (!PIPE) hR = fma(-K(K_OMR), oldR0, hR);
+                if (MODE == 0) cgR = cth * gc;
+              } else {
+                hR = fma(-l, hR, gc);
+              }
+              const double cg = (MODE == 0) ? cgR : gc, cgp = (MODE == 0) ? cth * gp : gp;
+              w[c] = tval(MODE == 2 ? hR * kap : fma(hR, kap, -cg), sr[c], cgp);
+              cgR = cgp;
             }
-            const double cg = (MODE == 0) ? cgR : gc, cgp = (MODE == 0) ? cth * gp : gp;
-            if (c == M) { hk_r = hR * kap; w[c] = tval(MODE == 2 ? hk_r : hk_r - cg, sr[c], cgp); }
-            else w[c] = tval(MODE == 2 ? hR * kap : fma(hR, kap, -cg), sr[c], cgp);
-            cgR = cgp;
+          } else {
+            // the middle cell takes both sweeps: h = g - l_dn h_{m-1} - l_up h_{m+1};  z = h kappa - c g
+            const double l_dn = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1), l_up = chunk_dbl(cur, 4 * ii + 2);
+            const double gc = w[MID];
+            const double hM = fma(-l_up, hR, fma(-l_dn, hL, gc));
+            zM = (MODE == 2) ? hM * kap : ((MODE == 1) ? fma(hM, kap, -gc) : fma(hM, kap, -cth * gc));
           }
         }
-        if (lvl) { rr = fma(fg, rp, fma(fa, rm, rr)); level = k + 1; }
+        if (lvl) rr = fma(fg, rp, fma(fa, rm, rr));
       }
-      if (PIPE) {
-#pragma unroll
-        for (int l = 0; l < 5; ++l) {
-          if (l >= level) {
-            const int s = 1 << l;
-            const double rm = shfl_up(rr, s), rp = shfl_dn(rr, s);
-            rr = fma(K(K_GA + l), rp, fma(K(K_AL + l), rm, rr));
-          }
-        }
-        if (!EARLY) {
-          rr *= K(K_INVD);                           // rr now holds xs
-          xsl = shfl_up(rr, 1);
-          x_last = fma(-K(K_UL), rr, fma(-K(K_VL), xsl, gl_old));
-          x_first = fma(-K(K_U0), rr, fma(-K(K_V0), xsl, g0_old));
-          x_first_next = shfl_dn(x_first, 1);
-          if (lane == 31) x_first_next = 0.0;
-          rs = fma(K(K_SBUP), x_first_next, fma(K(K_SBDI), rr, fma(K(K_SBLO), x_last, K(K_BSEP))));
-        }
-      }
-      // meeting point: z_M = (hk_r - s_M hk_l) delta - c g_M
-      double zM = fma(-sr[M], hk_l, hk_r) * delta;
-      if (MODE == 1) zM -= w_m_old;
-      if (MODE == 0) zM = fma(-cth, w_m_old, zM);
       if (PIPE) {
         // substitution outwards with the delayed correction riding on every link: the chain runs on
         // the uncorrected values zL / zR, the corrected ones go to w
-        const double xs = rr;
         double zL = zM, zR = zM;
 #pragma unroll
         for (int k = 0; k < NCH; ++k) {
           uint32_t* cur = (k & 1) ? rb : ra;
-          if (k & 1) { TC::wait(rb); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_lk, ra, zL); }
-          else       { TC::wait(ra); chunk_ld_after<TC>(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_lk, rb, zL); }
+          if (k & 1) { TC::wait(rb); chunk_ld_after(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_lk, ra, zL); }
+          else       { TC::wait(ra); chunk_ld_after(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_lk, rb, zL); }
           // links first, then the xsl products of the whole chunk, then the xs products: consecutive
           // FMAs that share an operand can take it from the operand-reuse cache instead of the
           // register file, whose bandwidth is what bounds these loops (fp64_operands.cu)
@@ -846,36 +717,38 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
 #pragma unroll
           for (int ii = 0; ii < IT; ++ii) {
             const int j = k * IT + ii;
-            const int cl = M - 1 - j, cr = M + j;
-            zL = fma(-sr[cl], zL, w[cl]);
-            zl[ii] = zL;
-            if (j < N - M) {
-              if (j > 0) zR = fma(-sr[cr], zR, w[cr]);
-              zr[ii] = zR;
-            }
+            if (j == 0) { zl[ii] = zM; zr[ii] = 0.0; continue; }
+            const int cl = MID - j, cr = MID + j;
+            zL = fma(-sr[cl], zL, w[cl]); zl[ii] = zL;
+            zR = fma(-sr[cr], zR, w[cr]); zr[ii] = zR;
           }
 #pragma unroll
           for (int ii = 0; ii < IT; ++ii) {
             const int j = k * IT + ii;
             zl[ii] = fma(chunk_dbl(cur, 4 * ii), xsl, zl[ii]);
-            if (j < N - M) zr[ii] = fma(chunk_dbl(cur, 4 * ii + 2), xsl, zr[ii]);
+            if (j > 0) zr[ii] = fma(chunk_dbl(cur, 4 * ii + 2), xsl, zr[ii]);
           }
 #pragma unroll
           for (int ii = 0; ii < IT; ++ii) {
             const int j = k * IT + ii;
-            w[M - 1 - j] = fma(chunk_dbl(cur, 4 * ii + 1), xs, zl[ii]);
-            if (j < N - M) w[M + j] = fma(chunk_dbl(cur, 4 * ii + 3), xs, zr[ii]);
+            w[MID - j] = fma(chunk_dbl(cur, 4 * ii + 1), xs, zl[ii]);
+            if (j > 0) w[MID + j] = fma(chunk_dbl(cur, 4 * ii + 3), xs, zr[ii]);
           }
         }
       } else {
-        w[M] = zM;
+        w[MID] = zM;
 #pragma unroll
-        for (int j = 0; j < M; ++j) {
-          const int cl = M - 1 - j, cr = M + 1 + j;
+        for (int j = 1; j <= MID; ++j) {
+          const int cl = MID - j, cr = MID + j;
           w[cl] = fma(-sr[cl], w[cl + 1], w[cl]);
-          if (cr < N) w[cr] = fma(-sr[cr], w[cr - 1], w[cr]);
+          w[cr] = fma(-sr[cr], w[cr - 1], w[cr]);
         }
       }
+    };
+    // reduced right-hand side of the step just swept:  base - slo ghat_last - sup ghat_first(next lane)
+    auto reduced_rhs = [&](double base, double g0_old, double gl_old) {
+      const double e_first_next = shfl_dn(ghat(w[0], g0_old), 1);     // lane 31: sup == 0
+      return fma(-K(K_SUP), e_first_next, fma(-K(K_SLO), ghat(w[N - 1], gl_old), base));
     };
 
     int64_t remaining = nsteps, n_ckpt = 0;
@@ -884,29 +757,30 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       const bool ck = ckpt != nullptr && ckpt_every > 0 && remaining >= ckpt_every;
       const int64_t L = ck ? ckpt_every : remaining; // steps until the true state is needed again
       // -------- first step of the segment: sweeps on the true state
-      double wl = shfl_up(w[C - 1], 1);
-      double wr = shfl_dn(w[0], 1);
+      double xs = w[C - 1];
+      double wl = shfl_up(xs, 1);
       if (lane == 0) wl = 0.0;
-      if (lane == 31) wr = 0.0;
-      double rs = fma(K(K_SBUP), wr, fma(K(K_SBDI), w[C - 1], fma(K(K_SBLO), w[N - 1], K(K_BSEP))));
-      double rr = 0.0, xsl = 0.0;
-      sweeps(std::false_type{}, wl, w[C - 1], t_lk, rr, 0.0, 0.0, xsl, rs);
-      rr = fma(-K(K_SUP), shfl_dn(w[0], 1), fma(-K(K_SLO), w[N - 1], rs));
+      // the true state in uncorrected form: g_old = x + V xsl + U xs (only its end cells are needed)
+      double g0_old = fma(su[0], xs, fma(sv[0], wl, w[0]));
+      double gl_old = fma(su[(N - 1) * 32], xs, fma(sv[(N - 1) * 32], wl, w[N - 1]));
+      double base = fma(xs, rth, K(K_BSEP));
+      sweeps(std::false_type{}, wl, xs, t_lk, 0.0, xs, base);
+      double rr = reduced_rhs(base, g0_old, gl_old);
       // -------- pipelined steps: PCR of step n overlaps the sweeps of step n+1
       for (int64_t i = 1; i < L; ++i) {
-        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, w[0], w[N - 1], xsl, rs);
-        const double g0n = shfl_dn(w[0], 1);        // lane 31: sup == 0
-        rr = fma(-K(K_SUP), g0n, fma(-K(K_SLO), w[N - 1], rs));
+        g0_old = w[0]; gl_old = w[N - 1];
+        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, xs, base);
+        rr = reduced_rhs(base, g0_old, gl_old);
       }
       // -------- end of the segment: finish the last step and materialise the true state
       {
-        double xs = rr;
+        double ys = rr;
 #pragma unroll
         for (int l = 0; l < 5; ++l) {
-          const double rm = shfl_up(xs, 1 << l), rp = shfl_dn(xs, 1 << l);
-          xs = fma(K(K_GA + l), rp, fma(K(K_AL + l), rm, xs));
+          const double rm = shfl_up(ys, 1 << l), rp = shfl_dn(ys, 1 << l);
+          ys = fma(K(K_GA + l), rp, fma(K(K_AL + l), rm, ys));
         }
-        xs *= K(K_INVD);
+        xs = from_yhat(ys * K(K_INVD), xs);
         const double xsl_end = shfl_up(xs, 1);      // lane 0: V == 0, value unused
 #pragma unroll
         for (int c = 0; c < N; ++c) w[c] = fma(-su[c * 32], xs, fma(-sv[c * 32], xsl_end, w[c]));
@@ -965,7 +839,7 @@ static int launch_fused(const fvm_problem& pr, const double* dt, double theta, i
   return (int)cudaGetLastError();
 }
 
-template <int MODE, int IT, bool PIPE>
+template <int MODE>
 static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
                              int64_t ckpt_every, double* w, double* ckpt, cudaStream_t stream) {
   constexpr int warps = kFusedThreads / 32;
@@ -975,28 +849,11 @@ static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double the
   if (st) return st;
   int64_t blocks = (pr.P + warps - 1) / warps;
   if (blocks > sms) blocks = sms;                // one CTA per SM: it holds the SM's whole TMEM
-  int launch_warps = warps;
-  const char* lw = getenv("FVM_FUSED_WARPS");    // experiment: 4 = one warp per scheduler
-  if (lw && lw[0] == '4') launch_warps = 4;
-  cudaError_t e;
-  if constexpr (PIPE) {
-    auto kern = fused_tmem_pipe_kernel<MODE, IT>;
-    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    kern<<<(unsigned)blocks, launch_warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
-  } else {
-    auto kern = fused_tmem_kernel<MODE, IT>;
-    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-    kern<<<(unsigned)blocks, launch_warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
-  }
+  auto kern = fused_tmem_pipe_kernel<MODE>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  kern<<<(unsigned)blocks, warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
   return (int)cudaGetLastError();
-}
-
-// FVM_FUSED_STORE=smem forces the shared-memory kernel (A/B comparison and profiling).
-static bool tmem_enabled() {
-  const char* s = getenv("FVM_FUSED_STORE");
-  return !(s && s[0] == 's');
 }
 
 template <int C>
@@ -1006,23 +863,10 @@ static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, 
                   ((pr.J - 1) % C) != C - 1;
   constexpr bool Q = true;
   if (rb) return launch_fused<C, 0, true, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-  if (C == 32 && tmem_enabled()) {
-    // FVM_FUSED_PIPE=0 selects the kernel without the delayed correction (A/B runs and profiling)
-    const char* pp = getenv("FVM_FUSED_PIPE");
-    if (pp && pp[0] == '0') {
-      if (theta == 0.5) return launch_fused_tmem<1, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      if (theta == 1.0) return launch_fused_tmem<2, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      return launch_fused_tmem<0, 4, false>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    }
-    const char* its = getenv("FVM_TMEM_IT");     // 1: .x8 chunks (experiments); default 2: .x16
-    if (its && its[0] == '1') {
-      if (theta == 0.5) return launch_fused_tmem<1, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      if (theta == 1.0) return launch_fused_tmem<2, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-      return launch_fused_tmem<0, 1, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    }
-    if (theta == 0.5) return launch_fused_tmem<1, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    if (theta == 1.0) return launch_fused_tmem<2, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    return launch_fused_tmem<0, 2, true>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  if (C == 32) {
+    if (theta == 0.5) return launch_fused_tmem<1>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    if (theta == 1.0) return launch_fused_tmem<2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    return launch_fused_tmem<0>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
   }
   if (theta == 0.5) return launch_fused<C, 1, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
   if (theta == 1.0) return launch_fused<C, 2, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);

@@ -39,7 +39,6 @@
 // first and last cell in both orders, so ghosts and tile neighbours need no special casing.
 #include "fvm_device.cuh"
 #include "cta_scan.cuh"
-#include <mutex>
 
 namespace fvm {
 
@@ -84,10 +83,13 @@ __global__ void __launch_bounds__(128) spike_tile_factor_kernel(
   const int64_t base = (pi * n_tiles + k) * T;
   const int64_t jg0 = (tile_offset + k) * T;               // global index of the tile's first cell
   auto at = [&](int r) { return base + tiled_pos(r, TPB, CPT); };
+  // beta[0] / beta[J-1]: only the tile that HOLDS the end cell may touch the end faces.  With the
+  // mesh split over ranks `faces` is the caller's pointer shifted by the slab offset, and a rank
+  // that does not own cell 0 (or J-1) has no memory behind faces[0..1] (faces[J-1..J]).
   double beta_l = 0.0, beta_r = 0.0;
-  if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
+  if (jg0 == 0 && pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
     beta_l = dvd(pr.left_flux[pi], sub(pr.faces[1], pr.faces[0]));
-  if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
+  if (pr.J - 1 >= jg0 && pr.J - 1 < jg0 + T && pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
     beta_r = dvd(-pr.right_flux[pi], sub(pr.faces[pr.J], pr.faces[pr.J - 1]));
   const int N = T - 1;                                     // interior cells
   double q_prev = 0.0, gv = 0.0;
@@ -559,28 +561,18 @@ namespace {
 constexpr int64_t kStaticMaxTiles = 65536;
 static __device__ __align__(256) double g_spike_rs_scratch[kStaticMaxTiles];
 
-constexpr int kMaxDevices = 64;
-double* g_scratch_addr[kMaxDevices];      // device address of the array above, per device
-bool g_scratch_known[kMaxDevices];
-std::mutex g_scratch_mutex;
-
 // The array's name is only a handle in host code; the address a kernel can use has to be asked
-// for, once per device, while that device is current.
+// for while the device that will run the kernel is current.  It is asked for on EVERY call and
+// never cached: the lookup is a host-side table access once the library's module is loaded on
+// the device, and a cached pointer would go stale after cudaDeviceReset() or under a second
+// context on the same device.  The first call on a device loads the module (so it should come
+// before any stream capture); the device is the CURRENT one, which must be the stream's.
 int static_scratch(double** out) {
-  int dev = -1;
-  cudaError_t e = cudaGetDevice(&dev);
+  double* ptr = nullptr;
+  cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_spike_rs_scratch);
   if (e != cudaSuccess) return (int)e;
-  if (dev < 0 || dev >= kMaxDevices) return FVM_ERR_UNSUPPORTED;
-  std::lock_guard<std::mutex> lock(g_scratch_mutex);
-  if (!g_scratch_known[dev]) {
-    double* ptr = nullptr;
-    e = cudaGetSymbolAddress((void**)&ptr, g_spike_rs_scratch);
-    if (e != cudaSuccess) return (int)e;
-    if (ptr == nullptr) return (int)cudaErrorInvalidSymbol;
-    g_scratch_addr[dev] = ptr;
-    g_scratch_known[dev] = true;
-  }
-  *out = g_scratch_addr[dev];
+  if (ptr == nullptr) return (int)cudaErrorInvalidSymbol;
+  *out = ptr;
   return FVM_OK;
 }
 }  // namespace

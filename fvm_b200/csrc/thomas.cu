@@ -3,11 +3,20 @@
 // One thread owns one system and walks its cells; with the interleaved layout
 // (cell stride = P) the 32 systems of a warp sit side by side, so every load and
 // store of the warp is one fully used 256-byte segment.  The recurrences carry only
-// one scalar (g or x); everything else in an iteration is independent of it, so the
+// one scalar (h or z); everything else in an iteration is independent of it, so the
 // loads of U rows are issued as a batch ahead of the dependent FMA chain.
 //
-// HBM bytes per cell-update (algorithmic): forward reads w, fp, fq, fb and writes g
-// (40 B), backward reads g, fq and writes w (24 B): 64 B.
+// The step has NO right-hand side:  B = I/theta - c A  (c = (1-theta)/theta) gives
+// A^-1 B = (1/theta) A^-1 - c I.  With the factors of fvm_theta_factor, l = fp, s = fq,
+// kappa = fb (= 1/(theta pivot)) and z = yhat - c w:
+//   forward   h_j = w_j + beta_j' - l_j h_{j-1} ;  t_j = h_j kappa_j - c w_j - c s_j w_{j+1}   (t over w)
+//   backward  z_j = t_j - s_j z_{j+1}                                                           (z over t)
+// A right-hand side  B w  would cancel terms of size dt*d/h^2 against each other at every step;
+// this form does not, and its error over 10^4 steps is 100x smaller (tests/test_gpu_long_run.py).
+//
+// HBM bytes per cell-update as this kernel moves them: forward reads w, l, kappa, s and writes t
+// (40 B), backward reads t, s and writes w (24 B): 64 B.  The algorithmic figure of SURVEY 8(d)
+// for three streamed per-cell arrays is 40 B (what a kernel that kept t on chip would move).
 #include "fvm_device.cuh"
 
 namespace fvm {
@@ -24,9 +33,9 @@ __global__ void __launch_bounds__(128) thomas_steps_kernel(
     const double* __restrict__ scale_right) {
   const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
-  const double* P_ = fp + p * f_ps;
-  const double* Q_ = fq + p * f_ps;
-  const double* B_ = fb + p * f_ps;
+  const double* L_ = fp + p * f_ps;
+  const double* S_ = fq + p * f_ps;
+  const double* K_ = fb + p * f_ps;
   double* W_ = w + p * w_ps;
   const double bl0 = bt_left ? bt_left[p] : 0.0;
   const double br0 = bt_right ? bt_right[p] : 0.0;
@@ -37,51 +46,49 @@ __global__ void __launch_bounds__(128) thomas_steps_kernel(
       if (scale_left) bl *= scale_left[s * P + p];
       if (scale_right) br *= scale_right[s * P + p];
     }
-    // forward: r~_j = fb_j w_j - c (fp_j w_{j-1} + fq_j w_{j+1}) ; g_j = r~_j - fp_j g_{j-1}
-    double wm = 0.0, w0 = W_[0], g = 0.0;
+    double w0 = W_[0], h = 0.0;
     int64_t j = 0;
     for (; j + U <= J; j += U) {
-      double pj[U], qj[U], bj[U], wn[U];
+      double lj[U], sj[U], kj[U], wn[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int64_t jj = j + u;
-        pj[u] = P_[jj * f_cs]; qj[u] = Q_[jj * f_cs]; bj[u] = B_[jj * f_cs];
+        lj[u] = L_[jj * f_cs]; sj[u] = S_[jj * f_cs]; kj[u] = K_[jj * f_cs];
         wn[u] = (jj + 1 < J) ? W_[(jj + 1) * w_cs] : 0.0;
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int64_t jj = j + u;
-        double t = fma(qj[u], wn[u], pj[u] * wm);
-        double r = fma(bj[u], w0, -cth * t);
+        double r = w0;
         if (jj == 0) r += bl;
         if (jj == J - 1) r += br;
-        g = fma(-pj[u], g, r);
-        W_[jj * w_cs] = g;
-        wm = w0; w0 = wn[u];
+        h = fma(-lj[u], h, r);
+        const double cw = cth * w0, cwn = cth * wn[u];
+        W_[jj * w_cs] = fma(-sj[u], cwn, fma(h, kj[u], -cw));
+        w0 = wn[u];
       }
     }
     for (; j < J; ++j) {
-      const double pj = P_[j * f_cs], qj = Q_[j * f_cs], bj = B_[j * f_cs];
+      const double lj = L_[j * f_cs], sj = S_[j * f_cs], kj = K_[j * f_cs];
       const double wn = (j + 1 < J) ? W_[(j + 1) * w_cs] : 0.0;
-      double t = fma(qj, wn, pj * wm);
-      double r = fma(bj, w0, -cth * t);
+      double r = w0;
       if (j == 0) r += bl;
       if (j == J - 1) r += br;
-      g = fma(-pj, g, r);
-      W_[j * w_cs] = g;
-      wm = w0; w0 = wn;
+      h = fma(-lj, h, r);
+      W_[j * w_cs] = fma(-sj, cth * wn, fma(h, kj, -cth * w0));
+      w0 = wn;
     }
-    // backward: x_j = g_j - fq_j x_{j+1}
-    double x = g;
+    // backward: z_j = t_j - s_j z_{j+1}   (s_{J-1} = 0: z_{J-1} = t_{J-1} is already in place)
+    double z = W_[(J - 1) * w_cs];
     j = J - 2;
     for (; j - (U - 1) >= 0; j -= U) {
-      double qj[U], gj[U];
+      double sj[U], tj[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) { qj[u] = Q_[(j - u) * f_cs]; gj[u] = W_[(j - u) * w_cs]; }
+      for (int u = 0; u < U; ++u) { sj[u] = S_[(j - u) * f_cs]; tj[u] = W_[(j - u) * w_cs]; }
 #pragma unroll
-      for (int u = 0; u < U; ++u) { x = fma(-qj[u], x, gj[u]); W_[(j - u) * w_cs] = x; }
+      for (int u = 0; u < U; ++u) { z = fma(-sj[u], z, tj[u]); W_[(j - u) * w_cs] = z; }
     }
-    for (; j >= 0; --j) { x = fma(-Q_[j * f_cs], x, W_[j * w_cs]); W_[j * w_cs] = x; }
+    for (; j >= 0; --j) { z = fma(-S_[j * f_cs], z, W_[j * w_cs]); W_[j * w_cs] = z; }
   }
 }
 

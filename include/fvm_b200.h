@@ -7,10 +7,12 @@
  *
  * Conventions
  *  - every pointer is a DEVICE pointer to fp64 data unless stated otherwise;
- *  - the caller owns every buffer; the library allocates nothing and keeps no
- *    state between calls; all work is enqueued on `stream` (a CUstream /
- *    cudaStream_t handle passed as void*; NULL = the legacy default stream) and
- *    no call synchronises the host;
+ *  - the caller owns every buffer; the library allocates nothing, keeps no state
+ *    between calls and reads no environment variable (one exception, stated at its
+ *    declaration: fvm_spike_local_static works in a fixed device array inside the
+ *    library image, whose contents persist from call to call); all work is
+ *    enqueued on `stream` (a CUstream / cudaStream_t handle passed as void*;
+ *    NULL = the legacy default stream) and no call synchronises the host;
  *  - strided arrays: element (problem p, cell j) of X lives at X[p*X_ps + j*X_cs]
  *    (strides in elements).  Problem-major [P][J] is (ps=J, cs=1); interleaved
  *    [J][P] is (ps=1, cs=P); a per-problem scalar is (ps=1, cs=0); one array
@@ -91,11 +93,14 @@ int fvm_assemble(const fvm_problem* prob, double* lo, double* di, double* up, do
  * and the per-step SuperLU factorisation inside spsolve (:411).
  * In : M diagonals (strides m_ps, m_cs), dt[P] (the reference's `k`), theta in (0, 1],
  *      alpha end entries, beta_left/right [P] (may be NULL = 0).
- * Out: fp, fq, fb (strides f_ps, f_cs), bt_left/bt_right [P]:
- *        inv_j = 1/(A_jj - A_j,j-1 * fq_{j-1});  fp_j = A_j,j-1 * inv_j;  fq_j = A_j,j+1 * inv_j;
- *        fb_j  = inv_j * B_jj;   bt = beta * inv  at the two ends.
- *      With c = (1-theta)/theta the off-diagonals of inv*B are -c*fp and -c*fq, so the
- *      three arrays carry both operators. */
+ * Out: fp, fq, fb (strides f_ps, f_cs), bt_left/bt_right [P] -- the un-normalised LU factors
+ *      of A, which carry both operators because B = I/theta - c A with c = (1-theta)/theta:
+ *        pivot_j = A_jj - fp_j * A_j-1,j ;  fp_j = l_j = A_j,j-1 / pivot_{j-1} ;
+ *        fq_j = s_j = A_j,j+1 / pivot_j ;   fb_j = kappa_j = 1 / (theta * pivot_j) ;
+ *        bt = theta * beta at the two ends.
+ *      The pivot recurrence is evaluated in double-double and each factor is rounded once:
+ *      the step kernels apply the same factors at every step, so chain round-off would
+ *      otherwise grow linearly with the number of steps. */
 int fvm_theta_factor(int64_t J, int64_t P, const double* lo, const double* di, const double* up,
                      int64_t m_ps, int64_t m_cs, const double* dt, double theta,
                      int32_t alpha_left, int32_t alpha_right, const double* beta_left,
@@ -103,7 +108,8 @@ int fvm_theta_factor(int64_t J, int64_t P, const double* lo, const double* di, c
                      int64_t f_ps, int64_t f_cs, double* bt_left, double* bt_right, void* stream);
 
 /* Variant 1: `nsteps` theta steps, one thread per system, state updated IN PLACE.
- * Replaces the loop body  rhs = B*w + beta ; w = spsolve(A, rhs)  [fvm_classes.py:408-411].
+ * Replaces the loop body  rhs = B*w + beta ; w = spsolve(A, rhs)  [fvm_classes.py:408-411],
+ * evaluated as  w' = (1/theta) A^-1 (w + theta*beta) - c w  (no right-hand side is formed).
  * Streams fp/fq/fb and w from HBM every step; use the interleaved layout (ps=1, cs=P)
  * for both so that a warp's accesses coalesce.  Any J >= 3. */
 int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, const double* fq,
@@ -281,8 +287,11 @@ int64_t fvm_spike_static_max_tiles(void);
  *  - Same arguments, results and status codes as fvm_spike_local, minus `rs`; allocates nothing.
  *  - P * n_tiles must not exceed fvm_spike_static_max_tiles(); beyond that the call returns
  *    FVM_ERR_SCRATCH_LIMIT and launches nothing (use fvm_spike_local with your own `rs`).
- *  - The first call on each device looks up the device address of the built-in array (with that
- *    device current) and remembers it; make that first call before any stream capture begins.
+ *  - Every call looks up the device address of the built-in array for the CURRENT device, which
+ *    must therefore be the device `stream` belongs to (cudaSetDevice before the call).  Nothing is
+ *    remembered between calls, so cudaDeviceReset() or a second context on the device is harmless.
+ *    The first call on a device makes the CUDA runtime load the library's module there: make that
+ *    first call before any stream capture begins.
  *  - All calls on a device share the one array, and it keeps what the last call wrote.  Nothing in
  *    it needs clearing (each call overwrites the part it uses before reading it), but two calls
  *    whose kernels overlap on the GPU -- different streams, or several host threads -- race on it:

@@ -34,7 +34,8 @@ The module also holds two helpers that are NOT in the reference and say so:
 :func:`kappa_fitted` (the cancellation-safe Bernoulli form the CUDA path uses, so
 that the GPU can be checked where the reference's formula returns NaN, Pe >= 709.8)
 and :func:`theta_run_thomas` (a no-pivot Thomas loop in numpy ``longdouble``, the
-arbiter when SuperLU and the GPU disagree by O(eps * cond)).
+arbiter when SuperLU and the GPU disagree by O(eps * cond)) with its C twin
+:func:`theta_run_arbiter` (``oracle/thomas_arbiter.c``: __float128, for 10^4-step runs).
 """
 from __future__ import annotations
 
@@ -315,6 +316,35 @@ def theta_run_thomas(A, B, beta, w_init, nsteps, every=1, dtype=np.longdouble):
         if (n + 1) % every == 0:
             out.append(np.asarray(w, dtype=float))
     return np.array(out)
+
+
+def theta_run_arbiter(A, B, beta, w_init, nsteps, snaps=None, precision="quad"):
+    """NOT IN THE REFERENCE.  The recurrence of :func:`theta_run_thomas` in C (oracle/thomas_arbiter.c,
+    built by oracle/Makefile), carried in __float128 ('quad') or long double: the exact solution of
+    the reference's fp64 operators, fast enough for 10^4-step runs.  A, B: dicts of (J,) diagonals;
+    returns the states after the steps listed in ``snaps`` (default: the last one), shape [n, J]."""
+    import ctypes
+    import os
+    so = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_build", "libthomas_arbiter.so")
+    if not os.path.exists(so):
+        import subprocess
+        subprocess.run(["make", "-C", os.path.dirname(so)[:-len("/_build")], "-s"], check=True)
+    lib = ctypes.CDLL(so)
+    fn = lib.arbiter_run_quad if precision == "quad" else lib.arbiter_run_longdouble
+    dp = ctypes.POINTER(ctypes.c_double)
+    ip = ctypes.POINTER(ctypes.c_int64)
+    fn.restype = ctypes.c_int
+    fn.argtypes = [ctypes.c_int64, ctypes.c_int64] + [dp] * 8 + [ctypes.c_int64, ip, dp]
+    arrs = [np.ascontiguousarray(x, dtype=np.float64) for x in
+            (A["lo"], A["di"], A["up"], B["lo"], B["di"], B["up"], beta, w_init)]
+    J = arrs[1].shape[0]
+    snaps = np.ascontiguousarray([nsteps] if snaps is None else snaps, dtype=np.int64)
+    out = np.zeros((len(snaps), J))
+    st = fn(J, int(nsteps), *[a.ctypes.data_as(dp) for a in arrs], len(snaps),
+            snaps.ctypes.data_as(ip), out.ctypes.data_as(dp))
+    if st != 0:
+        raise MemoryError("thomas_arbiter: allocation failed")
+    return out
 
 
 # --------------------------------------------------------------------------- synthetic inputs

@@ -1,36 +1,37 @@
-"""Parity over cfg 3's FULL run length (10,000 Crank-Nicolson steps) on the stiffest problems of the
-sweep (smallest Peclet number: largest dt*d/h^2, where round-off survives longest), against the
-reference's scipy loop (oracle) and against the longdouble Thomas arbiter.
+"""Parity over cfg 3's FULL run length (10,000 Crank-Nicolson steps) on the 16 stiffest problems of
+the whole 65,536-problem sweep (tests/golden/cfg3_long_run.npz): the CUDA path with the reference's
+own modified diffusivity against the reference's scipy loop and the exact solution of its
+operators, and with its own Bernoulli-form fitting against the exact solution of those operators.
     python profiles/microbench/long_run_parity.py [fused|thomas] > gpurun_out/long_run_parity.txt"""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
 import numpy as np
-import torch
-from oracle import fvm_oracle as O
 from fvm_b200 import BatchedAdvectionDiffusionModel, workloads as W
 
-J, ns, pool, pick = 1024, 10000, 4096, 6
-wl = W.batched_sweep(65536, J, first=0, count=pool)
-pe = wl["a"] / wl["d"]
-idx = np.concatenate([np.argsort(pe)[:pick - 2], np.argsort(pe)[-2:]])     # the stiffest, and two advective ones
-m = BatchedAdvectionDiffusionModel(wl["faces"], wl["a"][idx], wl["d"][idx], wl["k"][idx], "exponential")
-m.set_boundary_conditions(**wl["bc"])
+g = np.load(os.path.join(ROOT, "tests", "golden", "cfg3_long_run.npz"))
 variant = sys.argv[1] if len(sys.argv) > 1 else "fused"
+sc0 = 1e-6 * np.max(np.abs(g["w0"]), axis=-1)
 print("variant", variant)
-w, _ = m.run(wl["w0"][idx], 0.5, ns, variant=variant)
-w = w.cpu().numpy()
-As, Bs, betas = [], [], []
-for n, p in enumerate(idx):
-    asm = O.assemble(wl["faces"], wl["a"][p], wl["d"][p], "exponential", **wl["bc"])
-    A, B = O.theta_operators(asm, wl["k"][p], 0.5)
-    As.append(A); Bs.append(B); betas.append(asm["beta"])
-    ref = O.theta_run_scipy(asm, wl["k"][p], 0.5, wl["w0"][p], ns, every=ns)[0]
-    sc = max(np.max(np.abs(ref)), 1e-6 * np.max(np.abs(wl["w0"][p])))
-    print("problem %5d  a/d %.3e  gpu-vs-scipy %.2e" % (p, pe[p], np.max(np.abs(w[n] - ref)) / sc), flush=True)
-stack = lambda L, k: np.stack([x[k] for x in L])
-A = {k: stack(As, k) for k in ("lo", "di", "up")}
-B = {k: stack(Bs, k) for k in ("lo", "di", "up")}
-arb = O.theta_run_thomas(A, B, np.stack(betas), wl["w0"][idx], ns, every=ns)[0].astype(float)
-for n, p in enumerate(idx):
-    sc = max(np.max(np.abs(arb[n])), 1e-6 * np.max(np.abs(wl["w0"][p])))
-    print("problem %5d  gpu-vs-longdouble %.2e" % (p, np.max(np.abs(w[n] - arb[n])) / sc), flush=True)
+print("problems", " ".join(str(int(p)) for p in g["problems"]))
+print("a/d", " ".join("%.3g" % x for x in g["a"] / g["d"]), " k*d", " ".join("%.3g" % x for x in g["k"] * g["d"]))
+
+
+def err(got, want):
+    return np.max(np.abs(got - want), axis=-1) / np.maximum(np.max(np.abs(want), axis=-1), sc0)
+
+
+for label, scheme, d, targets in (("reference D (central scheme on D_reference)", "central", g["D_reference"], ("reference", "exact")),
+                                  ("own fitting (exponential scheme)", "exponential", g["d"], ("exact_fitted", "reference"))):
+    m = BatchedAdvectionDiffusionModel(W.graded_faces(1024), g["a"], d, g["k"], scheme)
+    m.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
+    w, ck = m.run(g["w0"], 0.5, 10000, checkpoint_every=1000, variant=variant)
+    ck = ck.cpu().numpy()
+    print(label)
+    for i, s in enumerate(g["snaps"]):
+        for name in targets:
+            e = err(ck[int(s) // 1000 - 1], g[name][:, i])
+            print("  step %5d vs %-12s max %.2e   per problem: %s" % (s, name, e.max(), " ".join("%.1e" % x for x in e)))
+for a, b in (("reference", "exact"), ("exact_fitted", "exact")):
+    e = np.max(np.abs(g[a] - g[b]), axis=-1) / np.max(np.abs(g[b]), axis=-1)
+    print("%s vs %s at steps %s: max %s" % (a, b, [int(s) for s in g["snaps"]], " ".join("%.1e" % x for x in e.max(axis=0))))

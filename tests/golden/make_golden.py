@@ -132,10 +132,66 @@ def cfg3_subset():
     return dict(snaps=np.array(snaps), states=np.array(states), a=wl["a"], d=wl["d"], k=wl["k"])
 
 
+LONG_RUN_STEPS = 10000
+LONG_RUN_SNAPS = [1000, 5000, 10000]
+
+
+def long_run_problems(n_each=8):
+    """The problems of cfg 3's 65,536 where round-off survives longest: the n_each smallest a/d
+    (most diffusive: largest dt*d/h^2 everywhere) and the n_each largest dt*d (stiffest fine end)."""
+    wl = W.batched_sweep(65536, 1024)
+    pe = wl["a"] / wl["d"]
+    kd = wl["k"] * wl["d"]
+    first = list(np.argsort(pe)[:n_each])
+    rest = [p for p in np.argsort(-kd) if p not in first][:n_each]
+    return wl, np.array(sorted(first + rest))
+
+
+def _long_run_one(args):
+    faces, a, d, k, bc, w0 = args
+    return R.reference_theta_run(faces, a, d, k, "exponential", bc, 0.5, w0, LONG_RUN_STEPS,
+                                 every=1)[[s - 1 for s in LONG_RUN_SNAPS]]
+
+
+def cfg3_long_run():
+    """cfg 3 at its FULL run length: the reference's literal scipy loop for all 10,000
+    Crank-Nicolson steps on the 16 stiffest problems of the 65,536-problem sweep, snapshots after
+    1,000 / 5,000 / 10,000 steps (`reference`), with the reference's own modified diffusivity of
+    every cell (`D_reference`, fvm_classes.py:117-131).  Beside it:
+      exact        -- the exact solution of the reference's fp64 operators (oracle/thomas_arbiter.c,
+                      __float128 Thomas).  The reference's SuperLU loop is 2e-12 ... 9e-11 from it
+                      after 10,000 steps: that is what a tolerance of 1e-10 has to absorb.
+      exact_fitted -- the same with the exponential fitting evaluated in the cancellation-safe
+                      form D = d (B(mu) + mu/2) (oracle.fitted_D; what north_star asks the CUDA path
+                      to use).  It is up to 7e-10 from `exact`: at these cell Peclet numbers
+                      (1e-4 ... 1e-2) the reference's kappa formula (:117) carries a cancellation
+                      error of ~1e-12 relative in D, per cell and depending on the libm behind
+                      numpy.exp, and 10,000 steps of a stiff operator amplify it that far."""
+    from concurrent.futures import ProcessPoolExecutor
+    wl, idx = long_run_problems()
+    jobs = [(wl["faces"], wl["a"][p], wl["d"][p], wl["k"][p], wl["bc"], wl["w0"][p]) for p in idx]
+    with ProcessPoolExecutor(min(8, os.cpu_count() or 1)) as ex:
+        ref = np.array(list(ex.map(_long_run_one, jobs)))
+    exact, exact_fitted, D_ref = [], [], []
+    for p in idx:
+        D_ref.append(R.reference_assembly(wl["faces"], wl["a"][p], wl["d"][p], wl["k"][p], "exponential",
+                                          wl["bc"])["D"])
+        for mode, out in (("reference", exact), ("fitted", exact_fitted)):
+            asm = O.assemble(wl["faces"], wl["a"][p], wl["d"][p], "exponential", exponential=mode, **wl["bc"])
+            if mode == "reference":
+                assert np.array_equal(asm["D"], D_ref[-1])
+            A, B = O.theta_operators(asm, wl["k"][p], 0.5)
+            out.append(O.theta_run_arbiter(A, B, asm["beta"], wl["w0"][p], LONG_RUN_STEPS, LONG_RUN_SNAPS))
+        print("long run exact", p, flush=True)
+    return dict(problems=idx, snaps=np.array(LONG_RUN_SNAPS), reference=ref, exact=np.array(exact),
+                exact_fitted=np.array(exact_fitted), D_reference=np.array(D_ref),
+                a=wl["a"][idx], d=wl["d"][idx], k=wl["k"][idx], w0=wl["w0"][idx])
+
+
 if __name__ == "__main__":
     only = sys.argv[1:]
     jobs = dict(assembly_cases=assembly_cases, cfg1_examples=cfg1_examples, demo_J149=demo_J149,
-                cfg3_subset=cfg3_subset, cfg2_subset=cfg2_subset)
+                cfg3_subset=cfg3_subset, cfg2_subset=cfg2_subset, cfg3_long_run=cfg3_long_run)
     for name, fn in jobs.items():
         if only and name not in only:
             continue

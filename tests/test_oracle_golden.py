@@ -146,3 +146,38 @@ def test_oracle_against_live_reference():
     ref = R.reference_theta_run(f, 1.0, 5e-3, 0.01, "exponential", bcs[1], 0.5, w0, 20)
     got = O.theta_run_scipy(O.assemble(f, 1.0, 5e-3, "exponential", **bcs[1]), 0.01, 0.5, w0, 20)
     assert np.array_equal(ref, got)
+
+
+def test_cfg3_long_run_fixture_says_what_the_gpu_tests_rely_on():
+    """tests/golden/cfg3_long_run.npz (10,000 Crank-Nicolson steps, the 16 stiffest problems of
+    cfg 3): pins the oracle and the C arbiter to it on one problem, and checks the three facts
+    tests/test_gpu_long_run.py builds on."""
+    g = load_golden("cfg3_long_run")
+    faces = W.graded_faces(1024)
+    bc = dict(left_flux=0.0, right_flux=0.0)
+    rel = lambda x, y: np.max(np.abs(x - y), axis=-1) / np.max(np.abs(y), axis=-1)
+    # (1) the reference's own loop is within 1e-10 of the exact solution of its operators, barely
+    e = rel(g["reference"], g["exact"])
+    assert 5e-11 < e.max() < 1e-10
+    # (2) the reference's kappa formula is noisy at these cell Peclet numbers: its D differs from the
+    # cancellation-safe evaluation by ~1e-12 relative ...
+    i = 2
+    asm_ref = O.assemble(faces, g["a"][i], g["d"][i], "exponential", **bc)
+    asm_fit = O.assemble(faces, g["a"][i], g["d"][i], "exponential", exponential="fitted", **bc)
+    assert np.array_equal(asm_ref["D"], g["D_reference"][i])
+    dD = np.abs(asm_ref["D"] - asm_fit["D"]) / asm_fit["D"]
+    assert 1e-13 < dD.max() < 5e-12
+    # ... which 10,000 stiff steps amplify beyond the 1e-10 parity tolerance
+    assert rel(g["exact_fitted"], g["exact"]).max() > 3e-10
+    # (3) oracle restatement + arbiter reproduce the fixture (first snapshot: 1,000 steps)
+    A, B = O.theta_operators(asm_ref, g["k"][i], 0.5)
+    n = int(g["snaps"][0])
+    got = O.theta_run_arbiter(A, B, asm_ref["beta"], g["w0"][i], n)[0]
+    assert np.array_equal(got, g["exact"][i, 0])
+    got = O.theta_run_scipy(asm_ref, g["k"][i], 0.5, g["w0"][i], n, every=n)[0]
+    assert rel(got, g["reference"][i, 0]) < 1e-12
+    # the longdouble numpy arbiter and the C one agree (short run: the numpy loop is slow)
+    short = O.theta_run_arbiter(A, B, asm_ref["beta"], g["w0"][i], 20)[0]
+    slow = O.theta_run_thomas({k: v[None] for k, v in A.items()}, {k: v[None] for k, v in B.items()},
+                              asm_ref["beta"][None], g["w0"][i][None], 20, every=20)[0][0]
+    assert rel(slow, short) < 1e-15
