@@ -55,6 +55,7 @@ def parse():
                          "cfg5: one mesh of 2^27 cells per GPU split over the ranks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-long-legs", action="store_true", help="skip the variant-3 legs (cfg 5 / cfg 4) of the default run")
     return ap.parse_args()
 
 
@@ -207,30 +208,200 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0}, "fallback (B200_PROFILING.md)"
 
 
-def partitioned_leg(dev, peaks, peak_src, log2_cells=26, nsteps=10):
-    """Variant 3 on one long system (cfg 5 parameters, single GPU): HBM roofline evidence."""
+def _slab_rows(faces, a, d, dt, theta, J, j0, j1, f_lo):
+    """CHECKER ONLY (not the product path): rows of A = I - dt*theta*M and B = I + dt*(1-theta)*M for the
+    global cells [j0, j1) of a graded mesh, scalar a and d, exponential fitting, zero-flux Robin ends,
+    restated in torch from SURVEY.md 8(a)'s closed form [fvm_classes.py:117-131,149-177,376-377].  Used
+    for the full-size residual ||A w_new - B w_old|| of the cfg 5 leg, where no oracle can run."""
     import torch
-    from fvm_b200 import PartitionedAdvectionDiffusionModel, workloads as W
-    J = 1 << log2_cells
-    sl = W.graded_slab(J, 0, J, dev)
-    m = PartitionedAdvectionDiffusionModel(sl["faces"], 1.0, sl["d_pe2"], sl["dt"], "exponential", P=1, J=J, device=dev)
-    m.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
-    m.prepare(0.5)
-    m.set_state(sl["w0"])
+    f = faces                                  # faces[i] = global face f_lo + i
+    o = j0 - f_lo                              # local index of face j0
+    n = j1 - j0
+    h = f[1:] - f[:-1]                         # widths of global cells f_lo ...
+    c = 0.5 * (f[1:] + f[:-1])
+    mu = a * h / d
+    D = d * (mu / torch.expm1(mu) + 0.5 * mu)
+    dx = c[1:] - c[:-1]                        # face between local cells i, i+1
+    af = h[1:] / (2 * dx) * a + h[:-1] / (2 * dx) * a   # NOT a: at 2^27+ cells dx carries ~1e-7 of rounding, as in the reference's arithmetic
+    Df = h[1:] / (2 * dx) * D[:-1] + h[:-1] / (2 * dx) * D[1:]
+    A_hi, A_lo, Dd = af * h[1:] / (2 * dx), af * h[:-1] / (2 * dx), Df / dx
+    z = torch.zeros(1, dtype=f.dtype, device=f.device)
+    # face arrays indexed by local cell: left face of cell i = face i-1, right face = face i; pad outside the mesh
+    def left(x):
+        return torch.cat([z, x])[o:o + n] if f_lo == 0 else x[o - 1:o - 1 + n]
+    def right(x):
+        full = torch.cat([x, z]) if f_lo + f.numel() - 1 == J else x
+        return full[o:o + n]
+    hh = h[o:o + n]
+    lo = (left(A_hi) + left(Dd)) / hh
+    di = (left(A_lo) - right(A_hi) - left(Dd) - right(Dd)) / hh
+    up = (-right(A_lo) + right(Dd)) / hh
+    sA, sB = dt * theta, dt * (1 - theta)
+    return (-sA * lo, 1 - sA * di, -sA * up), (sB * lo, 1 + sB * di, sB * up)
+
+
+def _timed_steps(m, dev, world, local, min_seconds=2.0):
+    """Warm up, find a step count that lasts `min_seconds`, time it with CUDA events and the clock sampler;
+    returns (ms per theta step = max over ranks, steps, clocks)."""
+    import torch
+    import torch.distributed as dist
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
     m.step(3)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(); m.step(10); e1.record()
     torch.cuda.synchronize()
-    e0.record(); m.step(nsteps); e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / nsteps
-    gbs = HBM_B_PER_CELL_UPDATE_SPIKE * J / (ms * 1e-3) / 1e9
-    return {"kernel": "tile_solve_kernel + reduced + correct (variant 3, one system of 2^%d cells)" % log2_cells,
-            "bound": "hbm", "cell_updates_per_s": J / (ms * 1e-3), "ms_per_theta_step": ms, "achieved": gbs,
-            "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "peak_source": peak_src,
-            "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_SPIKE,
-            "spike_extents_cells": [int(m.extents[0]), int(m.extents[1])], "tile_cells": m.T,
-            "traffic": ncu_traffic("r01_spike_tile_solve.summary.txt"),
-            "traffic_note": "tile_solve_kernel only, one launch at 2^26 cells (algorithmic 40 B x 2^26 = 2.68e9)"}
+    t = torch.tensor([e0.elapsed_time(e1) / 10], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    n = int(min(5000, max(20, np.ceil(min_seconds * 1e3 / float(t.item())))))
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    e0.record(); m.step(n); e1.record()
+    barrier()
+    clocks = sampler.stop()
+    t = torch.tensor([e0.elapsed_time(e1) / n], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item()), n, clocks
+
+def long_system_legs(world, rank, local, dev, peaks, peak_src, group):
+    """Variant 3 inside the default (driver-run) command, on ALL ranks:
+    cfg 5 -- ONE graded mesh of world x 2^27 cells split over the ranks (SPIKE, one 4-double NCCL all-gather
+    per theta step), timed for >= 2 s with clocks, next to the same kernels on 2^27 cells per rank with no
+    communication (the N = 1 figure the weak efficiency is quoted against), the all-gather's own duration,
+    agreement with a single-GPU solve of the whole mesh after 20 steps, and the residual of one step at
+    full size; cfg 4 -- 512 problems x 2^20 cells per GPU (BASELINE's 4,096 on 8 GPUs), theta = 1."""
+    import torch
+    import torch.distributed as dist
+    from fvm_b200 import PartitionedAdvectionDiffusionModel, workloads as W
+    from fvm_b200.partitioned import plan_partition
+    out = {}
+    T, Jr = 8192, 1 << 27
+
+    def model_cfg5(J, j0, j1, grp):
+        sl = W.graded_slab(J, j0, j1, dev)
+        m = PartitionedAdvectionDiffusionModel(sl["faces"], 1.0, sl["d_pe2"], sl["dt"], "exponential", P=1, J=J,
+                                               group=grp, device=dev)
+        m.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
+        m.prepare(0.5)
+        m.set_state(sl["w0"])
+        return m, sl
+
+    # ---- cfg 5, every rank alone on 2^27 cells (no collective): the N = 1 reference of the weak scaling
+    m1, _ = model_cfg5(Jr, 0, Jr, None)
+    ms1, n1, clocks1 = _timed_steps(m1, dev, world, local)
+    extents = [int(m1.extents[0]), int(m1.extents[1])]
+    del m1
+    torch.cuda.empty_cache()
+    leg = {"kernel": "tile_solve_kernel + reduced + separators (variant 3), cfg5: one graded mesh of %d x 2^27 cells"
+                     % world, "bound": "hbm", "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_SPIKE,
+           "peak": peaks["hbm_gbs"], "unit": "GB/s", "peak_source": peak_src, "tile_cells": T,
+           "spike_extents_cells": extents,
+           "single_gpu": {"cells": Jr, "ms_per_theta_step": ms1, "steps_timed": n1, "clocks": clocks1,
+                          "cell_updates_per_s": Jr / (ms1 * 1e-3),
+                          "achieved": HBM_B_PER_CELL_UPDATE_SPIKE * Jr / (ms1 * 1e-3) / 1e9},
+           "traffic": ncu_traffic("r01_spike_tile_solve.summary.txt"),
+           "traffic_note": "tile_solve_kernel only, one launch at 2^26 cells (algorithmic 40 B x 2^26 = 2.68e9)"}
+    # ---- cfg 5 proper: one mesh over all ranks
+    J = world * Jr
+    j0, j1 = plan_partition(J, T, world)["ranges"][rank]
+    m, sl = model_cfg5(J, j0, j1, group)
+    msN, nN, clocksN = _timed_steps(m, dev, world, local)
+    gather_us = None
+    if world > 1:
+        m.comm.timing = []
+        m.step(200)
+        torch.cuda.synchronize()
+        gather_us = 1e3 * float(np.mean([a.elapsed_time(b) for a, b in m.comm.timing]))
+        m.comm.timing = None
+    gbs = HBM_B_PER_CELL_UPDATE_SPIKE * Jr / (msN * 1e-3) / 1e9
+    leg.update({"cells": J, "n_gpus": world, "nccl_ranks": world if world > 1 else 0,
+                "ms_per_theta_step": msN, "steps_timed": nN, "clocks": clocksN,
+                "cell_updates_per_s": J / (msN * 1e-3), "achieved": gbs, "frac": gbs / peaks["hbm_gbs"],
+                "achieved_note": "per GPU: 40 B x 2^27 cells / ms_per_theta_step (whole step incl. the collective)",
+                "weak_efficiency_vs_n1": ms1 / msN,
+                "collective": {"name": "ncclAllGather (torch.distributed.all_gather_into_tensor), 4 doubles per rank "
+                                       "and step (fvm_b200/partitioned.py: _step_rank_level)",
+                               "us_per_step": gather_us,
+                               "share_of_step": None if gather_us is None else gather_us * 1e-3 / msN}})
+    # ---- residual of ONE theta step at full size: || A w_new - B w_old ||_inf / || B w_old ||_inf
+    m.set_state(sl["w0"])
+    m.step(19)
+    w_old = m.get_state()[0]
+    m.step(1)
+    w_new = m.get_state()[0]
+    gl = lambda w: torch.stack([w[0], w[-1]])
+    if world > 1:
+        e_old = [torch.empty(2, dtype=w_old.dtype, device=dev) for _ in range(world)]
+        e_new = [torch.empty(2, dtype=w_old.dtype, device=dev) for _ in range(world)]
+        dist.all_gather(e_old, gl(w_old)); dist.all_gather(e_new, gl(w_new))
+    zero = torch.zeros((), dtype=w_old.dtype, device=dev)
+    def ghosted(w, edges):
+        left = edges[rank - 1][1] if rank > 0 else zero
+        right = edges[rank + 1][0] if rank + 1 < world else zero
+        return torch.cat([left[None], w, right[None]])
+    go = ghosted(w_old, e_old if world > 1 else None)
+    gn = ghosted(w_new, e_new if world > 1 else None)
+    del w_old
+    (Al, Ad, Au), (Bl, Bd, Bu) = _slab_rows(m.faces, 1.0, sl["d_pe2"], sl["dt"], 0.5, J, m.j0, m.j1, m.f_lo)
+    rhs = Bl * go[:-2] + Bd * go[1:-1] + Bu * go[2:]
+    res = Al * gn[:-2] + Ad * gn[1:-1] + Au * gn[2:] - rhs
+    r = torch.stack([res.abs().max(), rhs.abs().max()])
+    del Al, Ad, Au, Bl, Bd, Bu, rhs, res, go, gn
+    if world > 1:
+        dist.all_reduce(r, op=dist.ReduceOp.MAX)
+    leg["residual_after_20_steps"] = {"value": float(r[0] / r[1]), "what": "max |A w_21 - B w_20| / max |B w_20| over all "
+                                      "%d cells, A and B restated in torch from the mesh (bench.py: _slab_rows)" % J}
+    # ---- N ranks against ONE GPU on the same mesh (rank 0 solves all of it; it fits: 7 arrays of J doubles)
+    if world > 1:
+        full = torch.empty(J, dtype=torch.float64, device=dev)
+        if rank == 0:
+            ms_, sl_ = model_cfg5(J, 0, J, None)
+            ms_.step(20)
+            full.copy_(ms_.get_state()[0])
+            del ms_, sl_
+            torch.cuda.empty_cache()
+        dist.broadcast(full, 0)
+        d = torch.stack([(w_new - full[m.j0:m.j1]).abs().max(), full[m.j0:m.j1].abs().max()])
+        # w_new is the state after 20 steps of the distributed run
+        dist.all_reduce(d, op=dist.ReduceOp.MAX)
+        mv = (w_new - sl["w0"][0]).abs().max()[None]
+        dist.all_reduce(mv, op=dist.ReduceOp.MAX)
+        leg["agreement_1_vs_n_ranks"] = {"value": float(d[0] / d[1]), "steps": 20,
+                                         "state_change_over_the_20_steps": float(mv[0] / d[1]),
+                                         "what": "max |w(%d ranks) - w(1 GPU)| / max |w| over all %d cells" % (world, J)}
+        del full
+    del m, sl, w_new
+    torch.cuda.empty_cache()
+    out["roofline_long_system_variant"] = leg
+    # ---- cfg 4: 512 problems x 2^20 cells per GPU, theta = 1, dt = 100 h_min / a, reaction term; no communication
+    Pn, J4 = 512, 1 << 20
+    wl = W.stiff_reaction(P=world * Pn, J=J4, first=rank * Pn, count=Pn)
+    m4 = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=Pn,
+                                            reaction=wl["reaction"], device=dev)
+    m4.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
+    m4.prepare(1.0)
+    m4.set_state(torch.as_tensor(wl["w0"], device=dev))
+    ms4, n4, clocks4 = _timed_steps(m4, dev, world, local)
+    finite = bool(torch.isfinite(m4.get_state()).all())
+    g4 = HBM_B_PER_CELL_UPDATE_SPIKE * Pn * J4 / (ms4 * 1e-3) / 1e9
+    out["cfg4_long_systems"] = {
+        "workload": "cfg4 stiff reaction-diffusion: %d problems/GPU x 2^20 cells (BASELINE: 4,096 = 512 per GPU on 8 GPUs), "
+                    "per-problem a/d/reaction, theta = 1, dt = 100 h_min/a, sharded, no communication" % Pn,
+        "n_gpus": world, "cell_updates_per_s": world * Pn * J4 / (ms4 * 1e-3), "ms_per_theta_step": ms4,
+        "steps_timed": n4, "clocks": clocks4, "bound": "hbm", "achieved": g4, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+        "frac": g4 / peaks["hbm_gbs"], "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_SPIKE,
+        "note": "per GPU; every cell lies inside the spike extents here (dt = 100 h_min/a: the spikes do not decay), so "
+                "the kernels really move 56 B per cell-update", "finite": finite,
+        "spike_extents_cells": [int(m4.extents[0]), int(m4.extents[1])]}
+    del m4, wl
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_partitioned(args):
@@ -461,12 +632,12 @@ def run_b200(args):
         except Exception as exc:  # noqa: BLE001
             hbm = {"error": repr(exc)}
 
-    long_leg = None
-    if rank == 0:
-        try:
-            long_leg = partitioned_leg(dev, peaks, peak_src, log2_cells=26)
-        except Exception as exc:  # noqa: BLE001
-            long_leg = {"error": repr(exc)}
+    # ---- variant 3 (cfg 5 over all ranks with its NCCL all-gather, cfg 4 sharded), every rank takes part
+    del w, w0, model
+    torch.cuda.empty_cache()
+    long_legs = {"roofline_long_system_variant": None, "cfg4_long_systems": None}
+    if not args.no_long_legs:
+        long_legs = long_system_legs(world, rank, local, dev, peaks, peak_src, dist.group.WORLD if world > 1 else None)
 
     if rank != 0:
         if world > 1:
@@ -521,7 +692,8 @@ def run_b200(args):
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": config(args), "e2e": e2e, "gpu_launches": K,
             "clocks": clocks, "roofline": roofline, "roofline_streaming_variant": hbm,
-            "roofline_long_system_variant": long_leg, "cpu_baseline": cpu, "finite": finite}
+            "roofline_long_system_variant": long_legs["roofline_long_system_variant"],
+            "cfg4_long_systems": long_legs["cfg4_long_systems"], "cpu_baseline": cpu, "finite": finite}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -39,6 +39,7 @@ class Comm(object):
 
     def __init__(self, group=None):
         self.group = group
+        self.timing = None          # set to a list to collect (start, end) CUDA events of every gather
         if group is None:
             self.rank, self.world, self.backend = 0, 1, None
         else:
@@ -59,6 +60,13 @@ class Comm(object):
             return torch.stack(parts).to(t.device)
         t = t.contiguous()
         out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+        if self.timing is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            dist.all_gather_into_tensor(out, t, group=self.group)
+            e1.record()
+            self.timing.append((e0, e1))
+            return out
         dist.all_gather_into_tensor(out, t, group=self.group)
         return out
 

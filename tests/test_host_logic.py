@@ -135,3 +135,25 @@ def test_bench_contract_pieces():
     assert bench.ncu_traffic("no_such_capture.txt") is None
     peaks, src = bench.measured_peaks()
     assert peaks["hbm_gbs"] > 1000 and "sm_max_mhz" in peaks and src
+
+
+def test_bench_slab_rows_checker_matches_the_oracle():
+    """bench.py's torch restatement of the rows of A and B (the full-size residual check of the
+    cfg 5 leg) against the oracle, for every kind of slab: first, middle, last, whole mesh."""
+    import importlib.util
+    import torch
+    from oracle import fvm_oracle as O
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_under_test2", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    J, a, d, dt, theta = 96, 1.0, 3e-3, 2e-3, 0.5
+    faces = O.graded_faces(J, 30.0)
+    asm = O.assemble(faces, a, d, "exponential", left_flux=0.0, right_flux=0.0, exponential="fitted")
+    A, B = O.theta_operators(asm, dt, theta)
+    for j0, j1 in ((0, 32), (32, 64), (64, 96), (0, 96)):
+        f_lo, f_hi = max(j0 - 1, 0), min(j1 + 1, J)
+        f = torch.as_tensor(faces[f_lo:f_hi + 1])
+        (Al, Ad, Au), (Bl, Bd, Bu) = bench._slab_rows(f, a, d, dt, theta, J, j0, j1, f_lo)
+        for got, want in ((Al, A["lo"]), (Ad, A["di"]), (Au, A["up"]), (Bl, B["lo"]), (Bd, B["di"]), (Bu, B["up"])):
+            assert np.allclose(got.numpy(), want[j0:j1], rtol=1e-12, atol=1e-13), (j0, j1)
