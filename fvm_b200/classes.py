@@ -15,9 +15,11 @@ import warnings
 
 import numpy as np
 from scipy import sparse
-from scipy.sparse import dia_matrix, linalg  # noqa: F401  (re-exported: scripts use `import *`)
+from scipy.sparse import dia_matrix  # noqa: F401  (re-exported: scripts use `import *`)
 
+from . import _lib
 from .batched import BatchedAdvectionDiffusionModel
+from .tracked import TrackedDia, linalg  # noqa: F401  (linalg: scipy.sparse.linalg with the spsolve fast path)
 
 # helper shapes of the reference module (fvm_classes.py:10-12), kept for `import *` users
 gaussian = lambda z, height, position, hwhm: height * np.exp(-np.log(2) * ((z - position) / hwhm) ** 2)  # noqa: E731
@@ -155,6 +157,8 @@ class AdvectionDiffusionModel(object):
         self.left_value = left_value
         self.right_value = right_value
         self._gpu.set_boundary_conditions(left_flux, right_flux, left_value, right_value)
+        self._m_host = None
+        self._dev_state = None
 
     def _assembled(self):
         if not hasattr(self, "left_flux"):
@@ -162,13 +166,24 @@ class AdvectionDiffusionModel(object):
                                  "(call set_boundary_conditions first)")
         return self._gpu.assemble()
 
-    def alpha_matrix(self):
-        """Mask that freezes Dirichlet rows; identity for a fully Robin system (:233-242)."""
+    def _alpha_diagonal(self):
         asm = self._assembled()
         diagonals = np.ones(self.mesh.J)
         diagonals[0] = asm["alpha_left"]
         diagonals[-1] = asm["alpha_right"]
-        return sparse.diags(diagonals, 0)
+        return diagonals
+
+    def _m_diagonals(self):
+        """lo, di, up of M as host arrays (read back once per set_boundary_conditions)."""
+        if getattr(self, "_m_host", None) is None:
+            asm = self._assembled()
+            self._m_host = tuple(asm[n][0].cpu().numpy() for n in ("lo", "di", "up"))
+        return self._m_host
+
+    def alpha_matrix(self):
+        """Mask that freezes Dirichlet rows; identity for a fully Robin system (:233-242).  A real
+        scipy ``dia_matrix`` (of a subclass that remembers which model it belongs to, tracked.py)."""
+        return TrackedDia.build(self, "alpha", 0.0, 1.0)
 
     def beta_vector(self):
         """The Robin boundary-condition vector (:244-263)."""
@@ -179,13 +194,27 @@ class AdvectionDiffusionModel(object):
         return b
 
     def coefficient_matrix(self):
-        """The J x J tridiagonal matrix M as a ``dia_matrix`` (:265-310)."""
-        asm = self._assembled()
-        J = self.mesh.J
-        lo = asm["lo"][0].cpu().numpy()
-        di = asm["di"][0].cpu().numpy()
-        up = asm["up"][0].cpu().numpy()
-        return dia_matrix(sparse.diags([lo[1:], di, up[:-1]], [-1, 0, 1], shape=(J, J)))
+        """The J x J tridiagonal matrix M as a ``dia_matrix`` (:265-310), tracked like alpha."""
+        return TrackedDia.build(self, "M")
+
+    def _gpu_theta_step(self, w, theta, dt):
+        """ONE theta step on the GPU for the spsolve fast path (tracked.py).  The state stays on the
+        device between calls: when ``w`` is the array the previous call returned (and nobody
+        changed it) nothing is uploaded."""
+        torch = _lib.require_cuda()
+        g = self._gpu
+        if float(g.k[0]) != float(dt):                 # the script's own k in I - k*theta*alpha*M wins
+            g.k = g.k.new_full((1,), float(dt))
+            g._factors = {}
+        st = getattr(self, "_dev_state", None)
+        if st is None or not np.array_equal(st[1], w):
+            dev = torch.as_tensor(w[None, :], device=g.device)
+        else:
+            dev = st[0]
+        new, _ = g.run(dev, theta, 1)
+        out = new[0].cpu().numpy()
+        self._dev_state = (new, out.copy())
+        return out
 
     # -------------------------------------------------------------- accelerated time loop
     def theta_run(self, w_init, theta, nsteps, checkpoint_every=0, variant="auto", save=None):
@@ -232,12 +261,10 @@ class Model(AdvectionDiffusionModel):
     theta = 0.5
 
     def A_matrix(self):
-        I = sparse.identity(self.mesh.J)
-        return I - self.k * self.theta * self.alpha_matrix() * self.coefficient_matrix()
+        return TrackedDia.build(self, "lin", 1.0, -(self.k * self.theta))
 
     def M_matrix(self):
-        I = sparse.identity(self.mesh.J)
-        return I + self.k * (1 - self.theta) * self.alpha_matrix() * self.coefficient_matrix()
+        return TrackedDia.build(self, "lin", 1.0, self.k * (1 - self.theta))
 
     def b_vector(self):
         return self.beta_vector()
