@@ -67,6 +67,9 @@ _SIGNATURES = {
     "fvm_fused_max_cells": (c_i64, []),
     "fvm_theta_run_fused": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_dbl, c_i64, c_i64,
                                            c_ptr, c_ptr, c_ptr]),
+    "fvm_fused_ex_max_cells": (c_i64, []),
+    "fvm_theta_run_fused_ex": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_dbl, c_i64, c_i64, c_ptr, c_ptr,
+                                              c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i64, c_i64, c_ptr, c_i64, c_ptr]),
     "fvm_spike_tile_cells": (c_i64, [c_i32]),
     "fvm_spike_tile_threads": (c_i64, [c_i32]),
     "fvm_spike_setup": (ctypes.c_int, [ctypes.POINTER(FvmProblem), c_ptr, c_dbl, c_i64, c_i64, c_i32,

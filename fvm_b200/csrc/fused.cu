@@ -44,7 +44,7 @@ struct Reduced {
   double invD;                   // 1 / final PCR diagonal
   double slo, sup;               // separator's row of A (off-diagonals)
   double sblo, sbdi, sbup;       // separator's row of B
-  double bfirst, bint, bsep;     // beta entries as they enter the sweeps
+  double bfirst, bint, bsep, bsep_r;   // beta entries as they enter the sweeps (bsep: left-flux part, bsep_r: right-flux part)
   int rb_c;                      // RB only: position of cell J-1 inside its lane
 };
 
@@ -74,7 +74,7 @@ __device__ __forceinline__ void setup_rows(const fvm_problem& pr, int64_t p, int
   if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
     beta_r = dvd(-pr.right_flux[p], sub(pr.faces[J], pr.faces[J - 1]));
   R.slo = 0.0; sdi = 1.0; R.sup = 0.0;
-  R.bfirst = 0.0; R.bint = 0.0; R.bsep = 0.0;
+  R.bfirst = 0.0; R.bint = 0.0; R.bsep = 0.0; R.bsep_r = 0.0;
   R.rb_c = RB ? (int)((J - 1) % C) : -1;
   double q_prev = 0.0, gv_prev = 0.0;
   const int64_t j0 = (int64_t)lane * C;
@@ -105,7 +105,7 @@ __device__ __forceinline__ void setup_rows(const fvm_problem& pr, int64_t p, int
     } else {
       R.slo = a.lo; sdi = a.di; R.sup = a.up;
       if (j == 0) R.bsep += beta_l;
-      if (j == J - 1) R.bsep += beta_r;
+      if (j == J - 1) R.bsep_r += beta_r;
     }
   }
   R.sblo = -cth * R.slo; R.sbdi = rth - cth * sdi; R.sbup = -cth * R.sup;
@@ -196,13 +196,26 @@ __device__ __forceinline__ double pcr_solve(double rr, const Reduced& R) {
   return rr * R.invD;
 }
 
+// What changes from step to step (nothing of this is in the reference, whose beta and k
+// are constants of a model: fvm_classes.py:221,228 only mention the case).  All pointers may be NULL.
+//  * boundary fluxes: step s uses  flux * scale_left[s*sc_ss + p*sc_ps]  (beta is linear in the flux,
+//    fvm_classes.py:244-263, so prob.left_flux / right_flux hold the UNIT or base flux);
+//  * time step: the run is cut into `n_runs` runs of steps [run_starts[r], run_starts[r+1]) that share one
+//    time step  dt_hist[run_starts[r]*dt_ss + p*dt_ps];  the kernel re-factors at the start of every run
+//    (set-up in the same launch, state parked in w_io meanwhile).
+struct FusedExtras {
+  const double* scale_left; const double* scale_right; int64_t sc_ps, sc_ss;
+  const double* dt_hist; int64_t dt_ps, dt_ss;
+  const int64_t* run_starts; int64_t n_runs;
+};
+
 // ------------------------------------------------------------------------------------------
 // Shared-memory variant.  RB: beta[J-1] is nonzero AND cell J-1 is an interior cell of its
 // lane (slow path).  QREG: q in registers (4 instead of 6 shared-memory reads per cell-update).
-template <int C, int MODE, bool RB, bool QREG>
+template <int C, int MODE, bool RB, bool QREG, bool EXT>
 __global__ void __launch_bounds__(kFusedThreads, 1)
 fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
-             int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
+             int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt, FusedExtras ex) {
   constexpr int N = C - 1;
   constexpr int NS = (N > 0 ? N : 1);
   extern __shared__ double smem[];
@@ -218,10 +231,21 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
   const int64_t J = pr.J;
   const double cth = (1.0 - theta) / theta;
 
+  const int64_t n_ck_total = (ckpt != nullptr && ckpt_every > 0) ? nsteps / ckpt_every : 0;
   for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
+   const int64_t n_runs = (EXT && ex.run_starts != nullptr) ? ex.n_runs : 1;
+   int64_t s_glob = 0;
+   for (int64_t run = 0; run < n_runs; ++run) {
+    int64_t run_len = nsteps;
+    double dt_run = dt[p];
+    if (EXT && ex.run_starts != nullptr) {
+      const int64_t s0 = ex.run_starts[run];
+      run_len = ex.run_starts[run + 1] - s0;
+      dt_run = ex.dt_hist[s0 * ex.dt_ss + p * ex.dt_ps];
+    }
     Reduced R;
     double sdi;
-    setup_rows<C, RB>(pr, p, lane, dt[p], theta, PutSmem{sp, sb}, sq, sv, R, sdi);
+    setup_rows<C, RB>(pr, p, lane, dt_run, theta, PutSmem{sp, sb}, sq, sv, R, sdi);
     double qr[NS];
     if (QREG) {
 #pragma unroll
@@ -233,8 +257,13 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
     double w[C];
     load_state<C>(w_io + p * J, J, lane, w);
 
-    int64_t until_ckpt = ckpt_every, n_ckpt = 0;
-    for (int64_t n = 0; n < nsteps; ++n) {
+    for (int64_t n = 0; n < run_len; ++n, ++s_glob) {
+      double bfirst = R.bfirst, bint = R.bint, bsep = R.bsep + R.bsep_r;
+      if (EXT) {
+        const double sc_l = ex.scale_left ? ex.scale_left[s_glob * ex.sc_ss + p * ex.sc_ps] : 1.0;
+        const double sc_r = ex.scale_right ? ex.scale_right[s_glob * ex.sc_ss + p * ex.sc_ps] : 1.0;
+        bfirst *= sc_l; bint *= sc_r; bsep = R.bsep * sc_l + R.bsep_r * sc_r;
+      }
       double wl = shfl_up(w[C - 1], 1);
       double wr = shfl_dn(w[0], 1);
       if (lane == 0) wl = 0.0;
@@ -247,19 +276,19 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
           const double pc = sp[c * 32];
           const double wc = w[c];
           double r = rhs_cell<MODE>(pc, QREG ? qr[c] : sq[c * 32], sb[c * 32], wm, wc, w[c + 1], cth);
-          if (c == 0) r += R.bfirst;
-          if (RB) { if (c == R.rb_c) r += R.bint; }
+          if (c == 0) r += bfirst;
+          if (RB) { if (c == R.rb_c) r += bint; }
           g = (c == 0) ? r : fma(-pc, g, r);
           w[c] = g;
           wm = wc;
         }
-        const double rs = fma(R.sbup, wr, fma(R.sbdi, w[C - 1], fma(R.sblo, wm, R.bsep)));
+        const double rs = fma(R.sbup, wr, fma(R.sbdi, w[C - 1], fma(R.sblo, wm, bsep)));
 #pragma unroll
         for (int c = N - 2; c >= 0; --c) w[c] = fma(-(QREG ? qr[c] : sq[c * 32]), w[c + 1], w[c]);
         const double g0n = shfl_dn(w[0], 1);
         rr = fma(-R.sup, g0n, fma(-R.slo, w[N - 1], rs));
       } else {
-        rr = fma(R.sbup, wr, fma(R.sbdi, w[0], fma(R.sblo, wl, R.bsep)));
+        rr = fma(R.sbup, wr, fma(R.sbdi, w[0], fma(R.sblo, wl, bsep)));
       }
       const double xs = pcr_solve(rr, R);
       if (N > 0) {
@@ -269,14 +298,13 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
       }
       w[C - 1] = xs;
 
-      if (ckpt != nullptr && ckpt_every > 0 && --until_ckpt == 0) {
-        until_ckpt = ckpt_every;
-        store_state<C>(ckpt + (n_ckpt * pr.P + p) * J, J, lane, w);
-        ++n_ckpt;
-      }
+      const int64_t done = s_glob + 1;
+      if (n_ck_total > 0 && done % ckpt_every == 0 && done / ckpt_every <= n_ck_total)
+        store_state<C>(ckpt + ((done / ckpt_every - 1) * pr.P + p) * J, J, lane, w);
     }
     store_state<C>(w_io + p * J, J, lane, w);
     __syncwarp();
+   }
   }
 }
 
@@ -566,10 +594,10 @@ __device__ __forceinline__ void pipe_setup(const fvm_problem& pr, int64_t p, int
   }
 }
 
-template <int MODE>
+template <int MODE, bool EXT>
 __global__ void __launch_bounds__(kFusedThreads, 1)
 fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
-                       int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
+                       int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt, FusedExtras ex) {
   constexpr int C = 32, N = kPipeN, MID = kPipeMid;
   constexpr int IT = 2;                              // slots per chunk (.x16): a slot = a left and a right cell
   constexpr int NCH = (MID + 1) / IT;                // 16 slots: 15 cell pairs and the middle cell
@@ -595,12 +623,23 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
   const uint32_t t_lk = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
   const uint32_t t_pp = t_lk + 128;                  // (P1, P2) pairs in substitution order
 
+  const int64_t n_ck_total = (ckpt != nullptr && ckpt_every > 0) ? nsteps / ckpt_every : 0;
   for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
-    // ------------------------------------------------------------------ set-up (once)
+   const int64_t n_runs = (EXT && ex.run_starts != nullptr) ? ex.n_runs : 1;
+   int64_t s_glob = 0;                               // steps done so far
+   for (int64_t run = 0; run < n_runs; ++run) {
+    int64_t run_len = nsteps;
+    double dt_run = dt[p];
+    if (EXT && ex.run_starts != nullptr) {
+      const int64_t s0 = ex.run_starts[run];
+      run_len = ex.run_starts[run + 1] - s0;
+      dt_run = ex.dt_hist[s0 * ex.dt_ss + p * ex.dt_ps];
+    }
+    // ------------------------------------------------------------------ set-up (once per run)
     double sr[N];                                    // sr[MID] is unused (the middle cell has no substitution link)
     {
       PipeConsts Kc;
-      pipe_setup(pr, p, lane, dt[p], theta, t_lk, t_pp, sS, sv, su, Kc);
+      pipe_setup(pr, p, lane, dt_run, theta, t_lk, t_pp, sS, sv, su, Kc);
 #pragma unroll
       for (int c = 0; c < N; ++c) sr[c] = sS[c * 32];
       __syncwarp();
@@ -638,7 +677,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
     // done, and the substitution applies the delayed correction link by link.  base returns the
     // part of the next reduced right-hand side that does not depend on this step's sweeps.
     auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double rr,
-                      double& xs, double& base) {
+                      double& xs, double& base, double sc_l, double sc_r) {
       constexpr bool PIPE = decltype(pipe_tag)::value;
       double hL = 0.0, hR = 0.0, zM = 0.0;
       double cgL = 0.0, cgR = 0.0;                    // MODE 0: c * g of the cell the chain is at
@@ -656,7 +695,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
         const bool lvl = PIPE && k < 5;
         if (lvl) { rm = shfl_up(rr, 1 << k); rp = shfl_dn(rr, 1 << k); fa = K(K_AL + k); fg = K(K_GA + k); }
         if (PIPE && k == 5) { xs = from_yhat(rr * K(K_INVD), xs); xsl = shfl_up(xs, 1); }
-        if (PIPE && k == 6) base = fma(xs, rth, K(K_BSEP));
+        if (PIPE && k == 6) base = fma(xs, rth, EXT ? K(K_BSEP) * sc_r : K(K_BSEP));
 #pragma unroll
         for (int ii = 0; ii < IT; ++ii) {
           const int i = k * IT + ii;
@@ -666,7 +705,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
               const double l = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1);
               const double gc = w[c], gn = w[c + 1];
               if (i == 0) {
-                hL = gc + K(K_BFIRST);
+                hL = gc + (EXT ? K(K_BFIRST) * sc_l : K(K_BFIRST));
                 if (!PIPE) hL = fma(-K(K_OML), oldL0, hL);
                 if (MODE == 0) cgL = cth * gc;
               } else {
@@ -751,11 +790,21 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       return fma(-K(K_SUP), e_first_next, fma(-K(K_SLO), ghat(w[N - 1], gl_old), base));
     };
 
-    int64_t remaining = nsteps, n_ckpt = 0;
+    // boundary-flux scales of step s (1 when there is no history); loaded one step ahead of their use
+    auto scale_of = [&](const double* hist, int64_t st) {
+      return (EXT && hist != nullptr && st < nsteps) ? hist[st * ex.sc_ss + p * ex.sc_ps] : 1.0;
+    };
+    int64_t remaining = run_len;
     TC::ld(t_lk, ra);                               // first (l, kappa) chunk
     while (remaining > 0) {
-      const bool ck = ckpt != nullptr && ckpt_every > 0 && remaining >= ckpt_every;
-      const int64_t L = ck ? ckpt_every : remaining; // steps until the true state is needed again
+      // steps until the true state is needed again: the next checkpoint or the end of the run
+      int64_t L = remaining;
+      if (n_ck_total > 0) {
+        const int64_t to_ck = ckpt_every - s_glob % ckpt_every;
+        if (s_glob / ckpt_every < n_ck_total && to_ck < L) L = to_ck;
+      }
+      double sc_l = scale_of(ex.scale_left, s_glob), sc_r = scale_of(ex.scale_right, s_glob);
+      double sc_ln = scale_of(ex.scale_left, s_glob + 1), sc_rn = scale_of(ex.scale_right, s_glob + 1);
       // -------- first step of the segment: sweeps on the true state
       double xs = w[C - 1];
       double wl = shfl_up(xs, 1);
@@ -763,13 +812,17 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       // the true state in uncorrected form: g_old = x + V xsl + U xs (only its end cells are needed)
       double g0_old = fma(su[0], xs, fma(sv[0], wl, w[0]));
       double gl_old = fma(su[(N - 1) * 32], xs, fma(sv[(N - 1) * 32], wl, w[N - 1]));
-      double base = fma(xs, rth, K(K_BSEP));
-      sweeps(std::false_type{}, wl, xs, t_lk, 0.0, xs, base);
+      double base = fma(xs, rth, EXT ? K(K_BSEP) * sc_r : K(K_BSEP));
+      sweeps(std::false_type{}, wl, xs, t_lk, 0.0, xs, base, sc_l, sc_r);
       double rr = reduced_rhs(base, g0_old, gl_old);
       // -------- pipelined steps: PCR of step n overlaps the sweeps of step n+1
       for (int64_t i = 1; i < L; ++i) {
+        if (EXT) {
+          sc_l = sc_ln; sc_r = sc_rn;
+          sc_ln = scale_of(ex.scale_left, s_glob + i + 1); sc_rn = scale_of(ex.scale_right, s_glob + i + 1);
+        }
         g0_old = w[0]; gl_old = w[N - 1];
-        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, xs, base);
+        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, xs, base, sc_l, sc_r);
         rr = reduced_rhs(base, g0_old, gl_old);
       }
       // -------- end of the segment: finish the last step and materialise the true state
@@ -787,14 +840,14 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
         w[C - 1] = xs;
       }
       remaining -= L;
-      if (ck) {
-        store_state<C>(ckpt + (n_ckpt * pr.P + p) * J, J, lane, w);
-        ++n_ckpt;
-      }
+      s_glob += L;
+      if (n_ck_total > 0 && s_glob % ckpt_every == 0 && s_glob / ckpt_every <= n_ck_total)
+        store_state<C>(ckpt + ((s_glob / ckpt_every - 1) * pr.P + p) * J, J, lane, w);
     }
     TC::wait(ra);                                   // drain the prefetch of the step that never comes
     store_state<C>(w_io + p * J, J, lane, w);
     __syncwarp();
+   }
   }
 
   tmem_fence_before_sync();
@@ -812,9 +865,9 @@ static int device_limits(int& sms, int& max_smem) {
   return 0;
 }
 
-template <int C, int MODE, bool RB, bool QREG>
+template <int C, int MODE, bool RB, bool QREG, bool EXT>
 static int launch_fused(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
-                        int64_t ckpt_every, double* w, double* ckpt, cudaStream_t stream) {
+                        int64_t ckpt_every, double* w, double* ckpt, const FusedExtras& ex, cudaStream_t stream) {
   constexpr int NS = (C > 1 ? C - 1 : 1);
   constexpr size_t per_warp = (size_t)(QREG ? 4 : 5) * NS * 32 * sizeof(double);
   int sms = 0, max_smem = 0;
@@ -825,7 +878,7 @@ static int launch_fused(const fvm_problem& pr, const double* dt, double theta, i
   if (warps < 1) return FVM_ERR_UNSUPPORTED;
   if ((int64_t)warps > pr.P) warps = (int)pr.P;
   const size_t smem = per_warp * warps;
-  auto kern = fused_kernel<C, MODE, RB, QREG>;
+  auto kern = fused_kernel<C, MODE, RB, QREG, EXT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   int per_sm = 1;
@@ -835,13 +888,13 @@ static int launch_fused(const fvm_problem& pr, const double* dt, double theta, i
   int64_t blocks = (pr.P + warps - 1) / warps;
   const int64_t resident = (int64_t)sms * per_sm;
   if (blocks > resident) blocks = resident;      // persistent: each warp strides over problems
-  kern<<<(unsigned)blocks, warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
+  kern<<<(unsigned)blocks, warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex);
   return (int)cudaGetLastError();
 }
 
-template <int MODE>
+template <int MODE, bool EXT>
 static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
-                             int64_t ckpt_every, double* w, double* ckpt, cudaStream_t stream) {
+                             int64_t ckpt_every, double* w, double* ckpt, const FusedExtras& ex, cudaStream_t stream) {
   constexpr int warps = kFusedThreads / 32;
   constexpr size_t smem = (size_t)warps * 3 * 31 * 32 * sizeof(double);
   int sms = 0, max_smem = 0;
@@ -849,28 +902,40 @@ static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double the
   if (st) return st;
   int64_t blocks = (pr.P + warps - 1) / warps;
   if (blocks > sms) blocks = sms;                // one CTA per SM: it holds the SM's whole TMEM
-  auto kern = fused_tmem_pipe_kernel<MODE>;
+  auto kern = fused_tmem_pipe_kernel<MODE, EXT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  kern<<<(unsigned)blocks, warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt);
+  kern<<<(unsigned)blocks, warps * 32, smem, stream>>>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex);
   return (int)cudaGetLastError();
 }
 
-template <int C>
+template <int C, bool EXT>
 static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
-                         int64_t ckpt_every, double* w, double* ckpt, cudaStream_t stream) {
+                         int64_t ckpt_every, double* w, double* ckpt, const FusedExtras& ex, cudaStream_t stream) {
   const bool rb = pr.right_kind == FVM_BC_ROBIN && pr.right_flux != nullptr &&
                   ((pr.J - 1) % C) != C - 1;
   constexpr bool Q = true;
-  if (rb) return launch_fused<C, 0, true, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  if (rb) return launch_fused<C, 0, true, Q, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
   if (C == 32) {
-    if (theta == 0.5) return launch_fused_tmem<1>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    if (theta == 1.0) return launch_fused_tmem<2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-    return launch_fused_tmem<0>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    if (theta == 0.5) return launch_fused_tmem<1, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+    if (theta == 1.0) return launch_fused_tmem<2, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+    return launch_fused_tmem<0, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
   }
-  if (theta == 0.5) return launch_fused<C, 1, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-  if (theta == 1.0) return launch_fused<C, 2, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-  return launch_fused<C, 0, false, Q>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  if (theta == 0.5) return launch_fused<C, 1, false, Q, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+  if (theta == 1.0) return launch_fused<C, 2, false, Q, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+  return launch_fused<C, 0, false, Q, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+}
+
+template <bool EXT>
+static int dispatch_cells(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
+                          int64_t ckpt_every, double* w, double* ckpt, const FusedExtras& ex, cudaStream_t s) {
+  const int64_t J = pr.J;
+  if (J <= 32) return dispatch_mode<1, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, s);
+  if (J <= 64) return dispatch_mode<2, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, s);
+  if (J <= 128) return dispatch_mode<4, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, s);
+  if (J <= 256) return dispatch_mode<8, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, s);
+  if (J <= 512) return dispatch_mode<16, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, s);
+  return dispatch_mode<32, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, s);
 }
 
 // fused_cta.cu
@@ -881,25 +946,47 @@ int run_fused_cta(const fvm_problem& pr, const double* dt, double theta, int64_t
 
 extern "C" int64_t fvm_fused_max_cells(void) { return 8192; }
 
-extern "C" int fvm_theta_run_fused(const fvm_problem* prob, const double* dt, double theta,
-                                   int64_t nsteps, int64_t checkpoint_every, double* w,
-                                   double* ckpt, void* stream) {
+static int check_fused_args(const fvm_problem* prob, const double* dt, double theta, int64_t nsteps,
+                            int64_t checkpoint_every, const double* w) {
   if (!prob || !prob->faces || !prob->a || !prob->d || !dt || !w) return FVM_ERR_INVALID_ARG;
   if (prob->J < 3 || prob->P < 1 || nsteps < 0 || checkpoint_every < 0) return FVM_ERR_INVALID_ARG;
   if (!(theta > 0.0 && theta <= 1.0)) return FVM_ERR_INVALID_ARG;
   if (prob->scheme < FVM_CENTRAL || prob->scheme > FVM_EXPONENTIAL) return FVM_ERR_INVALID_ARG;
   if ((prob->left_kind | prob->right_kind | prob->alpha_left | prob->alpha_right) & ~1)
     return FVM_ERR_INVALID_ARG;
+  return FVM_OK;
+}
+
+extern "C" int fvm_theta_run_fused(const fvm_problem* prob, const double* dt, double theta,
+                                   int64_t nsteps, int64_t checkpoint_every, double* w,
+                                   double* ckpt, void* stream) {
+  int st = check_fused_args(prob, dt, theta, nsteps, checkpoint_every, w);
+  if (st) return st;
   if (prob->J > fvm_fused_max_cells()) return FVM_ERR_UNSUPPORTED;
   if (nsteps == 0) return FVM_OK;
   cudaStream_t s = (cudaStream_t)stream;
-  const int64_t J = prob->J;
   using namespace fvm;
-  if (J <= 32) return dispatch_mode<1>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
-  if (J <= 64) return dispatch_mode<2>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
-  if (J <= 128) return dispatch_mode<4>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
-  if (J <= 256) return dispatch_mode<8>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
-  if (J <= 512) return dispatch_mode<16>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
-  if (J <= 32 * kFusedMaxC) return dispatch_mode<32>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
+  const FusedExtras none = {nullptr, nullptr, 0, 0, nullptr, 0, 0, nullptr, 0};
+  if (prob->J <= 32 * kFusedMaxC) return dispatch_cells<false>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, none, s);
   return run_fused_cta(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, s);
+}
+
+extern "C" int64_t fvm_fused_ex_max_cells(void) { return 32 * fvm::kFusedMaxC; }
+
+extern "C" int fvm_theta_run_fused_ex(const fvm_problem* prob, const double* dt, double theta, int64_t nsteps,
+                                      int64_t checkpoint_every, double* w, double* ckpt,
+                                      const double* scale_left, const double* scale_right, int64_t scale_ps,
+                                      int64_t scale_ss, const double* dt_hist, int64_t dt_ps, int64_t dt_ss,
+                                      const int64_t* run_starts, int64_t n_runs, void* stream) {
+  int st = check_fused_args(prob, dt, theta, nsteps, checkpoint_every, w);
+  if (st) return st;
+  if ((dt_hist != nullptr) != (run_starts != nullptr)) return FVM_ERR_INVALID_ARG;
+  if (run_starts != nullptr && n_runs < 1) return FVM_ERR_INVALID_ARG;
+  if (scale_left && !(prob->left_kind == FVM_BC_ROBIN && prob->left_flux)) return FVM_ERR_INVALID_ARG;
+  if (scale_right && !(prob->right_kind == FVM_BC_ROBIN && prob->right_flux)) return FVM_ERR_INVALID_ARG;
+  if (prob->J > fvm_fused_ex_max_cells()) return FVM_ERR_UNSUPPORTED;
+  if (nsteps == 0) return FVM_OK;
+  using namespace fvm;
+  const FusedExtras ex = {scale_left, scale_right, scale_ps, scale_ss, dt_hist, dt_ps, dt_ss, run_starts, n_runs};
+  return dispatch_cells<true>(*prob, dt, theta, nsteps, checkpoint_every, w, ckpt, ex, (cudaStream_t)stream);
 }

@@ -176,6 +176,27 @@ int64_t fvm_fused_max_cells(void);
 int fvm_theta_run_fused(const fvm_problem* prob, const double* dt, double theta, int64_t nsteps,
                         int64_t checkpoint_every, double* w, double* ckpt, void* stream);
 
+/* Variant 2 with what changes from step to step.  NO COUNTERPART IN THE REFERENCE,
+ * whose beta and k are constants of a model; fvm_classes.py:221,228 ("unless BCs are time varying")
+ * only hint at it.  Same on-chip kernels and arguments as fvm_theta_run_fused, for J <=
+ * fvm_fused_ex_max_cells() (1024: the warp-per-system kernels), plus:
+ *  - scale_left / scale_right (may be NULL): step s (0-based) uses the boundary flux
+ *    prob->left_flux[p] * scale_left[s*scale_ss + p*scale_ps]  (likewise on the right).  beta is
+ *    linear in the flux [fvm_classes.py:244-263], so with a unit flux in prob the scales ARE the
+ *    flux history; scale_ps = 0 shares one history between all problems.  A scaled end must be a
+ *    Robin end with a non-NULL flux array in prob.
+ *  - dt_hist, run_starts, n_runs (all NULL/0, or all given): the nsteps steps are cut into n_runs
+ *    runs [run_starts[r], run_starts[r+1]) (run_starts: DEVICE array of n_runs+1 int64, first 0, last
+ *    nsteps); all steps of run r use the time step dt_hist[run_starts[r]*dt_ss + p*dt_ps] and the
+ *    kernel re-factors the operators at the start of every run, inside the launch (`dt` is then
+ *    unused but must be valid).  Checkpoints count steps over the whole launch. */
+int64_t fvm_fused_ex_max_cells(void);
+int fvm_theta_run_fused_ex(const fvm_problem* prob, const double* dt, double theta, int64_t nsteps,
+                           int64_t checkpoint_every, double* w, double* ckpt,
+                           const double* scale_left, const double* scale_right, int64_t scale_ps,
+                           int64_t scale_ss, const double* dt_hist, int64_t dt_ps, int64_t dt_ss,
+                           const int64_t* run_starts, int64_t n_runs, void* stream);
+
 /* ---- Variant 3: partitioned SPIKE/Thomas for LONG systems (one huge mesh, or a batch of long
  * ones), optionally with the cells split in contiguous slabs over several GPUs.  Replaces the
  * same loop (fvm_classes.py:373-377,408-411) where J is far beyond what fits on chip; the
