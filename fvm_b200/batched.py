@@ -339,12 +339,34 @@ class BatchedAdvectionDiffusionModel(object):
         return m.get_state()
 
     # ------------------------------------------------------------------ time-varying boundary data
-    def run_time_varying(self, w, theta, left_flux_t=None, right_flux_t=None, checkpoint_every=0):
+    def _fused_ex(self, pr, k, w, theta, nsteps, ce, ckpt, sl=None, sr=None, sc_ps=0, sc_ss=0,
+                  dt_hist=None, dt_ps=0, dt_ss=0, run_starts=None):
+        """fvm_theta_run_fused_ex on a problem-major state w (P, J), in place."""
+        torch = _lib.require_cuda()
+        n_runs = int(run_starts.numel()) - 1 if run_starts is not None else 0
+        with torch.cuda.device(self.device):
+            st = _lib.lib().fvm_theta_run_fused_ex(
+                ctypes.byref(pr), _lib.ptr(k), float(theta), int(nsteps), int(ce), _lib.ptr(w), _lib.ptr(ckpt),
+                _lib.ptr(sl), _lib.ptr(sr), int(sc_ps), int(sc_ss), _lib.ptr(dt_hist), int(dt_ps), int(dt_ss),
+                ctypes.c_void_p(run_starts.data_ptr()) if run_starts is not None else None, n_runs,
+                _lib.stream_ptr())
+        _lib.check(st, "fvm_theta_run_fused_ex")
+        return w
+
+    def _ex_variant(self, variant):
+        if variant == "auto":
+            return "fused" if self.J <= int(_lib.lib().fvm_fused_ex_max_cells()) else "thomas"
+        if variant not in ("fused", "thomas"):
+            raise ValueError("variant must be 'auto', 'fused' or 'thomas'")
+        return variant
+
+    def run_time_varying(self, w, theta, left_flux_t=None, right_flux_t=None, checkpoint_every=0, variant="auto"):
         """Theta steps with boundary fluxes that change from step to step: step n uses
         ``left_flux_t[n]`` / ``right_flux_t[n]`` (shape (nsteps,) or (nsteps, P)) in beta; an end
         without a history keeps the flux of set_boundary_conditions.  NOT in the reference
-        (constant beta; fvm_classes.py:221,228 only mention the case) -- SURVEY.md 8(f)2.  Runs on
-        variant 1 (fvm_theta_step_thomas_tv).  Returns (w_final, checkpoints or None)."""
+        (constant beta; fvm_classes.py:221,228 only mention the case) -- SURVEY.md 8(f)2.  Runs on the
+        on-chip kernels (fvm_theta_run_fused_ex: the whole history in ONE launch) for J <= 1024, else on
+        variant 1 (fvm_theta_step_thomas_tv); ``variant`` forces one.  Returns (w_final, checkpoints or None)."""
         torch = _lib.require_cuda()
         if not hasattr(self, "left_flux"):
             raise AttributeError("boundary conditions are not set: call set_boundary_conditions first")
@@ -356,6 +378,8 @@ class BatchedAdvectionDiffusionModel(object):
         if (left_flux_t is not None and lk != _lib.BC_ROBIN) or (right_flux_t is not None and rk != _lib.BC_ROBIN):
             raise ValueError("a flux history needs a flux (Robin) boundary at that end")
 
+        variant = self._ex_variant(variant)
+
         def hist(x):
             if x is None:
                 return None
@@ -365,7 +389,12 @@ class BatchedAdvectionDiffusionModel(object):
             if t.ndim != 2 or t.shape[1] != self.P:
                 raise ValueError("a flux history must have shape (nsteps,) or (nsteps, P)")
             return t.contiguous()
-        sl, sr = hist(left_flux_t), hist(right_flux_t)
+        shared = variant == "fused" and all(x is None or np.ndim(x) == 1 for x in (left_flux_t, right_flux_t))
+        if shared:          # one history for every problem: problem stride 0, nothing is expanded
+            one = lambda x: None if x is None else self._dev(x).contiguous()
+            sl, sr = one(left_flux_t), one(right_flux_t)
+        else:
+            sl, sr = hist(left_flux_t), hist(right_flux_t)
         nsteps = int((sl if sl is not None else sr).shape[0])
         if sl is not None and sr is not None and sl.shape[0] != sr.shape[0]:
             raise ValueError("the two flux histories must have the same number of steps")
@@ -378,11 +407,19 @@ class BatchedAdvectionDiffusionModel(object):
                                          right_flux=1.0 if sr is not None else self.right_flux,
                                          left_value=self.left_value, right_value=self.right_value)
             self._unit = (key, twin)
-        f = self._unit[1].factor(theta)
-        w_t = self._dev(w).reshape(self.P, self.J).t().contiguous()
         ce = int(checkpoint_every or 0)
         n_ck = nsteps // ce if ce > 0 else 0
         ckpt = torch.empty((n_ck, self.P, self.J), dtype=torch.float64, device=self.device) if n_ck else None
+        if variant == "fused":
+            twin = self._unit[1]
+            wd = self._dev(w).reshape(self.P, self.J).clone()
+            if shared:
+                self._fused_ex(twin._problem(), self.k, wd, theta, nsteps, ce, ckpt, sl, sr, 0, 1)
+            else:
+                self._fused_ex(twin._problem(), self.k, wd, theta, nsteps, ce, ckpt, sl, sr, 1, self.P)
+            return wd, ckpt
+        f = self._unit[1].factor(theta)
+        w_t = self._dev(w).reshape(self.P, self.J).t().contiguous()
         segments = [ce] * n_ck + ([nsteps - n_ck * ce] if nsteps - n_ck * ce else [])
         done = 0
         with torch.cuda.device(self.device):
@@ -400,12 +437,13 @@ class BatchedAdvectionDiffusionModel(object):
                     ckpt[i].copy_(w_t.t())
         return w_t.t().contiguous(), ckpt
 
-    def run_variable_dt(self, w, theta, dt_t, checkpoint_every=0):
+    def run_variable_dt(self, w, theta, dt_t, checkpoint_every=0, variant="auto"):
         """Theta steps whose time step changes: step n uses ``dt_t[n]`` (shape (nsteps,) or
         (nsteps, P)) in place of the constructor's k.  NOT in the reference (one k per model,
-        fvm_classes.py:92,351) -- SURVEY.md 8(f)2.  Variant 1: the operators are re-factored
-        (fvm_theta_factor, one pass over the assembled diagonals) whenever the time step differs
-        from the previous step's; runs of equal steps share a factorisation and a launch."""
+        fvm_classes.py:92,351) -- SURVEY.md 8(f)2.  The operators are re-factored whenever the time
+        step differs from the previous step's; runs of equal steps share a factorisation.  J <= 1024:
+        ONE launch of the on-chip kernels, which re-factor inside the kernel at the start of every run
+        (fvm_theta_run_fused_ex).  Longer systems: variant 1, one fvm_theta_factor and one launch per run."""
         torch = _lib.require_cuda()
         if not (0.0 < float(theta) <= 1.0):
             raise ValueError("theta must be in (0, 1] for the variable-step run")
@@ -420,11 +458,19 @@ class BatchedAdvectionDiffusionModel(object):
         change = torch.ones(nsteps, dtype=torch.bool, device=self.device)
         if nsteps > 1:
             change[1:] = (dt[1:] != dt[:-1]).any(dim=1)
-        starts = [int(i) for i in torch.nonzero(change).flatten().cpu()] + [nsteps]
-        w_t = self._dev(w).reshape(self.P, self.J).t().contiguous()
         ce = int(checkpoint_every or 0)
         n_ck = nsteps // ce if ce > 0 else 0
         ckpt = torch.empty((n_ck, self.P, self.J), dtype=torch.float64, device=self.device) if n_ck else None
+        if self._ex_variant(variant) == "fused":
+            # the run boundaries never leave the device: the kernel reads them
+            run_starts = torch.cat([torch.nonzero(change).flatten(),
+                                    torch.tensor([nsteps], dtype=torch.int64, device=self.device)]).contiguous()
+            wd = self._dev(w).reshape(self.P, self.J).clone()
+            self._fused_ex(self._problem(), self.k, wd, theta, nsteps, ce, ckpt, dt_hist=dt, dt_ps=1, dt_ss=self.P,
+                           run_starts=run_starts)
+            return wd, ckpt
+        starts = [int(i) for i in torch.nonzero(change).flatten().cpu()] + [nsteps]
+        w_t = self._dev(w).reshape(self.P, self.J).t().contiguous()
         k_saved, f_saved = self.k, self._factors
         try:
             for s0, s1 in zip(starts[:-1], starts[1:]):

@@ -203,6 +203,8 @@ __device__ __forceinline__ double pcr_solve(double rr, const Reduced& R) {
 //  * time step: the run is cut into `n_runs` runs of steps [run_starts[r], run_starts[r+1]) that share one
 //    time step  dt_hist[run_starts[r]*dt_ss + p*dt_ps];  the kernel re-factors at the start of every run
 //    (set-up in the same launch, state parked in w_io meanwhile).
+__device__ const double kUnitScale = 1.0;
+
 struct FusedExtras {
   const double* scale_left; const double* scale_right; int64_t sc_ps, sc_ss;
   const double* dt_hist; int64_t dt_ps, dt_ss;
@@ -594,11 +596,14 @@ __device__ __forceinline__ void pipe_setup(const fvm_problem& pr, int64_t p, int
   }
 }
 
-template <int MODE, bool EXT>
+// EXT: 0 = constant coefficients; 1 = per-step boundary-flux scales; 2 = scales and runs of different time
+// steps (the run loop costs the steady-state loop its uniform registers, ~8 %, so it has its own instance).
+template <int MODE, int EXT_>
 __global__ void __launch_bounds__(kFusedThreads, 1)
 fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
                        int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt, FusedExtras ex) {
   constexpr int C = 32, N = kPipeN, MID = kPipeMid;
+  constexpr bool EXT = EXT_ >= 1, RUNS = EXT_ == 2;
   constexpr int IT = 2;                              // slots per chunk (.x16): a slot = a left and a right cell
   constexpr int NCH = (MID + 1) / IT;                // 16 slots: 15 cell pairs and the middle cell
   using TC = TmemChunk;
@@ -625,12 +630,12 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
 
   const int64_t n_ck_total = (ckpt != nullptr && ckpt_every > 0) ? nsteps / ckpt_every : 0;
   for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
-   const int64_t n_runs = (EXT && ex.run_starts != nullptr) ? ex.n_runs : 1;
+   const int64_t n_runs = (RUNS && ex.run_starts != nullptr) ? ex.n_runs : 1;
    int64_t s_glob = 0;                               // steps done so far
    for (int64_t run = 0; run < n_runs; ++run) {
     int64_t run_len = nsteps;
     double dt_run = dt[p];
-    if (EXT && ex.run_starts != nullptr) {
+    if (RUNS && ex.run_starts != nullptr) {
       const int64_t s0 = ex.run_starts[run];
       run_len = ex.run_starts[run + 1] - s0;
       dt_run = ex.dt_hist[s0 * ex.dt_ss + p * ex.dt_ps];
@@ -677,7 +682,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
     // done, and the substitution applies the delayed correction link by link.  base returns the
     // part of the next reduced right-hand side that does not depend on this step's sweeps.
     auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double rr,
-                      double& xs, double& base, double sc_l, double sc_r) {
+                      double& xs, double& base, double sc) {
       constexpr bool PIPE = decltype(pipe_tag)::value;
       double hL = 0.0, hR = 0.0, zM = 0.0;
       double cgL = 0.0, cgR = 0.0;                    // MODE 0: c * g of the cell the chain is at
@@ -695,7 +700,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
         const bool lvl = PIPE && k < 5;
         if (lvl) { rm = shfl_up(rr, 1 << k); rp = shfl_dn(rr, 1 << k); fa = K(K_AL + k); fg = K(K_GA + k); }
         if (PIPE && k == 5) { xs = from_yhat(rr * K(K_INVD), xs); xsl = shfl_up(xs, 1); }
-        if (PIPE && k == 6) base = fma(xs, rth, EXT ? K(K_BSEP) * sc_r : K(K_BSEP));
+        if (PIPE && k == 6) base = fma(xs, rth, EXT ? K(K_BSEP) * sc : K(K_BSEP));
 #pragma unroll
         for (int ii = 0; ii < IT; ++ii) {
           const int i = k * IT + ii;
@@ -705,7 +710,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
               const double l = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1);
               const double gc = w[c], gn = w[c + 1];
               if (i == 0) {
-                hL = gc + (EXT ? K(K_BFIRST) * sc_l : K(K_BFIRST));
+                hL = EXT ? fma(K(K_BFIRST), sc, gc) : gc + K(K_BFIRST);
                 if (!PIPE) hL = fma(-K(K_OML), oldL0, hL);
                 if (MODE == 0) cgL = cth * gc;
               } else {
@@ -790,10 +795,19 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       return fma(-K(K_SUP), e_first_next, fma(-K(K_SLO), ghat(w[N - 1], gl_old), base));
     };
 
-    // boundary-flux scales of step s (1 when there is no history); loaded one step ahead of their use
-    auto scale_of = [&](const double* hist, int64_t st) {
-      return (EXT && hist != nullptr && st < nsteps) ? hist[st * ex.sc_ss + p * ex.sc_ps] : 1.0;
-    };
+    // Boundary-flux scale of step s, loaded one step ahead of its use.  A lane needs at most one of
+    // the two histories: beta[0] enters at lane 0 only (K_BFIRST is 0 elsewhere), beta[J-1] at the
+    // lane whose separator is cell J-1 (K_BSEP is 0 elsewhere, and that lane is not lane 0: J > 512).
+    const double* hist = nullptr;
+    if (EXT) {
+      hist = (lane == 0) ? ex.scale_left : ex.scale_right;
+      if (hist != nullptr) hist += p * ex.sc_ps;
+    }
+    const int64_t hist_step = (EXT && hist != nullptr) ? ex.sc_ss : 0;
+    if (EXT && hist == nullptr) hist = &kUnitScale;  // no history at this end: the scale stays 1
+    if (EXT) hist += s_glob * hist_step;              // -> the scale of the next step to be taken
+    const double* const hist_last = EXT ? hist + (nsteps - 1 - s_glob) * hist_step : nullptr;
+    auto advance = [&]() { if (hist != hist_last) hist += hist_step; };
     int64_t remaining = run_len;
     TC::ld(t_lk, ra);                               // first (l, kappa) chunk
     while (remaining > 0) {
@@ -803,8 +817,8 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
         const int64_t to_ck = ckpt_every - s_glob % ckpt_every;
         if (s_glob / ckpt_every < n_ck_total && to_ck < L) L = to_ck;
       }
-      double sc_l = scale_of(ex.scale_left, s_glob), sc_r = scale_of(ex.scale_right, s_glob);
-      double sc_ln = scale_of(ex.scale_left, s_glob + 1), sc_rn = scale_of(ex.scale_right, s_glob + 1);
+      double sc = 1.0, sc_n = 1.0;
+      if (EXT) { sc = *hist; advance(); sc_n = *hist; }
       // -------- first step of the segment: sweeps on the true state
       double xs = w[C - 1];
       double wl = shfl_up(xs, 1);
@@ -812,17 +826,14 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       // the true state in uncorrected form: g_old = x + V xsl + U xs (only its end cells are needed)
       double g0_old = fma(su[0], xs, fma(sv[0], wl, w[0]));
       double gl_old = fma(su[(N - 1) * 32], xs, fma(sv[(N - 1) * 32], wl, w[N - 1]));
-      double base = fma(xs, rth, EXT ? K(K_BSEP) * sc_r : K(K_BSEP));
-      sweeps(std::false_type{}, wl, xs, t_lk, 0.0, xs, base, sc_l, sc_r);
+      double base = fma(xs, rth, EXT ? K(K_BSEP) * sc : K(K_BSEP));
+      sweeps(std::false_type{}, wl, xs, t_lk, 0.0, xs, base, sc);
       double rr = reduced_rhs(base, g0_old, gl_old);
       // -------- pipelined steps: PCR of step n overlaps the sweeps of step n+1
       for (int64_t i = 1; i < L; ++i) {
-        if (EXT) {
-          sc_l = sc_ln; sc_r = sc_rn;
-          sc_ln = scale_of(ex.scale_left, s_glob + i + 1); sc_rn = scale_of(ex.scale_right, s_glob + i + 1);
-        }
+        if (EXT) { sc = sc_n; advance(); sc_n = *hist; }
         g0_old = w[0]; gl_old = w[N - 1];
-        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, xs, base, sc_l, sc_r);
+        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, xs, base, sc);
         rr = reduced_rhs(base, g0_old, gl_old);
       }
       // -------- end of the segment: finish the last step and materialise the true state
@@ -892,7 +903,7 @@ static int launch_fused(const fvm_problem& pr, const double* dt, double theta, i
   return (int)cudaGetLastError();
 }
 
-template <int MODE, bool EXT>
+template <int MODE, int EXT>
 static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
                              int64_t ckpt_every, double* w, double* ckpt, const FusedExtras& ex, cudaStream_t stream) {
   constexpr int warps = kFusedThreads / 32;
@@ -917,9 +928,15 @@ static int dispatch_mode(const fvm_problem& pr, const double* dt, double theta, 
   constexpr bool Q = true;
   if (rb) return launch_fused<C, 0, true, Q, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
   if (C == 32) {
-    if (theta == 0.5) return launch_fused_tmem<1, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
-    if (theta == 1.0) return launch_fused_tmem<2, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
-    return launch_fused_tmem<0, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+    if (EXT && ex.run_starts != nullptr) {
+      if (theta == 0.5) return launch_fused_tmem<1, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+      if (theta == 1.0) return launch_fused_tmem<2, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+      return launch_fused_tmem<0, 2>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+    }
+    constexpr int E = EXT ? 1 : 0;
+    if (theta == 0.5) return launch_fused_tmem<1, E>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+    if (theta == 1.0) return launch_fused_tmem<2, E>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
+    return launch_fused_tmem<0, E>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
   }
   if (theta == 0.5) return launch_fused<C, 1, false, Q, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);
   if (theta == 1.0) return launch_fused<C, 2, false, Q, EXT>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, ex, stream);

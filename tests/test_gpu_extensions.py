@@ -29,9 +29,10 @@ def oracle_time_varying(faces, a, d, k, scheme, bc_of_step, theta, w0, nsteps):
     return np.array(out)
 
 
-@pytest.mark.parametrize("theta", [0.5, 1.0])
-def test_time_varying_fluxes_match_per_step_oracle(theta):
-    J, P, n = 300, 3, 24
+@pytest.mark.parametrize("variant,J", [("fused", 300), ("fused", 1000), ("fused", 61), ("thomas", 300)])
+@pytest.mark.parametrize("theta", [0.5, 1.0, 0.7])
+def test_time_varying_fluxes_match_per_step_oracle(theta, variant, J):
+    P, n = 3, 24
     f = W.graded_faces(J)
     rng = np.random.default_rng(11)
     a, d, k = rng.uniform(0.5, 1.5, P), rng.uniform(0.01, 0.05, P), rng.uniform(1e-3, 4e-3, P)
@@ -42,7 +43,7 @@ def test_time_varying_fluxes_match_per_step_oracle(theta):
     m = BatchedAdvectionDiffusionModel(f, a, d, k, "upwind")
     m.set_boundary_conditions(left_flux=0.7, right_flux=-0.1)
     # both ends vary
-    w, ck = m.run_time_varying(w0, theta, left_flux_t=lf, right_flux_t=rf, checkpoint_every=1)
+    w, ck = m.run_time_varying(w0, theta, left_flux_t=lf, right_flux_t=rf, checkpoint_every=1, variant=variant)
     assert ck.shape == (n, P, J)
     for p in range(P):
         want = oracle_time_varying(f, a[p], d[p], k[p], "upwind",
@@ -50,14 +51,14 @@ def test_time_varying_fluxes_match_per_step_oracle(theta):
         assert step_error(ck[:, p].cpu().numpy(), want, 1.0) < TOL, p
     assert np.array_equal(w.cpu().numpy(), ck[-1].cpu().numpy())
     # only the right end varies: the left keeps the flux of set_boundary_conditions
-    w2, _ = m.run_time_varying(w0, theta, right_flux_t=rf)
+    w2, _ = m.run_time_varying(w0, theta, right_flux_t=rf, variant=variant)
     want = oracle_time_varying(f, a[0], d[0], k[0], "upwind",
                                lambda s: dict(left_flux=0.7, right_flux=rf[s]), theta, w0[0], n)
     assert step_error(w2[0].cpu().numpy()[None], want[-1][None], 1.0) < TOL
     # a constant history reproduces run()
-    w3, _ = m.run_time_varying(w0, theta, left_flux_t=np.full(n, 0.7), right_flux_t=np.full(n, -0.1))
-    w4, _ = m.run(w0, theta, n, variant="thomas")
-    assert step_error(w3.cpu().numpy(), w4.cpu().numpy(), 1.0) < 1e-13
+    w3, _ = m.run_time_varying(w0, theta, left_flux_t=np.full(n, 0.7), right_flux_t=np.full(n, -0.1), variant=variant)
+    w4, _ = m.run(w0, theta, n, variant=variant)
+    assert step_error(w3.cpu().numpy(), w4.cpu().numpy(), 1.0) < 1e-12      # unit flux x 0.7 against flux 0.7: a rounding apart
 
 
 def test_time_varying_with_a_dirichlet_end_and_bad_arguments():
@@ -124,9 +125,11 @@ def test_run_until_steady_reaches_the_analytic_steady_state(tmp_path):
     assert np.array_equal(np.load(path), ck) and ck.shape == (4, J)
 
 
-def test_variable_time_step_matches_per_step_oracle():
-    """A time step that changes during the run (per problem, too): re-factored where it changes."""
-    J, P, n = 200, 2, 18
+@pytest.mark.parametrize("variant,J", [("fused", 200), ("fused", 1024), ("thomas", 200)])
+def test_variable_time_step_matches_per_step_oracle(variant, J):
+    """A time step that changes during the run (per problem, too): re-factored where it changes --
+    inside the kernel for the on-chip variant."""
+    P, n = 2, 18
     f = W.graded_faces(J)
     a, d = np.array([1.0, 0.6]), np.array([0.02, 0.05])
     cells = 0.5 * (f[1:] + f[:-1])
@@ -136,7 +139,7 @@ def test_variable_time_step_matches_per_step_oracle():
     bc = dict(left_flux=0.2, right_flux=0.0)
     m = BatchedAdvectionDiffusionModel(f, a, d, 1.0, "exponential", P=P)      # the constructor's k is not used
     m.set_boundary_conditions(**bc)
-    w, ck = m.run_variable_dt(w0, 0.5, dt, checkpoint_every=4)
+    w, ck = m.run_variable_dt(w0, 0.5, dt, checkpoint_every=4, variant=variant)
     assert ck.shape == (4, P, J)
     for p in range(P):
         asm = O.assemble(f, a[p], d[p], "exponential", **bc)
@@ -150,6 +153,6 @@ def test_variable_time_step_matches_per_step_oracle():
     # the model's own time step and factors are untouched afterwards
     assert float(m.k[0]) == 1.0
     # a constant history is run()
-    w1, _ = m.run_variable_dt(w0, 1.0, np.full(n, 1.0))
-    w2, _ = m.run(w0, 1.0, n, variant="thomas")
+    w1, _ = m.run_variable_dt(w0, 1.0, np.full(n, 1.0), variant=variant)
+    w2, _ = m.run(w0, 1.0, n, variant=variant)
     assert np.array_equal(w1.cpu().numpy(), w2.cpu().numpy())
