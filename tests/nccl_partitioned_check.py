@@ -1,8 +1,8 @@
-"""Multi-GPU correctness check of the partitioned solver over NCCL (not collected by pytest: it
-needs one GPU per rank).  Run under torchrun, e.g.
+"""Multi-GPU correctness check of the partitioned solver over NCCL, one GPU per rank.  Launched by
+tests/test_gpu_multi_nccl.py (pytest, skipped on a single-GPU box) or by hand under torchrun:
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
-        --master-port 29544 tests/multi_gpu_check.py
+        --master-port 29544 tests/nccl_partitioned_check.py
 
 Every rank holds a slab of one 200,000-cell graded mesh (production tiles, 8192 cells); the
 slabs' results are gathered and compared with (i) the same solver on a single rank and (ii) the
