@@ -529,6 +529,8 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from fvm_b200 import _lib
+    numa_node = _lib.bind_to_gpu_numa_node(local)      # host buffers next to this rank's GPU
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -601,7 +603,7 @@ def run_b200(args):
         e2e = {"value": world * cu_per_step_rank * K / (float(te.item()) * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": P * J * 8, "d2h_bytes_per_step": (1 + n_ck) * P * J * 8,
                "api": "BatchedAdvectionDiffusionModel.run_host (pinned host state in, final state and every "
-                      "checkpoint out to pinned host memory, every step)"}
+                      "checkpoint out to pinned host memory, every step)", "host_numa_node": numa_node}
         del h_ck
 
     # ---- streaming variant (HBM roofline evidence), rank 0 only, small step count

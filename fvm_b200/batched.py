@@ -534,7 +534,7 @@ class BatchedAdvectionDiffusionModel(object):
                     ckpt[(n + 1) // ce - 1].copy_(dst)
         return bufs[nsteps & 1]
 
-    def run_host(self, w_host, theta, nsteps, out=None, variant="auto", chunks=8, checkpoint_every=0,
+    def run_host(self, w_host, theta, nsteps, out=None, variant="auto", chunks=16, checkpoint_every=0,
                  ckpt_out=None):
         """Host-buffer form of :meth:`run`: ``w_host`` (P, J) lives in host memory (numpy array
         or CPU tensor; pinned memory makes the copies asynchronous and fast).  Copies it to the
@@ -587,8 +587,13 @@ class BatchedAdvectionDiffusionModel(object):
                 torch.cuda.current_stream().synchronize()
                 return out
             pr = self._problem()
-            n_chunks = max(1, min(int(chunks), self.P // 2048 if self.P >= 4096 else 1))
-            bounds = [self.P * i // n_chunks for i in range(n_chunks + 1)]
+            # groups of whole "waves": the on-chip kernels run 8 problems per SM at a time, so a group
+            # that is a multiple of 8 x SMs leaves no SM idle in its last wave
+            wave = 8 * torch.cuda.get_device_properties(self.device).multi_processor_count
+            per = -(-self.P // max(1, int(chunks)))
+            per = max(wave, -(-per // wave) * wave) if self.P >= 4 * wave else self.P
+            bounds = list(range(0, self.P, per)) + [self.P]
+            n_chunks = len(bounds) - 1
             main = torch.cuda.current_stream()
             for s in self._streams:
                 s.wait_stream(main)
