@@ -33,7 +33,8 @@ FLOP_PER_CELL_UPDATE = 11.0          # RHS 3 FMA, forward 1 FMA, backward 1 FMA 
 FP64_INSTR_PER_CELL_UPDATE = 6.0     # what the on-chip Crank-Nicolson solver issues: 4 for the sweeps + 2 spike-correction FMAs
 DFMA_DISTINCT_OPERANDS_PER_CLK_SM = 44.0   # measured: profiles/microbench/r01_fp64_operands_b200.txt
 ONCHIP_B_PER_CELL_UPDATE = 40.0      # five factored coefficients read once per step (32 B TMEM + 8 B registers)
-HBM_B_PER_CELL_UPDATE_THOMAS = 64.0  # variant 1: w, fp, fq, fb in; g out; g, fq in; w out
+HBM_B_PER_CELL_UPDATE_THOMAS = 40.0  # three per-cell-per-problem arrays streamed (24 B) + state in/out (16 B)
+HBM_B_MOVED_THOMAS = 64.0            # what thomas_steps_kernel really moves: w, l, kappa, s in, t out (40) + t, s in, w out (24)
 HBM_B_PER_CELL_UPDATE_SPIKE = 40.0   # variant 3: w, p, q, b in; g out (three per-cell arrays streamed)
 
 
@@ -181,7 +182,7 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-FUSED_SUMMARY = "r01_fused_cfg3_full.summary.txt"     # ncu --set full of the default command's dominant kernel
+FUSED_SUMMARY = "r02_fused_cfg3_full.summary.txt"     # ncu --set full of the default command's dominant kernel
 
 
 def ncu_traffic(summary_name):
@@ -629,7 +630,11 @@ def run_b200(args):
                    "cell_updates_per_s": P * J / (ms * 1e-3), "achieved": gbs, "peak": peaks["hbm_gbs"],
                    "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"], "peak_source": peak_src,
                    "algorithmic_bytes_per_cell_update": HBM_B_PER_CELL_UPDATE_THOMAS,
-                   "traffic": ncu_traffic("r01_thomas_v1.summary.txt")}
+                   "traffic_model": {"bytes_per_cell_update": HBM_B_MOVED_THOMAS,
+                                     "achieved": HBM_B_MOVED_THOMAS * P * J / (ms * 1e-3) / 1e9,
+                                     "note": "the two-pass kernel parks the eliminated value in HBM and re-reads s: "
+                                             "64 B moved for 40 B of algorithmic traffic"},
+                   "traffic": ncu_traffic("r02_thomas_v1.summary.txt")}
             del w_t
         except Exception as exc:  # noqa: BLE001
             hbm = {"error": repr(exc)}

@@ -92,6 +92,91 @@ __global__ void __launch_bounds__(128) thomas_steps_kernel(
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Tiny meshes (J <= JR): the whole system lives in the thread's registers for all `nsteps` steps of
+// the launch.  Per step only the three factor arrays are read (24 B per cell-update; s a second time
+// in the backward sweep), and they are served by L1 after the first step (see the persistent loop);
+// the state is read once at the start and written once at the end.
+// Same arithmetic, operation for operation, as thomas_steps_kernel.
+template <int JR>
+__global__ void __launch_bounds__(128) thomas_reg_kernel(
+    int J, int64_t P, const double* __restrict__ fp, const double* __restrict__ fq,
+    const double* __restrict__ fb, int64_t f_ps, int64_t f_cs, double cth,
+    const double* __restrict__ bt_left, const double* __restrict__ bt_right, double* __restrict__ w,
+    int64_t w_ps, int64_t w_cs, int64_t nsteps) {
+  // Persistent: the grid holds as many CTAs as keep the factors of the systems in flight inside the
+  // SM's L1 (3*J*8 B per system: 128 systems of 64 cells = 192 KB), and every CTA walks over groups
+  // of systems; the factors of a group then come from HBM once per LAUNCH, not once per step.
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) {
+  const double* L_ = fp + p * f_ps;
+  const double* S_ = fq + p * f_ps;
+  const double* K_ = fb + p * f_ps;
+  double* W_ = w + p * w_ps;
+  const double bl = bt_left ? bt_left[p] : 0.0;
+  const double br = bt_right ? bt_right[p] : 0.0;
+  double x[JR];
+#pragma unroll
+  for (int j = 0; j < JR; ++j) x[j] = (j < J) ? W_[j * w_cs] : 0.0;
+  const int64_t g8 = 8 * f_cs;
+  for (int64_t s = 0; s < nsteps; ++s) {
+    // Running pointers, passed through an empty asm at every group of 8 cells: the 3*JR addresses are
+    // loop invariants that the compiler would otherwise compute once and keep in registers across the
+    // steps (spilling the state), and loads are not hoisted beyond their group.
+    const double *lp = L_, *sp = S_, *kp = K_;
+    double h = 0.0;
+#pragma unroll
+    for (int g = 0; g < JR / 8; ++g) {
+      asm volatile("" : "+l"(lp), "+l"(sp), "+l"(kp) :: "memory");
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int j = 8 * g + u;
+        if (j < J) {
+          const double lj = lp[u * f_cs], sj = sp[u * f_cs], kj = kp[u * f_cs];
+          double r = x[j];
+          if (j == 0) r += bl;
+          if (j == J - 1) r += br;
+          h = fma(-lj, h, r);
+          const double wn = (j + 1 < JR) ? x[(j + 1) % JR] : 0.0;             // x[j+1] is 0 beyond the mesh
+          x[j] = fma(-sj, cth * wn, fma(h, kj, -(cth * x[j])));
+        }
+      }
+      lp += g8; sp += g8; kp += g8;
+    }
+    double z = 0.0;
+#pragma unroll
+    for (int g = JR / 8 - 1; g >= 0; --g) {
+      sp -= g8;
+      asm volatile("" : "+l"(sp) :: "memory");
+#pragma unroll
+      for (int u = 7; u >= 0; --u) {
+        const int j = 8 * g + u;
+        if (j < J) {
+          z = fma(-sp[u * f_cs], z, x[j]);   // s_{J-1} = 0: the first link returns t_{J-1}
+          x[j] = z;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < JR; ++j)
+    if (j < J) W_[j * w_cs] = x[j];
+  }
+}
+
+template <int JR>
+static void launch_thomas_reg(int64_t J, int64_t P, const double* fp, const double* fq, const double* fb,
+                              int64_t f_ps, int64_t f_cs, double cth, const double* bt_left, const double* bt_right,
+                              double* w, int64_t w_ps, int64_t w_cs, int64_t nsteps, cudaStream_t s) {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int64_t blocks = (P + 127) / 128;
+  const int64_t resident = (int64_t)sms * (JR <= 32 ? 2 : 1);
+  if (blocks > resident) blocks = resident;
+  thomas_reg_kernel<JR><<<(unsigned)blocks, 128, 0, s>>>((int)J, P, fp, fq, fb, f_ps, f_cs, cth, bt_left,
+                                                                   bt_right, w, w_ps, w_cs, nsteps);
+}
+
 }  // namespace fvm
 
 extern "C" int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, const double* fq,
@@ -104,6 +189,16 @@ extern "C" int fvm_theta_step_thomas(int64_t J, int64_t P, const double* fp, con
   const int64_t blocks = (P + 127) / 128;
   if (blocks > 0x7fffffffLL) return FVM_ERR_UNSUPPORTED;
   const double cth = (1.0 - theta) / theta;
+  if (J <= 64 && nsteps >= 4) {                  // tiny meshes, several steps: the system stays in registers and its
+                                                 // factors in L1 for the whole launch (a single step streams better)
+    if (J <= 32)
+      fvm::launch_thomas_reg<32>(J, P, fp, fq, fb, f_ps, f_cs, cth, bt_left, bt_right, w, w_ps, w_cs, nsteps,
+                                 (cudaStream_t)stream);
+    else
+      fvm::launch_thomas_reg<64>(J, P, fp, fq, fb, f_ps, f_cs, cth, bt_left, bt_right, w, w_ps, w_cs, nsteps,
+                                 (cudaStream_t)stream);
+    return (int)cudaGetLastError();
+  }
   fvm::thomas_steps_kernel<8, false><<<(unsigned)blocks, 128, 0, (cudaStream_t)stream>>>(
       J, P, fp, fq, fb, f_ps, f_cs, cth, bt_left, bt_right, w, w_ps, w_cs, nsteps, nullptr, nullptr);
   return (int)cudaGetLastError();
