@@ -513,7 +513,10 @@ class BatchedAdvectionDiffusionModel(object):
             c = self.compare(w_new, w)
             rel = c["max_abs_diff"] / torch.clamp(c["max_abs_ref"], min=1e-300)
             w, steps = w_new, steps + int(check_every)
-            if bool((rel <= tol).all()):               # one small device->host read per block
+            done, finite = (bool(v) for v in torch.stack([(rel <= tol).all(), torch.isfinite(rel).all()]).cpu())
+            if not finite:                             # diverged (Peclet / CFL violation, singular A): never steady
+                raise FloatingPointError("run_until_steady: the state is no longer finite after %d steps" % steps)
+            if done:                                   # one small device->host read per block
                 break
         return w, steps, rel
 

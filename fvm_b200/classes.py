@@ -228,7 +228,8 @@ class AdvectionDiffusionModel(object):
         w, ck = self._gpu.run(np.asarray(w_init, dtype=float)[None, :], theta, nsteps,
                               checkpoint_every, variant)
         w = w[0].cpu().numpy()
-        snaps = ck[:, 0].cpu().numpy() if checkpoint_every else None
+        # checkpoint_every > nsteps: no checkpoint was due, an empty (0, J) array comes back
+        snaps = None if not checkpoint_every else (ck[:, 0].cpu().numpy() if ck is not None else np.zeros((0, self.mesh.J)))
         if save is not None:
             np.save(save, snaps if snaps is not None else w[None, :])
         if checkpoint_every:
@@ -249,7 +250,9 @@ class AdvectionDiffusionModel(object):
         w, ck = self._gpu.run_time_varying(np.asarray(w_init, dtype=float)[None, :], theta, left_flux_t,
                                            right_flux_t, checkpoint_every)
         w = w[0].cpu().numpy()
-        return (w, ck[:, 0].cpu().numpy()) if checkpoint_every else w
+        if not checkpoint_every:
+            return w
+        return w, (ck[:, 0].cpu().numpy() if ck is not None else np.zeros((0, self.mesh.J)))
 
 
 class Model(AdvectionDiffusionModel):

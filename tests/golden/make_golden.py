@@ -98,26 +98,6 @@ def demo_J149():
                 lo=asm["lo"], di=asm["di"], up=asm["up"])
 
 
-def cfg2_subset():
-    """cfg 2 on a subset of the sweep: J=4096 graded mesh, 8 Peclet numbers x 3 schemes,
-    2000 Crank-Nicolson steps; snapshots after steps 1, 100, 2000.  The
-    exponential scheme is left out where the reference's kappa is NaN (Pe >= 709.8)."""
-    wl = W.peclet_sweep(4096)
-    pick = [0, 4, 8, 12, 16, 20, 24, 28]          # Pe = 1e-3, 1e-2, ..., 1e4
-    snaps = [1, 100, 2000]
-    out = dict(pick=np.array(pick), snaps=np.array(snaps), pe=wl["pe"][pick])
-    for scheme in O.SCHEMES:
-        for j in pick:
-            if scheme == "exponential" and wl["pe"][j] > 700:
-                continue
-            t0 = time.time()
-            st = R.reference_theta_run(wl["faces"], wl["a"][j], wl["d"][j], wl["k"][j], scheme,
-                                       wl["bc"], 0.5, wl["w0"][j], 2000, every=1)
-            out["%s_%02d" % (scheme, j)] = st[[s - 1 for s in snaps]]
-            print("cfg2", scheme, j, "%.1fs" % (time.time() - t0), flush=True)
-    return out
-
-
 def cfg3_subset():
     """cfg 3 on its first 8 problems: J=1024 graded mesh, exponential, zero-flux Robin,
     Crank-Nicolson, 2000 steps; snapshots after 1, 10, 100, 1000, 2000."""
@@ -130,6 +110,42 @@ def cfg3_subset():
         states.append(st[[s - 1 for s in snaps]])
         print("cfg3", p, flush=True)
     return dict(snaps=np.array(snaps), states=np.array(states), a=wl["a"], d=wl["d"], k=wl["k"])
+
+
+def _cfg2_one(args):
+    faces, a, d, k, scheme, bc, w0, snaps = args
+    st = R.reference_theta_run(faces, a, d, k, scheme, bc, 0.5, w0, snaps[-1], every=1)
+    return st[[s - 1 for s in snaps]]
+
+
+def cfg2_full():
+    """cfg 2 in full: J=4096 graded mesh, all 29 Peclet numbers x 3 schemes = 87 problems, 2000
+    Crank-Nicolson steps with the reference's loop; snapshots after 100 and 2000 steps.  For the five
+    Peclet numbers >= 709.8 the reference's exponential kappa is NaN (fvm_classes.py:117: inf/inf) and
+    so is its solution; `exponential_nan` lists them, and `exponential_fitted_XX` holds, for those, the
+    exact solution (oracle/thomas_arbiter.c) of the operators assembled with the cancellation- and
+    overflow-safe form D = d (B(mu) + mu/2) (oracle.fitted_D) -- what the CUDA path is checked against
+    where the reference has no answer."""
+    from concurrent.futures import ProcessPoolExecutor
+    wl = W.peclet_sweep(4096)
+    snaps = [100, 2000]
+    out = dict(snaps=np.array(snaps), pe=wl["pe"])
+    jobs, keys = [], []
+    for scheme in O.SCHEMES:
+        for j in range(len(wl["pe"])):
+            jobs.append((wl["faces"], wl["a"][j], wl["d"][j], wl["k"][j], scheme, wl["bc"], wl["w0"][j], snaps))
+            keys.append("%s_%02d" % (scheme, j))
+    with ProcessPoolExecutor(min(8, os.cpu_count() or 1)) as ex:
+        for key, st in zip(keys, ex.map(_cfg2_one, jobs)):
+            out[key] = st
+    nan = [j for j in range(len(wl["pe"])) if not np.all(np.isfinite(out["exponential_%02d" % j]))]
+    out["exponential_nan"] = np.array(nan)
+    for j in nan:
+        del out["exponential_%02d" % j]
+        asm = O.assemble(wl["faces"], wl["a"][j], wl["d"][j], "exponential", exponential="fitted", **wl["bc"])
+        A, B = O.theta_operators(asm, wl["k"][j], 0.5)
+        out["exponential_fitted_%02d" % j] = O.theta_run_arbiter(A, B, asm["beta"], wl["w0"][j], snaps[-1], snaps)
+    return out
 
 
 LONG_RUN_STEPS = 10000
@@ -191,7 +207,7 @@ def cfg3_long_run():
 if __name__ == "__main__":
     only = sys.argv[1:]
     jobs = dict(assembly_cases=assembly_cases, cfg1_examples=cfg1_examples, demo_J149=demo_J149,
-                cfg3_subset=cfg3_subset, cfg2_subset=cfg2_subset, cfg3_long_run=cfg3_long_run)
+                cfg3_subset=cfg3_subset, cfg3_long_run=cfg3_long_run, cfg2_full=cfg2_full)
     for name, fn in jobs.items():
         if only and name not in only:
             continue

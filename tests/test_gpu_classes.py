@@ -106,3 +106,23 @@ def test_device_diagnostics_match_numpy():
     assert np.array_equal(out["peclet_min"], mu.min(1)) and np.array_equal(out["peclet_max"], mu.max(1))
     assert np.array_equal(out["cfl_min"], cfl.min(1)) and np.array_equal(out["cfl_max"], cfl.max(1))
     assert np.allclose(out["area"], (w * h).sum(1), rtol=1e-13)
+
+
+def test_checkpoint_interval_longer_than_the_run_and_divergence_guard():
+    """theta_run with checkpoint_every > nsteps returns an empty checkpoint array (not a TypeError);
+    run_until_steady raises instead of stepping a NaN state to max_steps."""
+    import warnings
+    from fvm_b200 import AdvectionDiffusionModel, BatchedAdvectionDiffusionModel
+    f = np.linspace(0, 1, 41)
+    m = AdvectionDiffusionModel(f, 1.0, 0.05, 1e-3, discretisation="central")
+    m.set_boundary_conditions(left_value=1.0, right_value=0.0)
+    w0 = np.zeros(40); w0[0] = 1.0
+    w, ck = m.theta_run(w0, 0.5, 5, checkpoint_every=10)
+    assert ck.shape == (0, 40) and np.all(np.isfinite(w))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        b = BatchedAdvectionDiffusionModel(f, 1.0, 0.05, 1e-3, "central", P=1)
+    b.set_boundary_conditions(left_value=1.0, right_value=0.0)
+    bad = np.full((1, 40), np.nan)
+    with pytest.raises(FloatingPointError):
+        b.run_until_steady(bad, 1.0, check_every=5, max_steps=1000)

@@ -95,25 +95,33 @@ def test_cta_per_system_sizes(J):
 
 
 @pytest.mark.parametrize("variant", VARIANTS)
-def test_cfg2_subset_2000_steps(variant):
-    """cfg 2 (J=4096, Dirichlet flags) on the golden subset of the sweep: the streaming variant
-    and the on-chip CTA-per-system variant."""
-    g = load_golden("cfg2_subset")
+def test_cfg2_full_sweep_2000_steps(variant):
+    """cfg 2 in full (J=4096, Dirichlet flags, all 29 Peclet numbers x 3 schemes = 87 problems, 2000
+    Crank-Nicolson steps) against the unmodified reference's loop: the streaming variant and the
+    on-chip CTA-per-system variant.  Where the reference has no answer -- exponential fitting at
+    Pe >= 709.8, its kappa is inf/inf (fvm_classes.py:117) -- the check is against the exact solution
+    of the operators assembled with the overflow-safe form (tests/golden/make_golden.py cfg2_full)."""
+    g = load_golden("cfg2_full")
     wl = W.peclet_sweep(4096)
-    snaps = list(g["snaps"])
+    snaps = [int(s) for s in g["snaps"]]
+    nan = set(int(j) for j in g["exponential_nan"])
+    assert nan == {24, 25, 26, 27, 28} and all(wl["pe"][j] >= 709.8 for j in nan)
     for scheme in O.SCHEMES:
-        pick = [j for j in g["pick"] if "%s_%02d" % (scheme, j) in g.files]
-        m = BatchedAdvectionDiffusionModel(wl["faces"], wl["a"][pick], wl["d"][pick], wl["k"][pick], scheme)
+        m = BatchedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], scheme)
         m.set_boundary_conditions(**wl["bc"])
-        w = torch.as_tensor(wl["w0"][pick], device="cuda")
+        w = torch.as_tensor(wl["w0"], device="cuda")
         done = 0
-        for s in snaps:
+        for i, s in enumerate(snaps):
             w, _ = m.run(w, 0.5, s - done, variant=variant)
             done = s
             got = w.cpu().numpy()
-            for n, j in enumerate(pick):
-                want = g["%s_%02d" % (scheme, j)][snaps.index(s)]
-                err = step_error(got[n], want, 1.0)
+            assert np.all(np.isfinite(got))
+            for j in range(len(wl["pe"])):
+                key = "%s_%02d" % (scheme, j)
+                if scheme == "exponential" and j in nan:
+                    assert key not in g.files                      # recorded: reference = NaN
+                    key = "exponential_fitted_%02d" % j
+                err = step_error(got[j], g[key][i], 1.0)
                 assert err < TOL, (scheme, j, s, err)
 
 
