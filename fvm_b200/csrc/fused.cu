@@ -2,28 +2,22 @@
 //
 // Partition: lane l owns the C contiguous cells [l*C, (l+1)*C); the first N = C-1 are
 // "interior" cells, the last one is the lane's SEPARATOR.  With the separators known the
-// 32 interior blocks decouple, so (per step, all with coefficients factored ONCE per launch):
-//   1. r~  = inv*(B w)                      3 FMA / cell   (B's off-diagonals are -c*p, -c*q)
-//   2. local forward / backward sweep       2 FMA / cell   g = T^-1 r   (T = interior block of A)
-//   3. reduced system on the 32 separators  precomputed parallel cyclic reduction, 5 levels
-//                                           of 2 shuffles + 2 FMA, no divisions
-//   4. x = g - v*xs(l-1) - u*xs(l)          2 FMA / cell   (v, u = left/right spikes T^-1 e)
-// State w[C] lives in registers for the whole launch.  Five coefficients per interior cell
-// (p, q, b, v, u) must be read every step; where they live decides the speed, because a
-// step is bound by on-chip bandwidth, not arithmetic:
-//   * fused_kernel      (any J <= 1024): q in registers, p/b/v/u in shared memory
-//                       ([coef][c][lane], lane-consecutive doubles: conflict-free).
-//   * fused_tmem_kernel (512 < J <= 1024): q in registers, p/b/v/u in TENSOR MEMORY.
-//                       TMEM (256 KB/SM) is idle in this workload -- there is no MMA -- and
-//                       its tcgen05.ld path is separate from, and wider than, the 128 B/clk
-//                       shared-memory pipe (profiles/microbench/r01_tmem_bw_b200.txt).  Each
-//                       warp owns 256 columns of its lane quadrant: columns [0,128) hold
-//                       (p_c, b_c) pairs, [128,256) hold (v_c, u_c) pairs, 4 columns per cell.
-//                       Shared memory is only a staging area during set-up.
-// HBM traffic: J doubles in, J doubles out, J per checkpoint.
-//
-// Assembly (fvm_device.cuh) and factorisation run inside the same launch, one lane per
-// owned cell, so a launch needs only the mesh, the per-problem scalars and the state.
+// 32 interior blocks decouple (SPIKE).  A theta step has NO right-hand side: B = I/theta - c A
+// gives A^-1 B = A^-1/theta - c I, so with the un-normalised LU factors (l, kappa, s) of a lane's
+// block T, all factored ONCE per launch (in double-double, dd.cuh, each rounded once):
+//   1. sweeps on the block          4 operations / cell for Crank-Nicolson
+//   2. separator system (32 rows)   precomputed parallel cyclic reduction, 5 levels of 2 shuffles + 2 FMA
+//   3. spike correction             2 FMA / cell   (V, U = T^-1 of the couplings to the two separators)
+// State w[C] lives in registers for the whole launch; where the coefficients live decides the speed:
+//   * fused_kernel           (J <= 512, and the slow path of a right flux at a lane-interior cell):
+//                            s in registers, l, kappa, V, U in shared memory.
+//   * fused_tmem_pipe_kernel (512 < J <= 1024, the default of cfg 3): s in registers, (l, kappa) and
+//                            the delayed-correction vectors (P1, P2) in TENSOR MEMORY, which is idle
+//                            in this workload -- there is no MMA -- and whose tcgen05.ld path is
+//                            separate from, and wider than, the 128 B/clk shared-memory pipe.
+// HBM traffic: J doubles in, J doubles out, J per checkpoint.  Assembly (fvm_device.cuh) and the
+// factorisation run inside the same launch, so a launch needs only the mesh, the per-problem scalars
+// and the state.
 #include "fvm_device.cuh"
 #include "tmem.cuh"
 #include "dd.cuh"
@@ -38,49 +32,67 @@ constexpr int kFusedThreads = 256;   // upper bound used for register allocation
 __device__ __forceinline__ double shfl_up(double x, int s) { return __shfl_up_sync(kFull, x, s); }
 __device__ __forceinline__ double shfl_dn(double x, int s) { return __shfl_down_sync(kFull, x, s); }
 
-// Per-lane constants of one system, fixed for the whole launch.
+// Per-lane constants of one system of the shared-memory kernel, fixed for the whole launch.
 struct Reduced {
   double al[5], ga[5];           // PCR elimination factors of the separator system, per level
   double invD;                   // 1 / final PCR diagonal
   double slo, sup;               // separator's row of A (off-diagonals)
-  double sblo, sbdi, sbup;       // separator's row of B
-  double bfirst, bint, bsep, bsep_r;   // beta entries as they enter the sweeps (bsep: left-flux part, bsep_r: right-flux part)
+  double bfirst, bint;           // theta*beta[0] / theta*beta[J-1] where they enter the elimination (interior cells)
+  double bsep, bsep_r;           // beta at the separator: left-flux part (cell 0), right-flux part (cell J-1)
   int rb_c;                      // RB only: position of cell J-1 inside its lane
 };
 
-// Where phase 1 puts (p_c, b_c).
-struct PutSmem {
-  double* sp; double* sb;
-  __device__ __forceinline__ void operator()(int c, double p, double b) const { sp[c * 32] = p; sb[c * 32] = b; }
-};
-struct PutTmem {
-  uint32_t t_pb;
-  __device__ __forceinline__ void operator()(int c, double p, double b) const { tmem_st_2d(t_pb + 4 * c, p, b); }
-};
+// PCR factorisation of the 32-unknown separator system (RL, RD, RU per lane) in double-double: the
+// elimination factors of each of the 5 levels and the final diagonal are kept (each rounded once), so
+// that a step only applies them to its right-hand side (pcr_solve).  K: any struct with al, ga, invD.
+template <class KT>
+__device__ __forceinline__ void pcr_factor_dd(int lane, dd RL, dd RD, dd RU, KT& K) {
+#pragma unroll 1
+  for (int l = 0; l < 5; ++l) {
+    const int s = 1 << l;
+    const bool hm = lane >= s, hp = lane + s < 32;
+    const dd Dm = dd_shfl_up(RD, s), Dp = dd_shfl_dn(RD, s);
+    const dd Lm = dd_shfl_up(RL, s), Um = dd_shfl_up(RU, s);
+    const dd Lp = dd_shfl_dn(RL, s), Up = dd_shfl_dn(RU, s);
+    dd a_ = dd_make(0.0), g_ = dd_make(0.0);
+    if (hm) a_ = dd_neg(dd_div(RL, Dm));
+    if (hp) g_ = dd_neg(dd_div(RU, Dp));
+    K.al[l] = dd_round(a_); K.ga[l] = dd_round(g_);
+    RD = dd_add(RD, dd_add(dd_mul(a_, Um), dd_mul(g_, Lp)));
+    RL = dd_mul(a_, Lm);
+    RU = dd_mul(g_, Up);
+  }
+  K.invD = dd_round(dd_recip(RD));
+}
 
-// Phase 1: assemble this lane's rows of A, factor the interior block (p, q, b), run the
-// forward sweep of the left spike (into sv) and keep the separator's row.
-template <int C, bool RB, class Put>
-__device__ __forceinline__ void setup_rows(const fvm_problem& pr, int64_t p, int lane, double dt_p,
-                                           double theta, const Put& put, double* sq, double* sv,
-                                           Reduced& R, double& sdi) {
+// Set-up of one system of the shared-memory kernel, in double-double.
+// Phase 1 (top-down over the lane's C cells): rows of A, un-normalised LU of the interior block
+// (l -> sl, kappa -> sk, s -> ss with its low word in tlo), elimination of the left spike with the
+// UNROUNDED factors (g -> sv, low word in glo), the separator's row.  Phase 2 (bottom-up): both
+// spikes V -> sv, U -> su of the exact block, the separator system and its PCR factors.
+template <int C, bool RB>
+__device__ __forceinline__ void setup_system(const fvm_problem& pr, int64_t p, int lane, double dt_p, double theta,
+                                             double* sl, double* sk, double* ss, double* sv, double* su,
+                                             double* tlo, double* glo, Reduced& R) {
   constexpr int N = C - 1;
   const int64_t J = pr.J;
-  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
+  const double rth = 1.0 / theta;
   const double dt_theta = mul(dt_p, theta);
   double beta_l = 0.0, beta_r = 0.0;
   if (pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
     beta_l = dvd(pr.left_flux[p], sub(pr.faces[1], pr.faces[0]));
   if (pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
     beta_r = dvd(-pr.right_flux[p], sub(pr.faces[J], pr.faces[J - 1]));
-  R.slo = 0.0; sdi = 1.0; R.sup = 0.0;
+  R.slo = 0.0; R.sup = 0.0;
   R.bfirst = 0.0; R.bint = 0.0; R.bsep = 0.0; R.bsep_r = 0.0;
   R.rb_c = RB ? (int)((J - 1) % C) : -1;
-  double q_prev = 0.0, gv_prev = 0.0;
+  double sdi = 1.0;
   const int64_t j0 = (int64_t)lane * C;
   // sliding window over faces: one expm1 and one face (5 divisions) per row
   double D0 = cell_D(pr, p, j0);
   Face FL = problem_face(pr, p, j0 - 1, cell_D(pr, p, j0 - 1), D0);
+  dd s_prev = dd_make(0.0), inv_prev = dd_make(0.0), hv = dd_make(0.0);
+  double up_last = 0.0;                              // A_{N-1,N}: coupling of the last interior cell to the separator
 #pragma unroll 1
   for (int c = 0; c < C; ++c) {
     const int64_t j = j0 + c;
@@ -93,71 +105,56 @@ __device__ __forceinline__ void setup_rows(const fvm_problem& pr, int64_t p, int
     }
     D0 = Dp; FL = FR;
     if (c < N) {
-      const double inv = 1.0 / (a.di - a.lo * q_prev);
-      const double pc = a.lo * inv;
-      q_prev = a.up * inv;
-      gv_prev = (c == 0) ? pc : -pc * gv_prev;      // forward sweep of the left spike
-      put(c, pc, inv * (rth - cth * a.di));
-      sq[c * 32] = q_prev;
-      sv[c * 32] = gv_prev;
-      if (j == 0) R.bfirst = beta_l * inv;
-      if (RB && j == J - 1) R.bint = beta_r * inv;
+      const dd inv = dd_recip(dd_add_d(dd_neg(dd_mul_d(s_prev, a.lo)), a.di));
+      const dd l = dd_mul_d(inv_prev, a.lo);
+      const dd kap = dd_mul_d(inv, rth);
+      s_prev = dd_mul_d(inv, a.up);
+      inv_prev = inv;
+      hv = (c == 0) ? dd_make(a.lo) : dd_neg(dd_mul(hv, l));
+      const dd g = dd_mul(hv, kap);
+      sl[c * 32] = dd_round(l); sk[c * 32] = dd_round(kap);
+      ss[c * 32] = s_prev.hi; tlo[c * 32] = s_prev.lo;
+      sv[c * 32] = g.hi; glo[c * 32] = g.lo;
+      up_last = a.up;
+      if (j == 0) R.bfirst = theta * beta_l;
+      if (RB && j == J - 1) R.bint = theta * beta_r;
     } else {
       R.slo = a.lo; sdi = a.di; R.sup = a.up;
       if (j == 0) R.bsep += beta_l;
       if (j == J - 1) R.bsep_r += beta_r;
     }
   }
-  R.sblo = -cth * R.slo; R.sbdi = rth - cth * sdi; R.sbup = -cth * R.sup;
+  dd RL = dd_make(R.slo), RD = dd_make(sdi), RU = dd_make(R.sup);
+  if (N > 0) {
+    // substitution of both spikes, in yhat units (Vhat = V / theta): U starts from the last interior cell
+    dd vn = dd_make(sv[(N - 1) * 32], glo[(N - 1) * 32]);
+    dd un = dd_mul_d(dd_mul_d(inv_prev, rth), up_last);
+    sv[(N - 1) * 32] = dd_round(dd_mul_d(vn, theta)); su[(N - 1) * 32] = dd_round(dd_mul_d(un, theta));
+    const dd vlast = dd_mul_d(vn, theta), ulast = dd_mul_d(un, theta);
+#pragma unroll 1
+    for (int c = N - 2; c >= 0; --c) {
+      const dd sc = dd_make(ss[c * 32], tlo[c * 32]);
+      vn = dd_sub(dd_make(sv[c * 32], glo[c * 32]), dd_mul(vn, sc));
+      un = dd_neg(dd_mul(un, sc));
+      sv[c * 32] = dd_round(dd_mul_d(vn, theta)); su[c * 32] = dd_round(dd_mul_d(un, theta));
+    }
+    const dd v0 = dd_mul_d(vn, theta), u0 = dd_mul_d(un, theta);
+    const dd v0n = dd_shfl_dn(v0, 1), u0n = dd_shfl_dn(u0, 1);        // next lane's first interior cell
+    RL = dd_neg(dd_mul_d(vlast, R.slo));
+    RD = dd_sub(dd_add_d(dd_neg(dd_mul_d(ulast, R.slo)), sdi), dd_mul_d(v0n, R.sup));   // sup == 0 on lane 31
+    RU = dd_neg(dd_mul_d(u0n, R.sup));
+  }
+  pcr_factor_dd(lane, RL, RD, RU, R);
 }
 
-// Parallel cyclic reduction of the 32-unknown separator system (RL, RD, RU per lane): the
-// elimination factors of each of the 5 levels and the final diagonal are kept, so that a
-// step only applies them to its right-hand side (pcr_solve).
-__device__ __forceinline__ void pcr_factor(int lane, double RL, double RD, double RU, Reduced& R) {
+__device__ __forceinline__ double pcr_solve(double rr, const Reduced& R) {
 #pragma unroll
   for (int l = 0; l < 5; ++l) {
     const int s = 1 << l;
-    const bool hm = lane >= s, hp = lane + s < 32;
-    const double Dm = shfl_up(RD, s), Dp = shfl_dn(RD, s);
-    const double Lm = shfl_up(RL, s), Um = shfl_up(RU, s);
-    const double Lp = shfl_dn(RL, s), Up = shfl_dn(RU, s);
-    const double a_ = hm ? -RL / Dm : 0.0;
-    const double g_ = hp ? -RU / Dp : 0.0;
-    R.al[l] = a_; R.ga[l] = g_;
-    RD = RD + (hm ? a_ * Um : 0.0) + (hp ? g_ * Lp : 0.0);
-    RL = hm ? a_ * Lm : 0.0;
-    RU = hp ? g_ * Up : 0.0;
+    const double rm = shfl_up(rr, s), rp = shfl_dn(rr, s);
+    rr = fma(R.ga[l], rp, fma(R.al[l], rm, rr));
   }
-  R.invD = 1.0 / RD;
-}
-
-// Phase 2: backward sweeps of both spikes (sv: gv -> v; su <- u, reading q from sq, which
-// may alias su), the separator system and its PCR factors.
-template <int C>
-__device__ __forceinline__ void setup_reduced(int lane, const double* sq, double* sv, double* su,
-                                              double sdi, Reduced& R) {
-  constexpr int N = C - 1;
-  double RL = R.slo, RD = sdi, RU = R.sup;
-  if (N > 0) {
-    double vn = sv[(N - 1) * 32];
-    double un = sq[(N - 1) * 32];
-    su[(N - 1) * 32] = un;
-    const double vlast = vn, ulast = un;
-#pragma unroll 1
-    for (int c = N - 2; c >= 0; --c) {
-      const double qc = sq[c * 32];
-      vn = sv[c * 32] - qc * vn;
-      un = -qc * un;
-      sv[c * 32] = vn;
-      su[c * 32] = un;
-    }
-    const double v0n = shfl_dn(vn, 1), u0n = shfl_dn(un, 1);   // next lane's first interior cell
-    RL = -R.slo * vlast;
-    RD = sdi - R.slo * ulast - R.sup * v0n;         // sup == 0 on lane 31
-    RU = -R.sup * u0n;
-  }
-  pcr_factor(lane, RL, RD, RU, R);
+  return rr * R.invD;
 }
 
 template <int C>
@@ -177,25 +174,6 @@ __device__ __forceinline__ void store_state(double* __restrict__ dst, int64_t J,
   }
 }
 
-// r~ of one interior cell.  MODE 0: any theta in (0,1];  1: Crank-Nicolson (c = 1);  2: implicit (c = 0).
-template <int MODE>
-__device__ __forceinline__ double rhs_cell(double pc, double qc, double bc, double wm, double wc,
-                                           double wp, double cth) {
-  if (MODE == 2) return bc * wc;
-  const double t = fma(qc, wp, pc * wm);
-  return (MODE == 1) ? fma(bc, wc, -t) : fma(-cth, t, bc * wc);
-}
-
-__device__ __forceinline__ double pcr_solve(double rr, const Reduced& R) {
-#pragma unroll
-  for (int l = 0; l < 5; ++l) {
-    const int s = 1 << l;
-    const double rm = shfl_up(rr, s), rp = shfl_dn(rr, s);
-    rr = fma(R.ga[l], rp, fma(R.al[l], rm, rr));
-  }
-  return rr * R.invD;
-}
-
 // What changes from step to step (nothing of this is in the reference, whose beta and k
 // are constants of a model: fvm_classes.py:221,228 only mention the case).  All pointers may be NULL.
 //  * boundary fluxes: step s uses  flux * scale_left[s*sc_ss + p*sc_ps]  (beta is linear in the flux,
@@ -212,8 +190,14 @@ struct FusedExtras {
 };
 
 // ------------------------------------------------------------------------------------------
-// Shared-memory variant.  RB: beta[J-1] is nonzero AND cell J-1 is an interior cell of its
-// lane (slow path).  QREG: q in registers (4 instead of 6 shared-memory reads per cell-update).
+// Shared-memory variant (J <= 512, and the RB slow path of J <= 1024).  Same formulation as the
+// tensor-memory kernel below -- no right-hand side, separator rows in yhat, set-up in double-double,
+// spikes of the exact block -- without its twisted factorisation and delayed correction: per step
+//   h_c = g_c + theta*beta_c - l_c h_{c-1};  t_c = h_c kappa_c - c g_c - c s_c g_{c+1};  z_c = t_c - s_c z_{c+1}
+//   R yhat_s = xs/theta + beta_s - slo ghat_last - sup ghat_first(next lane),  ghat = z + c g
+//   x'_c = z_c - V_c yhat_s(l-1) - U_c yhat_s(l);   x'_s = yhat_s - c xs
+// l, kappa, V, U in shared memory ([coef][c][lane], lane-consecutive doubles: conflict-free), s in
+// registers (QREG).  RB: beta[J-1] is nonzero AND cell J-1 is an interior cell of its lane.
 template <int C, int MODE, bool RB, bool QREG, bool EXT>
 __global__ void __launch_bounds__(kFusedThreads, 1)
 fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
@@ -224,14 +208,17 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps = blockDim.x >> 5;
-  constexpr int NARR = QREG ? 4 : 5;
-  double* sp = smem + (size_t)warp * (NARR * NS * 32) + lane;   // [c*32] indexing below
-  double* sb = sp + NS * 32;
-  double* sv = sb + NS * 32;
+  constexpr int NARR = 7;                            // l, kappa, V, U, and during set-up s, low words of s and g
+  double* sl = smem + (size_t)warp * (NARR * NS * 32) + lane;   // [c*32] indexing below
+  double* sk = sl + NS * 32;
+  double* sv = sk + NS * 32;
   double* su = sv + NS * 32;
-  double* sq = QREG ? su : su + NS * 32;   // QREG: q is staged in u's slots during set-up only
+  double* ss = su + NS * 32;
+  double* tlo = ss + NS * 32;
+  double* glo = tlo + NS * 32;
   const int64_t J = pr.J;
-  const double cth = (1.0 - theta) / theta;
+  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
+  auto cmul = [&](double x) { return (MODE == 1) ? x : cth * x; };      // c * x (MODE 2 never asks)
 
   const int64_t n_ck_total = (ckpt != nullptr && ckpt_every > 0) ? nsteps / ckpt_every : 0;
   for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
@@ -246,14 +233,10 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
       dt_run = ex.dt_hist[s0 * ex.dt_ss + p * ex.dt_ps];
     }
     Reduced R;
-    double sdi;
-    setup_rows<C, RB>(pr, p, lane, dt_run, theta, PutSmem{sp, sb}, sq, sv, R, sdi);
+    setup_system<C, RB>(pr, p, lane, dt_run, theta, sl, sk, ss, sv, su, tlo, glo, R);
     double qr[NS];
-    if (QREG) {
 #pragma unroll
-      for (int c = 0; c < NS; ++c) qr[c] = (c < N) ? sq[c * 32] : 0.0;
-    }
-    setup_reduced<C>(lane, sq, sv, su, sdi, R);
+    for (int c = 0; c < NS; ++c) qr[c] = (c < N) ? ss[c * 32] : 0.0;
     __syncwarp();
 
     double w[C];
@@ -266,39 +249,37 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
         const double sc_r = ex.scale_right ? ex.scale_right[s_glob * ex.sc_ss + p * ex.sc_ps] : 1.0;
         bfirst *= sc_l; bint *= sc_r; bsep = R.bsep * sc_l + R.bsep_r * sc_r;
       }
-      double wl = shfl_up(w[C - 1], 1);
-      double wr = shfl_dn(w[0], 1);
-      if (lane == 0) wl = 0.0;
-      if (lane == 31) wr = 0.0;
-      double rr;
+      const double xs_old = w[C - 1];
+      double rr = fma(xs_old, rth, bsep);
       if (N > 0) {
-        double wm = wl, g = 0.0;
+        const double g0_old = w[0], gl_old = w[N - 1];
+        double h = 0.0;
 #pragma unroll
         for (int c = 0; c < N; ++c) {
-          const double pc = sp[c * 32];
-          const double wc = w[c];
-          double r = rhs_cell<MODE>(pc, QREG ? qr[c] : sq[c * 32], sb[c * 32], wm, wc, w[c + 1], cth);
+          const double gc = w[c];
+          double r = gc;
           if (c == 0) r += bfirst;
           if (RB) { if (c == R.rb_c) r += bint; }
-          g = (c == 0) ? r : fma(-pc, g, r);
-          w[c] = g;
-          wm = wc;
+          h = (c == 0) ? r : fma(-sl[c * 32], h, r);
+          double t = (MODE == 2) ? h * sk[c * 32] : fma(h, sk[c * 32], -cmul(gc));
+          if (MODE != 2 && c + 1 < N) t = fma(-qr[c], cmul(w[c + 1]), t);
+          w[c] = t;
         }
-        const double rs = fma(R.sbup, wr, fma(R.sbdi, w[C - 1], fma(R.sblo, wm, bsep)));
 #pragma unroll
-        for (int c = N - 2; c >= 0; --c) w[c] = fma(-(QREG ? qr[c] : sq[c * 32]), w[c + 1], w[c]);
-        const double g0n = shfl_dn(w[0], 1);
-        rr = fma(-R.sup, g0n, fma(-R.slo, w[N - 1], rs));
-      } else {
-        rr = fma(R.sbup, wr, fma(R.sbdi, w[0], fma(R.sblo, wl, bsep)));
+        for (int c = N - 2; c >= 0; --c) w[c] = fma(-qr[c], w[c + 1], w[c]);
+        // ghat = z + c g: the block solution of yhat with the separators at zero
+        const double gh_last = (MODE == 2) ? w[N - 1] : w[N - 1] + cmul(gl_old);
+        const double gh_first = (MODE == 2) ? w[0] : w[0] + cmul(g0_old);
+        const double gh_first_next = shfl_dn(gh_first, 1);        // lane 31: sup == 0
+        rr = fma(-R.sup, gh_first_next, fma(-R.slo, gh_last, rr));
       }
-      const double xs = pcr_solve(rr, R);
+      const double ys = pcr_solve(rr, R);
       if (N > 0) {
-        const double xsl = shfl_up(xs, 1);          // lane 0: v == 0, value unused
+        const double ysl = shfl_up(ys, 1);          // lane 0: V == 0, value unused
 #pragma unroll
-        for (int c = 0; c < N; ++c) w[c] = fma(-su[c * 32], xs, fma(-sv[c * 32], xsl, w[c]));
+        for (int c = 0; c < N; ++c) w[c] = fma(-su[c * 32], ys, fma(-sv[c * 32], ysl, w[c]));
       }
-      w[C - 1] = xs;
+      w[C - 1] = (MODE == 2) ? ys : ys - cmul(xs_old);
 
       const int64_t done = s_glob + 1;
       if (n_ck_total > 0 && done % ckpt_every == 0 && done / ckpt_every <= n_ck_total)
@@ -390,26 +371,6 @@ struct PipeConsts {
   double bsep, bfirst;           // beta at the separator; theta * beta at global cell 0
   double om_l, om_r;             // (1 - theta) * coupling of the block's end cells to the separators
 };
-
-// PCR factorisation of the 32-unknown separator system in dd; the factors are rounded once.
-__device__ __forceinline__ void pcr_factor_dd(int lane, dd RL, dd RD, dd RU, PipeConsts& K) {
-#pragma unroll 1
-  for (int l = 0; l < 5; ++l) {
-    const int s = 1 << l;
-    const bool hm = lane >= s, hp = lane + s < 32;
-    const dd Dm = dd_shfl_up(RD, s), Dp = dd_shfl_dn(RD, s);
-    const dd Lm = dd_shfl_up(RL, s), Um = dd_shfl_up(RU, s);
-    const dd Lp = dd_shfl_dn(RL, s), Up = dd_shfl_dn(RU, s);
-    dd a_ = dd_make(0.0), g_ = dd_make(0.0);
-    if (hm) a_ = dd_neg(dd_div(RL, Dm));
-    if (hp) g_ = dd_neg(dd_div(RU, Dp));
-    K.al[l] = dd_round(a_); K.ga[l] = dd_round(g_);
-    RD = dd_add(RD, dd_add(dd_mul(a_, Um), dd_mul(g_, Lp)));
-    RL = dd_mul(a_, Lm);
-    RU = dd_mul(g_, Up);
-  }
-  K.invD = dd_round(dd_recip(RD));
-}
 
 // Set-up of one system (see 5. above).  On return: (l, kappa) and (P1, P2) are in tensor memory,
 // s in sS, V and U in sv / su (natural cell order), the step constants in K.
@@ -880,7 +841,7 @@ template <int C, int MODE, bool RB, bool QREG, bool EXT>
 static int launch_fused(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
                         int64_t ckpt_every, double* w, double* ckpt, const FusedExtras& ex, cudaStream_t stream) {
   constexpr int NS = (C > 1 ? C - 1 : 1);
-  constexpr size_t per_warp = (size_t)(QREG ? 4 : 5) * NS * 32 * sizeof(double);
+  constexpr size_t per_warp = (size_t)7 * NS * 32 * sizeof(double);   // l, kappa, V, U + three set-up staging arrays
   int sms = 0, max_smem = 0;
   int st = device_limits(sms, max_smem);
   if (st) return st;

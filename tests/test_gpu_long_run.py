@@ -113,3 +113,26 @@ def test_full_run_length_with_the_fitted_diffusivity(variant):
         assert e_own.max() <= 1e-11, (variant, g["snaps"][s_i], e_own)
         assert e_ref.max() <= 1e-9, (variant, g["snaps"][s_i], g["problems"][e_ref.argmax()], e_ref.max())
     print("%s, own fitting: worst vs exact of own operators %.2e, vs reference %.2e" % (variant, worst[0], worst[1]))
+
+
+@pytest.mark.parametrize("J", [256, 500])
+def test_full_run_length_on_the_shared_memory_kernel(J):
+    """The smaller on-chip kernel (J <= 512: `fused_kernel`, one warp per system, coefficients in
+    shared memory) over 10,000 stiff Crank-Nicolson steps, against the exact solution of the
+    operators the oracle assembles (central scheme: assembly is bit-identical to the reference's, so
+    these ARE the reference's operators).  Same bar as the cfg 3 kernels: 1e-11."""
+    from fvm_b200 import BatchedAdvectionDiffusionModel
+    from oracle import fvm_oracle as O
+    wl = W.batched_sweep(64, J, seed=3)
+    pick = np.argsort(wl["a"] / wl["d"])[:3]                    # the three most diffusive (stiffest) problems
+    a, d, k, w0 = wl["a"][pick], wl["d"][pick], wl["k"][pick], wl["w0"][pick]
+    m = BatchedAdvectionDiffusionModel(wl["faces"], a, d, k, "central")
+    m.set_boundary_conditions(**BC)
+    got = {v: m.run(w0, 0.5, 10000, variant=v)[0].cpu().numpy() for v in ("fused", "thomas")}
+    for q in range(len(pick)):
+        asm = O.assemble(wl["faces"], a[q], d[q], "central", **BC)
+        A, B = O.theta_operators(asm, k[q], 0.5)
+        exact = O.theta_run_arbiter(A, B, asm["beta"], w0[q], 10000)[0]
+        for v in got:
+            err = _err(got[v][q], exact, w0[q])
+            assert err <= 1e-11, (J, v, q, err)
