@@ -115,16 +115,17 @@ def test_full_run_length_with_the_fitted_diffusivity(variant):
     print("%s, own fitting: worst vs exact of own operators %.2e, vs reference %.2e" % (variant, worst[0], worst[1]))
 
 
-@pytest.mark.parametrize("J", [256, 500])
-def test_full_run_length_on_the_shared_memory_kernel(J):
-    """The smaller on-chip kernel (J <= 512: `fused_kernel`, one warp per system, coefficients in
-    shared memory) over 10,000 stiff Crank-Nicolson steps, against the exact solution of the
-    operators the oracle assembles (central scheme: assembly is bit-identical to the reference's, so
-    these ARE the reference's operators).  Same bar as the cfg 3 kernels: 1e-11."""
+@pytest.mark.parametrize("J,nprob", [(256, 3), (500, 3), (2048, 1)])
+def test_full_run_length_on_the_other_on_chip_kernels(J, nprob):
+    """The other on-chip kernels -- `fused_kernel` (J <= 512: one warp per system, coefficients in
+    shared memory) and `fused_cta_kernel` (J > 1024: one CTA per system) -- over 10,000 stiff
+    Crank-Nicolson steps, against the exact solution of the operators the oracle assembles (central
+    scheme: assembly is bit-identical to the reference's, so these ARE the reference's operators).
+    Same bar as the cfg 3 kernels: 1e-11."""
     from fvm_b200 import BatchedAdvectionDiffusionModel
     from oracle import fvm_oracle as O
     wl = W.batched_sweep(64, J, seed=3)
-    pick = np.argsort(wl["a"] / wl["d"])[:3]                    # the three most diffusive (stiffest) problems
+    pick = np.argsort(wl["a"] / wl["d"])[:nprob]                # the most diffusive (stiffest) problems
     a, d, k, w0 = wl["a"][pick], wl["d"][pick], wl["k"][pick], wl["w0"][pick]
     m = BatchedAdvectionDiffusionModel(wl["faces"], a, d, k, "central")
     m.set_boundary_conditions(**BC)
