@@ -47,8 +47,8 @@ class Comm(object):
             self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
             self.backend = dist.get_backend(group)
 
-    def all_gather(self, t):
-        """t: tensor of identical shape on every rank -> tensor [world, *t.shape]."""
+    def all_gather(self, t, out=None):
+        """t: tensor of identical shape on every rank -> tensor [world, *t.shape] (``out`` if given: NCCL only)."""
         import torch
         if self.world == 1:
             return t.unsqueeze(0)
@@ -59,7 +59,8 @@ class Comm(object):
             dist.all_gather(parts, host, group=self.group)
             return torch.stack(parts).to(t.device)
         t = t.contiguous()
-        out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+        if out is None:
+            out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
         if self.timing is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -276,11 +277,11 @@ class PartitionedAdvectionDiffusionModel(object):
         self._theta = theta
         self._ready = theta
 
-    def _reduced_local_solve(self, rhs):
+    def _reduced_local_solve(self, rhs, out=None):
         """Solve this rank's block of the separator system (its own nt unknowns, couplings to the
         neighbouring ranks cut, last unknown = the rank's separator, decoupled): rhs (P, nt) -> (P, nt)."""
         torch = _lib.require_cuda()
-        out = torch.empty_like(rhs)
+        out = torch.empty_like(rhs) if out is None else out
         with torch.cuda.device(self.device):
             st = _lib.lib().fvm_spike_reduce_solve(self.nt, self.P, _lib.ptr(self.rp), _lib.ptr(self.rq),
                                                    _lib.ptr(self.rinv), _lib.ptr(rhs), _lib.ptr(out),
@@ -337,6 +338,8 @@ class PartitionedAdvectionDiffusionModel(object):
                                     self.W0_all[:, first]], dim=1).contiguous()
         self.xs_ext = torch.zeros((P, nt + 1), dtype=torch.float64, device=dev)
         self.packet = torch.zeros((P, 4), dtype=torch.float64, device=dev)
+        self._gr = torch.zeros((P, nt), dtype=torch.float64, device=dev)          # work arrays of a step: nothing is
+        self._allp = torch.zeros((W, P, 4), dtype=torch.float64, device=dev)      # allocated inside the time loop
         self.next_first = torch.zeros(P, dtype=torch.float64, device=dev)
 
     # ------------------------------------------------------------------ state
@@ -465,11 +468,11 @@ class PartitionedAdvectionDiffusionModel(object):
         """Second half of a step with the rank-level hierarchy (see _prepare_rank_level): local block
         solve of the separator system, ONE all-gather of 4 doubles per problem, top system, finalize."""
         lib, P, nt, comm = _lib.lib(), self.P, self.nt, self.comm
-        gr = self._reduced_local_solve(self.rr)       # block solution; the separator row passes its rhs through
+        gr = self._reduced_local_solve(self.rr, self._gr)   # block solution; the separator row passes its rhs through
         st = lib.fvm_spike_rank_pack(P, nt, _lib.ptr(gr), _lib.ptr(self.g_first), _lib.ptr(self.packet),
                                      _lib.stream_ptr())
         _lib.check(st, "fvm_spike_rank_pack")
-        allp = comm.all_gather(self.packet)                              # (W, P, 4)
+        allp = comm.all_gather(self.packet, self._allp)                  # (W, P, 4), into a buffer kept across steps
         st = lib.fvm_spike_rank_top(P, nt, comm.world, comm.rank, _lib.ptr(allp), _lib.ptr(self.top_inv),
                                     _lib.ptr(self.top_cst), _lib.ptr(gr), _lib.ptr(self.Vr), _lib.ptr(self.Wr),
                                     _lib.ptr(self.xs_ext), _lib.ptr(self.next_first), _lib.stream_ptr())
