@@ -282,7 +282,8 @@ def long_system_legs(world, rank, local, dev, peaks, peak_src, group):
     from fvm_b200 import PartitionedAdvectionDiffusionModel, workloads as W
     from fvm_b200.partitioned import plan_partition
     out = {}
-    T, Jr = 8192, 1 << 27
+    from fvm_b200 import _lib
+    T, Jr = int(_lib.lib().fvm_spike_tile_cells(2)), 1 << 27       # the default tile of PartitionedAdvectionDiffusionModel
 
     def model_cfg5(J, j0, j1, grp):
         sl = W.graded_slab(J, j0, j1, dev)
@@ -427,7 +428,8 @@ def run_partitioned(args):
         inner = 20 if args.inner is None else args.inner
         J = world << 27
         from fvm_b200.partitioned import plan_partition
-        T = 8192
+        from fvm_b200 import _lib
+        T = int(_lib.lib().fvm_spike_tile_cells(2))
         j0, j1 = plan_partition(J, T, world)["ranges"][rank]
         sl = W.graded_slab(J, j0, j1, dev)
         m = PartitionedAdvectionDiffusionModel(sl["faces"], 1.0, sl["d_pe2"], sl["dt"], "exponential", P=1, J=J,

@@ -169,7 +169,7 @@ struct LazyCorrection {
 };
 
 template <int TPB, int CPT, int MODE, bool LAZY>
-__global__ void __launch_bounds__(TPB) tile_solve_kernel(
+__global__ void __launch_bounds__(TPB, (TPB == 256 ? 2 : 1)) tile_solve_kernel(
     int64_t n_tiles, const double* __restrict__ p, const double* __restrict__ q,
     const double* __restrict__ b, const double* __restrict__ sep, const double* __restrict__ bends,
     int has_first_cell, int64_t jl_last, double cth, const double* __restrict__ w_in,
@@ -356,9 +356,9 @@ __global__ void __launch_bounds__(256) correct_kernel(int64_t n_tiles, int TPB, 
 
 // ------------------------------------------------------------------------------------------ C-ABI
 namespace {
-constexpr int kTileCfgs = 2;
-inline int tile_threads(int cfg) { return cfg == 0 ? 512 : 64; }
-inline int tile_cpt(int cfg) { return cfg == 0 ? 16 : 4; }
+constexpr int kTileCfgs = 3;      // 0: 512 x 16 = 8192 cells (production), 1: 64 x 4 (tests), 2: 256 x 16 = 4096 cells, two CTAs per SM
+inline int tile_threads(int cfg) { return cfg == 0 ? 512 : (cfg == 1 ? 64 : 256); }
+inline int tile_cpt(int cfg) { return cfg == 1 ? 4 : 16; }
 inline int tile_cells(int cfg) { return tile_threads(cfg) * tile_cpt(cfg); }
 }
 
@@ -447,11 +447,12 @@ extern "C" int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const
   if (n_tiles < 1 || P < 1 || P > 65535 || !(theta > 0.0 && theta <= 1.0)) return FVM_ERR_INVALID_ARG;
   if (config < 0 || config >= kTileCfgs || n_tiles > 0x7fffffffLL) return FVM_ERR_INVALID_ARG;
   cudaStream_t s = (cudaStream_t)stream;
-  int st = config == 0
-               ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+  int st = config == 0 ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
                                             w_in, w_out, rs, w_stride, s)
-               : launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
-                                          w_in, w_out, rs, w_stride, s);
+       : config == 1 ? launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+                                            w_in, w_out, rs, w_stride, s)
+                     : launch_tile_solve<256, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+                                            w_in, w_out, rs, w_stride, s);
   if (st) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
   fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,
@@ -522,11 +523,12 @@ extern "C" int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, 
   lz.Vt = Vt; lz.Wt = Wt; lz.xs = xs; lz.tile_offset = tile_offset; lz.n_tiles_global = n_tiles_global;
   extent_threads(config, extents_host, lz.tl, lz.tr);
   cudaStream_t s = (cudaStream_t)stream;
-  int st = config == 0
-               ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+  int st = config == 0 ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
                                             w_in, w_out, rs, w_stride, s, &lz)
-               : launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
-                                          w_in, w_out, rs, w_stride, s, &lz);
+       : config == 1 ? launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+                                            w_in, w_out, rs, w_stride, s, &lz)
+                     : launch_tile_solve<256, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
+                                            w_in, w_out, rs, w_stride, s, &lz);
   if (st) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
   fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,
@@ -594,11 +596,12 @@ extern "C" int fvm_spike_local_static(int64_t n_tiles, int64_t P, int32_t config
   // Nothing in the scratch has to start at zero: the first kernel writes every entry
   // [0, P*n_tiles) before the second one reads it; what earlier calls left behind is overwritten.
   cudaStream_t s = (cudaStream_t)stream;
-  st = config == 0
-           ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
+  st = config == 0 ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
                                         w_out, rs, w_stride, s)
-           : launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
-                                      w_out, rs, w_stride, s);
+       : config == 1 ? launch_tile_solve<64, 4>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
+                                        w_out, rs, w_stride, s)
+                     : launch_tile_solve<256, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
+                                        w_out, rs, w_stride, s);
   if (st) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
   fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,

@@ -94,11 +94,12 @@ class PartitionedAdvectionDiffusionModel(object):
         [max(j0-1, 0), min(j1+1, J)] of this rank's range [j0, j1), per-cell coefficients
         cover the cells [max(j0-1, 0), min(j1, J-1)].
     ``a``, ``d``, ``reaction`` may also be scalars or (P,) per-problem scalars; ``k`` (the time
-    step) is a scalar or (P,).
+    step) is a scalar or (P,).  ``config`` picks the tile: 2 (default) = 4,096 cells, 256 threads, two CTAs
+    per SM, so one tile's scans overlap the other's loads; 0 = 8,192 cells, 512 threads; 1 = 256 cells (tests).
     """
 
     def __init__(self, faces, a, d, k, discretisation="central", P=1, reaction=None, strict_bc=False,
-                 J=None, group=None, config=0, spike_tol=1e-30, device=None, hierarchical=True, lazy=True):
+                 J=None, group=None, config=2, spike_tol=1e-30, device=None, hierarchical=True, lazy=True):
         torch = _lib.require_cuda()
         lib = _lib.lib()
         if discretisation not in _lib.SCHEMES:

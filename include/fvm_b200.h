@@ -211,8 +211,11 @@ int fvm_theta_run_fused_ex(const fvm_problem* prob, const double* dt, double the
  * Work arrays (all caller-owned): p, q, b, Vt, Wt [P][n_tiles*T]; sep [P][n_tiles][10];
  * bends [P][2]; rs, rr [P][n_tiles]; g_first [P]; xs, rp, rq, rinv [P][n_global]. */
 
-/* Cells per tile of a tile configuration (0: production, 8192; 1: small tiles for tests), 0 if
- * the configuration does not exist. */
+/* Cells per tile of a tile configuration, 0 if the configuration does not exist.
+ *   0: 8192 cells (512 threads x 16 cells, one CTA per SM)
+ *   1: 256 cells (small tiles: tests reach many tiles on small meshes)
+ *   2: 4096 cells (256 threads x 16 cells, two CTAs per SM: the scans of one tile overlap the loads
+ *      of the other; 16 % faster per step on cfg 5 and the host layer's default) */
 int64_t fvm_spike_tile_cells(int32_t config);
 
 /* Threads TPB of the CTA that owns a tile.  Every per-cell array of variant 3 (p, q, b, Vt, Wt

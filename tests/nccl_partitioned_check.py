@@ -4,7 +4,7 @@ tests/test_gpu_multi_nccl.py (pytest, skipped on a single-GPU box) or by hand un
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
         --master-port 29544 tests/nccl_partitioned_check.py
 
-Every rank holds a slab of one 200,000-cell graded mesh (production tiles, 8192 cells); the
+Every rank holds a slab of one 200,000-cell graded mesh (production tiles, 4096 cells); the
 slabs' results are gathered and compared with (i) the same solver on a single rank and (ii) the
 oracle's scipy loop (the reference's algorithm).  Prints one JSON line on rank 0; exits non-zero
 on failure.  (The single-GPU emulation of this test, ranks over gloo sharing one GPU, is

@@ -45,8 +45,10 @@ def test_small_tiles_against_oracle(J):
             assert step_error(got[p], want, np.max(np.abs(w0[p]))) < TOL, (J, bc, theta, p)
 
 
-def test_production_tiles_against_oracle():
-    """Tile configuration 0 (8192 cells per tile), three tiles, per-cell coefficients, large dt."""
+@pytest.mark.parametrize("config", [0, 2])
+def test_production_tiles_against_oracle(config):
+    """Tile configurations 0 (8192 cells per tile, three tiles) and 2 (4096 cells, two CTAs per SM, the
+    default; five tiles), per-cell coefficients, large dt."""
     J = 20000
     f = W.graded_faces(J, 100.0)
     c = 0.5 * (f[1:] + f[:-1])
@@ -56,7 +58,7 @@ def test_production_tiles_against_oracle():
     k = 40.0 * h.min()
     w0 = W.pulse(c) + 0.1
     bc = dict(left_flux=0.0, right_flux=0.0)
-    m = PartitionedAdvectionDiffusionModel(f, a, d, k, "exponential", config=0)
+    m = PartitionedAdvectionDiffusionModel(f, a, d, k, "exponential", config=config)
     m.set_boundary_conditions(**bc)
     got = m.run(w0[None, :], 0.5, 20).cpu().numpy()[0]
     want = oracle_run(f, a, d, k, "exponential", bc, 0.5, w0, 20)
