@@ -5,30 +5,32 @@
 //
 //   set-up (once per model)
 //     spike_assemble_kernel : rows of A = I - dt*theta*alpha*M for every local cell
-//     spike_tile_factor_kernel : per tile, LU of the interior block (p, q, b as in the other
-//                             variants, factorisation restarted at the tile's first cell) and
-//                             the tile spikes Vt = T^-1(lo_first e_first), Wt = T^-1(up_last e_last)
+//     spike_tile_factor_kernel : per tile, un-normalised LU of the interior block (l, kappa, s as in
+//                             the other variants, restarted at the tile's first cell) and the tile
+//                             spikes Vt = T^-1(lo_first e_first), Wt = T^-1(up_last e_last); every
+//                             chain in double-double, every stored number rounded once
 //     (host)                  reduced tridiagonal over ALL tile separators of ALL ranks,
-//     reduced_factor_kernel   factored once
-//   every step
-//     tile_solve_kernel     : one CTA per tile: r~ = inv*(B w); tile-local Thomas, parallelised
+//     reduced_factor_kernel   factored once (double-double chain)
+//   every step (no right-hand side: w' = A^-1(w/theta + beta) - c w, c = (1-theta)/theta)
+//     tile_solve_kernel     : one CTA per tile: tile-local solve of A g = w/theta + beta, parallelised
 //                             over the CTA by a scan of affine maps g_out = A*g_in + B (each
 //                             thread owns CPT consecutive cells: one sequential pass for its
 //                             (A, B), a shuffle/shared-memory scan, one pass with the true carry);
-//                             same backwards.  Reads w, p, q, b and writes g: 40 B per cell.
-//     reduced_rhs_kernel    : rr_k = rs_k - lo_k g_last(k) - up_k g_first(k+1)
-//     (host, multi-GPU)       all-gather of rr over the ranks (NCCL), nT doubles per rank
-//     reduced_solve_kernel  : Thomas on the factored separator system, one CTA, affine scans
-//     correct_kernel        : x = g - Vt xs(k-1) - Wt xs(k), only over the extent where a spike
-//                             exceeds `spike_tol` (spikes decay away from the tile edges).  In a
-//                             time loop this pass is skipped: the next step's tile_solve_kernel
-//                             applies the correction while it loads the tile (LAZY), and only the
-//                             separators and ghosts are written between steps.
+//                             same backwards; writes z = g - c w.  Reads w, l, kappa, s and writes
+//                             z: 40 B per cell.  No cell needs its neighbours' old values.
+//     reduced_rhs_kernel    : rr_k = w_s/theta + beta_s - lo_k g_last(k) - up_k g_first(k+1)
+//     (host, multi-GPU)       all-gather over the ranks (NCCL)
+//     reduced_solve_kernel  : Thomas on the factored separator system, one CTA, affine scans: the
+//                             separators' values ys of y = A^-1(w/theta + beta)
+//     correct_kernel        : w' = z - Vt ys(k-1) - Wt ys(k), only over the extent where a spike
+//                             exceeds `spike_tol` (spikes decay away from the tile edges; at the
+//                             separator Vt = 0, Wt = -1).  In a time loop this pass is skipped: the
+//                             next step's tile_solve_kernel applies the correction while it loads
+//                             the tile (LAZY), and nothing is written between steps.
 //   multi-GPU, rank level   : rank_pack_kernel / rank_top_kernel around ONE all-gather per step
 //
 // All indices are LOCAL to the rank's slab unless they say "global"; the slab starts at global
-// cell j_offset = tile_offset*T.  State arrays carry one ghost cell on each side
-// (w[-1], w[n_local]) that holds the neighbouring rank's edge value.
+// cell j_offset = tile_offset*T.
 //
 // LAYOUT.  Thread t of a tile's CTA owns the CPT consecutive cells [t*CPT, (t+1)*CPT) (the
 // recurrences need a blocked ownership), but every per-cell array of the library (p, q, b, Vt,
@@ -39,6 +41,7 @@
 // first and last cell in both orders, so ghosts and tile neighbours need no special casing.
 #include "fvm_device.cuh"
 #include "cta_scan.cuh"
+#include "dd.cuh"
 
 namespace fvm {
 
@@ -46,7 +49,7 @@ namespace fvm {
 __device__ __forceinline__ int tiled_pos(int r, int TPB, int CPT) { return (r % CPT) * TPB + r / CPT; }
 
 // Per-tile constants, SEP_STRIDE doubles per tile.
-enum { SEP_LO = 0, SEP_UP, SEP_BLO, SEP_BDI, SEP_BUP, SEP_BETA, SEP_RL, SEP_RDA, SEP_V0, SEP_W0, SEP_STRIDE };
+enum { SEP_LO = 0, SEP_UP, SEP_RL, SEP_RDA, SEP_V0, SEP_W0, SEP_STRIDE };
 
 // ------------------------------------------------------------------------------------------ set-up
 // Rows of A for the local cells; lo -> p, di -> b, up -> q (transformed in place by the next kernel).
@@ -69,8 +72,15 @@ __global__ void __launch_bounds__(256) spike_assemble_kernel(fvm_problem pr, con
   p[o] = a.lo; b[o] = a.di; q[o] = a.up;
 }
 
-// One thread per tile: LU of the interior block restarted at the tile's first cell, the tile
-// spikes, the separator's rows and the tile's contribution to the reduced system.
+// One thread per tile: un-normalised LU of the interior block restarted at the tile's first cell
+// (l_c = lo_c / pivot_{c-1}, kappa_c = 1 / (theta pivot_c), s_c = up_c / pivot_c; DESIGN.md section 4,
+// the same factors as every other variant), the tile spikes, the separator's rows and the tile's
+// contribution to the reduced system.  Every chain -- the pivots from the top, the pivots from the
+// bottom, the products that make the spikes -- is carried in double-double and every stored number is
+// rounded ONCE: a theta step applies these numbers ten thousand times, so a rounding error that a
+// chain has amplified is a systematic error of the run (dd.cuh).  In: p, b, q = lo, di, up of A.
+// Out: p = l, b = kappa, q = s, Vt, Wt; at the separator l = kappa = s = 0, Vt = 0 and Wt = -1, so
+// that the correction  x = z - Vt xs(k-1) - Wt xs(k)  ADDS the separator's own value there.
 __global__ void __launch_bounds__(128) spike_tile_factor_kernel(
     fvm_problem pr, double theta, int64_t tile_offset, int64_t n_tiles, int TPB, int CPT, double* __restrict__ p,
     double* __restrict__ q, double* __restrict__ b, double* __restrict__ Vt, double* __restrict__ Wt,
@@ -78,187 +88,202 @@ __global__ void __launch_bounds__(128) spike_tile_factor_kernel(
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t pi = blockIdx.y;
   if (k >= n_tiles) return;
-  const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
   const int T = TPB * CPT;
   const int64_t base = (pi * n_tiles + k) * T;
   const int64_t jg0 = (tile_offset + k) * T;               // global index of the tile's first cell
   auto at = [&](int r) { return base + tiled_pos(r, TPB, CPT); };
-  // beta[0] / beta[J-1]: only the tile that HOLDS the end cell may touch the end faces.  With the
-  // mesh split over ranks `faces` is the caller's pointer shifted by the slab offset, and a rank
-  // that does not own cell 0 (or J-1) has no memory behind faces[0..1] (faces[J-1..J]).
-  double beta_l = 0.0, beta_r = 0.0;
-  if (jg0 == 0 && pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
-    beta_l = dvd(pr.left_flux[pi], sub(pr.faces[1], pr.faces[0]));
-  if (pr.J - 1 >= jg0 && pr.J - 1 < jg0 + T && pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
-    beta_r = dvd(-pr.right_flux[pi], sub(pr.faces[pr.J], pr.faces[pr.J - 1]));
   const int N = T - 1;                                     // interior cells
-  double q_prev = 0.0, gv = 0.0;
+  // theta * beta of the two end cells of the mesh, added to the state before the forward sweep.  Only
+  // the tile that HOLDS the end cell may touch the end faces: with the mesh split over ranks `faces` is
+  // the caller's pointer shifted by the slab offset, and a rank that does not own cell 0 (or J-1) has
+  // no memory behind faces[0..1] (faces[J-1..J]).
+  if (jg0 == 0 && pr.left_kind == FVM_BC_ROBIN && pr.left_flux)
+    bends[2 * pi] = mul(theta, dvd(pr.left_flux[pi], sub(pr.faces[1], pr.faces[0])));
+  if (pr.J - 1 >= jg0 && pr.J - 1 < jg0 + T && pr.right_kind == FVM_BC_ROBIN && pr.right_flux)
+    bends[2 * pi + 1] = mul(theta, dvd(-pr.right_flux[pi], sub(pr.faces[pr.J], pr.faces[pr.J - 1])));
+  const int64_t oN = at(N);
+  const double loN = p[oN], diN = b[oN], upN = q[oN];
+  // pass 1, bottom-up: pivots of the UL factorisation, pv_c = di_c - up_c lo_{c+1} / pv_{c+1}; the left
+  // spike V = T^-1 (lo_0 e_0) is then a running product of m_c = lo_c / pv_c.  m is parked in Vt (hi), Wt (lo).
+  {
+    dd m = dd_make(0.0);
+    for (int c = N - 1; c >= 0; --c) {
+      const int64_t o = at(c);
+      const dd pv = dd_sub(dd_make(b[o]), dd_mul_d(m, q[o]));
+      m = dd_div(dd_make(p[o]), pv);
+      Vt[o] = m.hi; Wt[o] = m.lo;
+    }
+  }
+  // pass 2, top-down: pivots of the LU factorisation, the stored factors, and V_c = -m_c V_{c-1}.
+  // s_c is needed once more in double-double (pass 3): its low part is parked in Wt.
+  const dd dth = dd_make(theta);
+  dd sprev = dd_make(0.0), rprev = dd_make(0.0), V = dd_make(0.0), Vlast = dd_make(0.0);
+  double V0 = 0.0;
+  int eL = 0, eR = 1;
   for (int c = 0; c < N; ++c) {
     const int64_t o = at(c);
     const double lo = p[o], di = b[o], up = q[o];
-    const double inv = 1.0 / (di - lo * q_prev);
-    const double pc = lo * inv;
-    q_prev = up * inv;
-    gv = (c == 0) ? pc : -pc * gv;                         // forward sweep of the left spike
-    p[o] = pc; q[o] = q_prev; b[o] = inv * (rth - cth * di);
-    Vt[o] = gv;
-    if (jg0 + c == 0) bends[2 * pi] = beta_l * inv;        // beta[0] as it enters the sweep
-    if (jg0 + c == pr.J - 1) bends[2 * pi + 1] = beta_r * inv;   // beta[J-1] when cell J-1 is a tile-interior cell
+    const dd piv = dd_sub(dd_make(di), dd_mul_d(sprev, lo));
+    const dd l = dd_mul_d(rprev, lo);                      // c = 0: couples to the previous separator -> spike
+    rprev = dd_recip(piv);
+    sprev = dd_mul_d(rprev, up);
+    const dd m = dd_make(Vt[o], Wt[o]);
+    V = (c == 0) ? m : dd_neg(dd_mul(m, V));
+    const double Vr = dd_round(V);
+    if (c == 0) V0 = Vr;
+    if (fabs(Vr) > spike_tol) eL = c + 1;                  // cells [0, eL) need the left correction
+    p[o] = (c == 0) ? 0.0 : dd_round(l);
+    b[o] = dd_round(dd_div(rprev, dth));
+    q[o] = sprev.hi;
+    Vt[o] = Vr; Wt[o] = sprev.lo;
   }
+  Vlast = V;
+  // pass 3, bottom-up: right spike W = T^-1 (up_{N-1} e_{N-1}): W_{N-1} = s_{N-1}, W_c = -s_c W_{c+1}
+  dd Wd = dd_make(0.0), Wlast = dd_make(0.0);
+  for (int c = N - 1; c >= 0; --c) {
+    const int64_t o = at(c);
+    const dd sc = dd_make(q[o], Wt[o]);
+    Wd = (c == N - 1) ? sc : dd_neg(dd_mul(sc, Wd));
+    if (c == N - 1) Wlast = Wd;
+    const double Wr = dd_round(Wd);
+    if (fabs(Wr) > spike_tol) eR = N - c;                  // cells [N-eR, N) need the right correction
+    Wt[o] = Wr;
+  }
+  q[at(N - 1)] = 0.0;                                      // s_{N-1} couples to the separator -> spike, not sweep
+  p[oN] = 0.0; q[oN] = 0.0; b[oN] = 0.0; Vt[oN] = 0.0; Wt[oN] = -1.0;
   double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
-  {
-    const int64_t oN = at(N);
-    const double lo = p[oN], di = b[oN], up = q[oN];
-    s[SEP_LO] = lo; s[SEP_UP] = up;
-    s[SEP_BLO] = -cth * lo; s[SEP_BDI] = rth - cth * di; s[SEP_BUP] = -cth * up;
-    double bs = 0.0;
-    if (jg0 + N == 0) bs += beta_l;
-    if (jg0 + N == pr.J - 1) bs += beta_r;
-    s[SEP_BETA] = bs;
-    p[oN] = 0.0; q[oN] = 0.0; b[oN] = 0.0;                 // separator: not part of the tile solve
-    Vt[oN] = 0.0; Wt[oN] = 0.0;
-    // backward sweeps of both spikes
-    double vn = Vt[at(N - 1)], un = q[at(N - 1)];
-    Wt[at(N - 1)] = un;
-    const double vlast = vn, ulast = un;
-    int eL = (fabs(vn) > spike_tol) ? N : 0, eR = 1;
-    for (int c = N - 2; c >= 0; --c) {
-      const int64_t o = at(c);
-      const double qc = q[o];
-      vn = Vt[o] - qc * vn;
-      un = -qc * un;
-      Vt[o] = vn; Wt[o] = un;
-      if (fabs(vn) > spike_tol && c + 1 > eL) eL = c + 1;  // cells [0, eL) need the left correction
-      if (fabs(un) > spike_tol) eR = N - c;                // cells [N-eR, N) need the right correction
-    }
-    s[SEP_RL] = -lo * vlast;
-    s[SEP_RDA] = di - lo * ulast;                          // the -up*V0(k+1) term is added by the host
-    s[SEP_V0] = vn; s[SEP_W0] = un;
-    atomicMax(&extents[0], eL);
-    atomicMax(&extents[1], eR);
-  }
+  s[SEP_LO] = loN; s[SEP_UP] = upN;
+  s[SEP_RL] = -dd_round(dd_mul_d(Vlast, loN));
+  s[SEP_RDA] = dd_round(dd_sub(dd_make(diN), dd_mul_d(Wlast, loN)));   // the -up*V0(k+1) term is added by the host
+  s[SEP_V0] = V0; s[SEP_W0] = dd_round(Wd);
+  atomicMax(&extents[0], eL);
+  atomicMax(&extents[1], eR);
 }
 
-// Thomas factorisation of the reduced tridiagonal (one thread per problem; n = global tiles).
+// Thomas factorisation of the reduced tridiagonal (one thread per problem; n = global tiles): pivot
+// chain in double-double, stored factors rounded once.
 __global__ void reduced_factor_kernel(int64_t n, int64_t P, const double* __restrict__ RL,
                                       const double* __restrict__ RD, const double* __restrict__ RU,
                                       double* __restrict__ rp, double* __restrict__ rq, double* __restrict__ rinv) {
   const int64_t pi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (pi >= P) return;
-  double q_prev = 0.0;
+  dd q_prev = dd_make(0.0);
   for (int64_t k = 0; k < n; ++k) {
     const int64_t o = pi * n + k;
-    const double inv = 1.0 / (RD[o] - RL[o] * q_prev);
-    rp[o] = RL[o] * inv;
-    q_prev = RU[o] * inv;
-    rq[o] = q_prev;
-    rinv[o] = inv;
+    const dd inv = dd_recip(dd_sub(dd_make(RD[o]), dd_mul_d(q_prev, RL[o])));
+    rp[o] = dd_round(dd_mul_d(inv, RL[o]));
+    q_prev = dd_mul_d(inv, RU[o]);
+    rq[o] = q_prev.hi;
+    rinv[o] = inv.hi;
   }
 }
 
 // ------------------------------------------------------------------------------------------ per step
-// LAZY correction: w_in holds the previous step's UNCORRECTED tile solutions g (true values only at
-// the separators and in the ghosts); the correction x = g - Vt xs(k-1) - Wt xs(k) is applied while
-// the tile is loaded, by the threads whose cells lie inside the spike extents (the first tl and the
-// last tr threads of the CTA).  This replaces correct_kernel's separate read-modify-write pass:
-// Vt, Wt are still read (16 B per corrected cell) but g is not re-read and x is never written.
+// One theta step without a right-hand side: with B = I/theta - cA, c = (1-theta)/theta,
+//   w' = A^-1 (w/theta + beta) - c w,
+// and per tile, with the un-normalised factors:  h_c = w_c + theta beta_c - l_c h_{c-1}  (forwards),
+// g_c = h_c kappa_c - s_c g_{c+1}  (backwards),  z_c = g_c - c w_c.  z is what the kernel writes: the
+// new state up to the spike correction  w' = z - Vt ys(k-1) - Wt ys(k), where ys are the separators'
+// values of y = A^-1(...), the solution of the reduced system.  No neighbour of a cell enters, so a
+// tile needs nothing from the tiles next to it.
+//
+// LAZY correction: w_in holds the previous step's UNCORRECTED z; the correction is applied while the
+// tile is loaded, by the threads whose cells lie inside the spike extents (the first tl and the last
+// tr >= 1 threads of the CTA; the separator is the last cell of the last thread, its Wt is -1).  This
+// replaces correct_kernel's separate read-modify-write pass: Vt, Wt are still read (16 B per corrected
+// cell) but z is not re-read and the corrected state is never written.
 struct LazyCorrection {
   const double* Vt; const double* Wt; const double* xs;   // xs indexed by tile_offset + k, per problem n_tiles_global
   int64_t tile_offset, n_tiles_global;
   int tl, tr;
 };
 
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+               : "memory");
+}
+
+// MODE 0: general theta, 1: theta = 1/2 (c = 1), 2: theta = 1 (c = 0).  Dynamic shared memory: s of the
+// tile (T doubles, filled by cp.async so that it never occupies registers across the forward scan) and,
+// unless c = 0, the loaded state (T doubles); every thread reads back only what it parked itself.
 template <int TPB, int CPT, int MODE, bool LAZY>
 __global__ void __launch_bounds__(TPB, (TPB == 256 ? 2 : 1)) tile_solve_kernel(
-    int64_t n_tiles, const double* __restrict__ p, const double* __restrict__ q,
-    const double* __restrict__ b, const double* __restrict__ sep, const double* __restrict__ bends,
-    int has_first_cell, int64_t jl_last, double cth, const double* __restrict__ w_in,
+    int64_t n_tiles, const double* __restrict__ fl, const double* __restrict__ fs,
+    const double* __restrict__ fk, const double* __restrict__ sep, const double* __restrict__ bends,
+    int has_first_cell, int64_t jl_last, double rth, double cth, const double* __restrict__ w_in,
     double* __restrict__ w_out, double* __restrict__ rs, int64_t w_stride, LazyCorrection lz) {
   constexpr int T = TPB * CPT;
+  extern __shared__ double park[];                         // [0, T): s; [T, 2T): w
   __shared__ double sm[66];
-  __shared__ double sedge[LAZY ? 2 * TPB : 1];
   const int64_t k = blockIdx.x, pi = blockIdx.y;
   const int tid = threadIdx.x;
-  const int64_t base = (pi * n_tiles + k) * T + tid;                 // into p, q, b (tiled: + c*TPB)
-  const int64_t wbase = pi * w_stride + k * T;                       // tile's first position in w (ghosted)
-  double w[CPT + 2], pc[CPT], qc[CPT], g[CPT];
+  const int64_t base = (pi * n_tiles + k) * T + tid;                 // into the factors (tiled: + c*TPB)
+  const int64_t wbase = pi * w_stride + k * T + tid;                 // into the state
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) cp_async8(park + c * TPB + tid, fs + base + c * TPB);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  double h[CPT], lc[CPT], kc[CPT];
 #pragma unroll
   for (int c = 0; c < CPT; ++c) {
-    pc[c] = p[base + c * TPB]; qc[c] = q[base + c * TPB]; g[c] = b[base + c * TPB];
-    w[c + 1] = w_in[wbase + c * TPB + tid];
+    h[c] = w_in[wbase + c * TPB]; lc[c] = fl[base + c * TPB]; kc[c] = fk[base + c * TPB];
   }
-  if (!LAZY) {
-    // left neighbour of this thread's first cell = last cell of thread tid-1 (or the position just
-    // before the tile: previous tile's separator / the left ghost); right neighbour likewise
-    w[0] = w_in[tid == 0 ? wbase - 1 : wbase + (CPT - 1) * TPB + tid - 1];
-    w[CPT + 1] = w_in[tid == TPB - 1 ? wbase + T : wbase + tid + 1];
-  } else {
-    const int64_t kg = lz.tile_offset + k;
-    const double* X_ = lz.xs + pi * lz.n_tiles_global;
-    const double xk = X_[kg];
-    const double xl = kg > 0 ? X_[kg - 1] : 0.0;
-    if (tid < lz.tl || tid >= TPB - lz.tr) {               // (the separator's Vt, Wt are 0: it stays xs)
+  if (LAZY) {
+    if (tid < lz.tl || tid >= TPB - lz.tr) {
+      const int64_t kg = lz.tile_offset + k;
+      const double* X_ = lz.xs + pi * lz.n_tiles_global;
+      const double xk = X_[kg];
+      const double xl = kg > 0 ? X_[kg - 1] : 0.0;
 #pragma unroll
       for (int c = 0; c < CPT; ++c)
-        w[c + 1] = fma(-lz.Wt[base + c * TPB], xk, fma(-lz.Vt[base + c * TPB], xl, w[c + 1]));
-    }
-    sedge[tid] = w[1];
-    sedge[TPB + tid] = w[CPT];
-    __syncthreads();
-    w[0] = tid == 0 ? w_in[wbase - 1] : sedge[TPB + tid - 1];   // before the tile: a separator or the ghost, both true
-    if (tid < TPB - 1) {
-      w[CPT + 1] = sedge[tid + 1];
-    } else if (k + 1 < n_tiles) {                          // next tile's first cell, corrected with ITS separators
-      const int64_t on = (pi * n_tiles + k + 1) * T;
-      w[CPT + 1] = fma(-lz.Wt[on], X_[kg + 1], fma(-lz.Vt[on], xk, w_in[wbase + T]));
-    } else {
-      w[CPT + 1] = w_in[wbase + T];                        // right ghost: already a true value
+        h[c] = fma(-lz.Wt[base + c * TPB], xk, fma(-lz.Vt[base + c * TPB], xl, h[c]));
     }
   }
+  if (MODE != 2) {
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) {
-    if (MODE == 2) {
-      g[c] = g[c] * w[c + 1];
-    } else {
-      const double t = fma(qc[c], w[c + 2], pc[c] * w[c]);
-      g[c] = (MODE == 1) ? fma(g[c], w[c + 1], -t) : fma(-cth, t, g[c] * w[c + 1]);
-    }
+    for (int c = 0; c < CPT; ++c) park[T + c * TPB + tid] = h[c];
   }
-  if (has_first_cell && k == 0 && threadIdx.x == 0) g[0] += bends[2 * pi];
-  {                                                        // beta[J-1] at a tile-interior cell (rare)
+  if (has_first_cell && k == 0 && tid == 0) h[0] += bends[2 * pi];
+  {                                                        // theta*beta[J-1] (its cell is wherever the mesh ends)
     const int64_t l0 = k * T + (int64_t)tid * CPT;
     if (jl_last >= l0 && jl_last < l0 + CPT) {
       const int cl = (int)(jl_last - l0);
 #pragma unroll
-      for (int c = 0; c < CPT; ++c) if (c == cl) g[c] += bends[2 * pi + 1];
+      for (int c = 0; c < CPT; ++c) if (c == cl) h[c] += bends[2 * pi + 1];
     }
   }
-  if (threadIdx.x == TPB - 1) {                            // the separator's right-hand side
-    const double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
-    rs[pi * n_tiles + k] = fma(s[SEP_BUP], w[CPT + 1], fma(s[SEP_BDI], w[CPT], fma(s[SEP_BLO], w[CPT - 1], s[SEP_BETA])));
-  }
-  cta_forward<TPB, CPT>(g, [&](int c) { return pc[c]; }, sm, 0.0, nullptr);
-  cta_backward<TPB, CPT>(g, [&](int c) { return qc[c]; }, sm, 0.0, nullptr);
+  cta_forward<TPB, CPT>(h, [&](int c) { return lc[c]; }, sm, 0.0, nullptr);
+  const double h_sep = h[CPT - 1];                         // last thread: w_s + theta*beta_s (l = 0 there)
 #pragma unroll
-  for (int c = 0; c < CPT; ++c) w_out[wbase + c * TPB + tid] = g[c];
+  for (int c = 0; c < CPT; ++c) h[c] *= kc[c];
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  cta_backward<TPB, CPT>(h, [&](int c) { return park[c * TPB + tid]; }, sm, 0.0, nullptr);
+  // what the reduced system needs of this tile: the separator row's right-hand side less its coupling
+  // to the tile's last interior cell, and the tile's first value (coupled to the previous separator)
+  double* r2 = rs + 2 * (pi * n_tiles + k);
+  if (tid == TPB - 1) r2[0] = fma(-sep[(pi * n_tiles + k) * SEP_STRIDE + SEP_LO], h[CPT - 2], h_sep * rth);
+  if (tid == 0) r2[1] = h[0];
+#pragma unroll
+  for (int c = 0; c < CPT; ++c) {
+    double z = h[c];
+    if (MODE == 1) z = h[c] - park[T + c * TPB + tid];
+    if (MODE == 0) z = fma(-cth, park[T + c * TPB + tid], h[c]);
+    w_out[wbase + c * TPB] = z;
+  }
 }
 
-// rr_k = rs_k - lo_k g_last(k) - up_k g_first(k+1); the last local tile leaves the g_first term
-// to whoever knows the next rank's first cell (g_first_out[pi] = this rank's own first value).
-__global__ void __launch_bounds__(256) reduced_rhs_kernel(int64_t n_tiles, int TPB, int CPT, const double* __restrict__ sep,
-                                                          const double* __restrict__ rs, const double* __restrict__ g,
-                                                          int64_t w_stride, double* __restrict__ rr,
+// rr_k = rs_k - up_k g_first(k+1); the last local tile leaves that term to whoever knows the next
+// rank's first value (g_first_out[pi] = this rank's own first value).
+__global__ void __launch_bounds__(256) reduced_rhs_kernel(int64_t n_tiles, const double* __restrict__ sep,
+                                                          const double* __restrict__ rs, double* __restrict__ rr,
                                                           int64_t rr_stride, double* __restrict__ g_first_out) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t pi = blockIdx.y;
   if (k >= n_tiles) return;
-  const int T = TPB * CPT;
-  const double* s = sep + (pi * n_tiles + k) * SEP_STRIDE;
-  const double* gp = g + pi * w_stride + k * T;
-  double r = fma(-s[SEP_LO], gp[tiled_pos(T - 2, TPB, CPT)], rs[pi * n_tiles + k]);
-  if (k + 1 < n_tiles) r = fma(-s[SEP_UP], gp[T], r);
+  const double* r2 = rs + 2 * (pi * n_tiles + k);
+  double r = r2[0];
+  if (k + 1 < n_tiles) r = fma(-sep[(pi * n_tiles + k) * SEP_STRIDE + SEP_UP], r2[3], r);
   rr[pi * rr_stride + k] = r;
-  if (k == 0) g_first_out[pi] = gp[0];
+  if (k == 0) g_first_out[pi] = r2[1];
 }
 
 // Thomas solve of the factored reduced system by ONE CTA per problem, in chunks of TPB*CPT
@@ -316,17 +341,17 @@ __global__ void __launch_bounds__(TPB) reduced_solve_kernel(int64_t n, const dou
   }
 }
 
-// x = g - Vt*xs(k-1) - Wt*xs(k) over the spike extents, x_sep = xs(k); also refreshes the two
-// ghost cells of the local state.  xs is indexed GLOBALLY (tile_offset + k).  The extents are
-// rounded up to whole threads' chunks: tl threads from the left edge, tr from the right; items
-// are enumerated in tiled order so that the accesses coalesce.
+// w = z - Vt*xs(k-1) - Wt*xs(k) over the spike extents (the separator is the last cell of the right
+// extent: Vt = 0, Wt = -1 there).  xs is indexed GLOBALLY (tile_offset + k).  The extents are rounded up
+// to whole threads' chunks: tl threads from the left edge, tr >= 1 from the right; items are enumerated
+// in tiled order so that the accesses coalesce.  NOT idempotent: once per step.
 __global__ void __launch_bounds__(256) correct_kernel(int64_t n_tiles, int TPB, int CPT, int tl, int tr,
                                                       int64_t tile_offset, int64_t n_tiles_global,
                                                       const double* __restrict__ Vt, const double* __restrict__ Wt,
                                                       const double* __restrict__ xs, double* __restrict__ w,
-                                                      int64_t w_stride, const double* __restrict__ next_first) {
+                                                      int64_t w_stride) {
   const int T = TPB * CPT;
-  const int per_tile = (tl + tr) * CPT + 1;
+  const int per_tile = (tl + tr) * CPT;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t pi = blockIdx.y;
   if (idx >= n_tiles * per_tile) return;
@@ -337,16 +362,9 @@ __global__ void __launch_bounds__(256) correct_kernel(int64_t n_tiles, int TPB, 
   const double xk = X_[kg];
   const double xl = (kg > 0) ? X_[kg - 1] : 0.0;
   double* wp = w + pi * w_stride + k * T;
-  if (m == (tl + tr) * CPT) {                              // the separator itself, and the ghosts
-    wp[T - 1] = xk;
-    if (k == 0) wp[-1] = xl;                               // left ghost = previous rank's last separator
-    if (k == n_tiles - 1) wp[T] = next_first ? next_first[pi] : 0.0;   // right ghost = next rank's first cell
-    return;
-  }
   int t, c;
   if (m < tl * CPT) { c = m / tl; t = m % tl; }
   else { const int m2 = m - tl * CPT; c = m2 / tr; t = TPB - tr + m2 % tr; }
-  if (t == TPB - 1 && c == CPT - 1) return;                // the separator is written above
   const int pos = c * TPB + t;
   const int64_t o = (pi * n_tiles + k) * T + pos;
   wp[pos] = fma(-Wt[o], xk, fma(-Vt[o], xl, wp[pos]));
@@ -406,36 +424,37 @@ extern "C" int fvm_spike_reduced_factor(int64_t n, int64_t P, const double* RL, 
   return (int)cudaGetLastError();
 }
 
+template <int TPB, int CPT, int MODE, bool LAZY>
+static int launch_tile_solve_inst(dim3 grid, cudaStream_t s, int64_t n_tiles, const double* p, const double* q,
+                                  const double* b, const double* sep, const double* bends, int has_first,
+                                  int64_t jl_last, double theta, const double* w_in, double* w_out, double* rs,
+                                  int64_t w_stride, const fvm::LazyCorrection& lz) {
+  auto kern = fvm::tile_solve_kernel<TPB, CPT, MODE, LAZY>;
+  const size_t smem = (size_t)TPB * CPT * sizeof(double) * (MODE == 2 ? 1 : 2);
+  if (smem > 48 * 1024) {                                  // per call, not cached: valid on whichever device is current
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+  }
+  kern<<<grid, TPB, smem, s>>>(n_tiles, p, q, b, sep, bends, has_first, jl_last, 1.0 / theta, (1.0 - theta) / theta,
+                               w_in, w_out, rs, w_stride, lz);
+  return (int)cudaGetLastError();
+}
+
 template <int TPB, int CPT>
 static int launch_tile_solve(int64_t n_tiles, int64_t P, const double* p, const double* q, const double* b,
                              const double* sep, const double* bfirst, int has_first, int64_t jl_last, double theta,
                              const double* w_in, double* w_out, double* rs, int64_t w_stride, cudaStream_t s,
                              const fvm::LazyCorrection* lazy = nullptr) {
   dim3 grid((unsigned)n_tiles, (unsigned)P);
-  const double cth = (1.0 - theta) / theta;
-  if (lazy) {
-    if (theta == 0.5)
-      fvm::tile_solve_kernel<TPB, CPT, 1, true><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
-                                                                   cth, w_in, w_out, rs, w_stride, *lazy);
-    else if (theta == 1.0)
-      fvm::tile_solve_kernel<TPB, CPT, 2, true><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
-                                                                   cth, w_in, w_out, rs, w_stride, *lazy);
-    else
-      fvm::tile_solve_kernel<TPB, CPT, 0, true><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
-                                                                   cth, w_in, w_out, rs, w_stride, *lazy);
-    return (int)cudaGetLastError();
-  }
   const fvm::LazyCorrection none = {nullptr, nullptr, nullptr, 0, 0, 0, 0};
-  if (theta == 0.5)
-    fvm::tile_solve_kernel<TPB, CPT, 1, false><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
-                                                                   cth, w_in, w_out, rs, w_stride, none);
-  else if (theta == 1.0)
-    fvm::tile_solve_kernel<TPB, CPT, 2, false><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
-                                                                   cth, w_in, w_out, rs, w_stride, none);
-  else
-    fvm::tile_solve_kernel<TPB, CPT, 0, false><<<grid, TPB, 0, s>>>(n_tiles, p, q, b, sep, bfirst, has_first, jl_last,
-                                                                   cth, w_in, w_out, rs, w_stride, none);
-  return (int)cudaGetLastError();
+#define FVM_TILE_INST(MODE, LAZY, LZ)                                                                          \
+  launch_tile_solve_inst<TPB, CPT, MODE, LAZY>(grid, s, n_tiles, p, q, b, sep, bfirst, has_first, jl_last, theta, w_in, \
+                                               w_out, rs, w_stride, LZ)
+  if (lazy) return theta == 0.5 ? FVM_TILE_INST(1, true, *lazy) : theta == 1.0 ? FVM_TILE_INST(2, true, *lazy)
+                                                                               : FVM_TILE_INST(0, true, *lazy);
+  return theta == 0.5 ? FVM_TILE_INST(1, false, none) : theta == 1.0 ? FVM_TILE_INST(2, false, none)
+                                                                     : FVM_TILE_INST(0, false, none);
+#undef FVM_TILE_INST
 }
 
 extern "C" int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
@@ -455,8 +474,7 @@ extern "C" int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const
                                             w_in, w_out, rs, w_stride, s);
   if (st) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
-  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,
-                                            rr, rr_stride, g_first);
+  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, sep, rs, rr, rr_stride, g_first);
   return (int)cudaGetLastError();
 }
 
@@ -471,39 +489,39 @@ extern "C" int fvm_spike_reduce_solve(int64_t n_global, int64_t P, const double*
   return (int)cudaGetLastError();
 }
 
+// whole threads' chunks of the spike extents: tl threads from the left edge, tr >= 1 from the right
+// (the separator is the last cell of the last thread); the two ranges never overlap
+static void extent_threads(int config, const int32_t* extents_host, int& tl, int& tr) {
+  const int T = tile_cells(config), TPB = tile_threads(config), CPT = tile_cpt(config);
+  tl = (extents_host[0] + CPT - 1) / CPT;
+  tr = TPB - (T - 1 - extents_host[1]) / CPT;
+  if (tr < 1) tr = 1;
+  if (tr > TPB) tr = TPB;
+  if (tl > TPB - tr) tl = TPB - tr;
+}
+
 extern "C" int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, const int32_t* extents_host,
                                   int64_t tile_offset, int64_t n_tiles_global, const double* Vt, const double* Wt,
-                                  const double* xs, double* w, int64_t w_stride, const double* next_first,
-                                  void* stream) {
+                                  const double* xs, double* w, int64_t w_stride, void* stream) {
   if (!extents_host || !Vt || !Wt || !xs || !w || n_tiles < 1 || P < 1 || P > 65535) return FVM_ERR_INVALID_ARG;
   if (config < 0 || config >= kTileCfgs) return FVM_ERR_INVALID_ARG;
   const int T = tile_cells(config), TPB = tile_threads(config), CPT = tile_cpt(config);
-  const int eL = extents_host[0], eR = extents_host[1];
-  if (eL < 0 || eR < 0 || eL > T - 1 || eR > T - 1) return FVM_ERR_INVALID_ARG;
-  int tl = (eL + CPT - 1) / CPT;                           // whole threads' chunks from the left edge
-  int tr = TPB - (T - 1 - eR) / CPT;                       // ... and from the right edge
-  if (tl > TPB) tl = TPB;
-  if (tr > TPB - tl) tr = TPB - tl;                        // the two ranges never overlap
-  const int64_t total = n_tiles * (int64_t)((tl + tr) * CPT + 1);
+  if (extents_host[0] < 0 || extents_host[1] < 0 || extents_host[0] > T - 1 || extents_host[1] > T - 1)
+    return FVM_ERR_INVALID_ARG;
+  int tl, tr;
+  extent_threads(config, extents_host, tl, tr);
+  const int64_t total = n_tiles * (int64_t)((tl + tr) * CPT);
   dim3 g((unsigned)((total + 255) / 256), (unsigned)P);
   fvm::correct_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(n_tiles, TPB, CPT, tl, tr, tile_offset, n_tiles_global, Vt,
-                                                          Wt, xs, w, w_stride, next_first);
+                                                          Wt, xs, w, w_stride);
   return (int)cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------
-// Lazy correction: fvm_spike_local_lazy + fvm_spike_separators replace fvm_spike_local +
-// fvm_spike_finalize in a time loop.  The state buffer then holds the uncorrected tile solutions
-// between steps (true values at the separators and ghosts); fvm_spike_finalize materialises the true
-// state when it is needed (output, checkpoints).
-static void extent_threads(int config, const int32_t* extents_host, int& tl, int& tr) {
-  const int T = tile_cells(config), TPB = tile_threads(config), CPT = tile_cpt(config);
-  tl = (extents_host[0] + CPT - 1) / CPT;                  // whole threads' chunks from the left edge
-  tr = TPB - (T - 1 - extents_host[1]) / CPT;              // ... and from the right edge
-  if (tl > TPB) tl = TPB;
-  if (tr > TPB - tl) tr = TPB - tl;                        // the two ranges never overlap
-}
-
+// Lazy correction: fvm_spike_local_lazy replaces fvm_spike_local + fvm_spike_finalize in a time loop.
+// The state buffer then holds the uncorrected z between steps and the separator values of the step
+// that produced it stay in `xs`; fvm_spike_finalize materialises the true state when it is needed
+// (output, checkpoints).
 extern "C" int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
                                     const double* b, const double* sep, const double* bends,
                                     int32_t has_first_cell, int64_t last_cell_local, double theta,
@@ -531,28 +549,15 @@ extern "C" int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, 
                                             w_in, w_out, rs, w_stride, s, &lz);
   if (st) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
-  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,
-                                            rr, rr_stride, g_first);
-  return (int)cudaGetLastError();
-}
-
-extern "C" int fvm_spike_separators(int64_t n_tiles, int64_t P, int32_t config, int64_t tile_offset,
-                                    int64_t n_tiles_global, const double* xs, double* w, int64_t w_stride,
-                                    const double* next_first, void* stream) {
-  if (!xs || !w || n_tiles < 1 || P < 1 || P > 65535) return FVM_ERR_INVALID_ARG;
-  if (config < 0 || config >= kTileCfgs) return FVM_ERR_INVALID_ARG;
-  dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
-  fvm::correct_kernel<<<g, 256, 0, (cudaStream_t)stream>>>(n_tiles, tile_threads(config), tile_cpt(config), 0, 0,
-                                                          tile_offset, n_tiles_global, nullptr, nullptr, xs, w, w_stride,
-                                                          next_first);
+  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, sep, rs, rr, rr_stride, g_first);
   return (int)cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------
 // fvm_spike_local_static: fvm_spike_local for callers that cannot provide the `rs` work array.
 //
-// Between its two kernels fvm_spike_local parks the separators' right-hand sides in `rs`, an
-// array the caller must allocate.  A time loop that lives inside a larger application often
+// Between its two kernels fvm_spike_local parks two numbers per tile (the separator's right-hand
+// side and the tile's first value) in `rs`, an array the caller must allocate.  A time loop that lives inside a larger application often
 // cannot do that: the application may have handed every byte of device memory to its own pool
 // when it started, or the step may sit in a latency-critical section where cudaMalloc is not
 // acceptable because it synchronises the whole device.  For such callers the scratch lives in
@@ -560,8 +565,8 @@ extern "C" int fvm_spike_separators(int64_t n_tiles, int64_t P, int32_t config, 
 // libfvm_b200.so carries these 512 KiB until the process exits, and a call needs
 // P * n_tiles <= FVM_SPIKE_STATIC_MAX_TILES.
 namespace {
-constexpr int64_t kStaticMaxTiles = 65536;
-static __device__ __align__(256) double g_spike_rs_scratch[kStaticMaxTiles];
+constexpr int64_t kStaticMaxTiles = 32768;
+static __device__ __align__(256) double g_spike_rs_scratch[2 * kStaticMaxTiles];
 
 // The array's name is only a handle in host code; the address a kernel can use has to be asked
 // for while the device that will run the kernel is current.  It is asked for on EVERY call and
@@ -594,7 +599,7 @@ extern "C" int fvm_spike_local_static(int64_t n_tiles, int64_t P, int32_t config
   int st = static_scratch(&rs);
   if (st) return st;
   // Nothing in the scratch has to start at zero: the first kernel writes every entry
-  // [0, P*n_tiles) before the second one reads it; what earlier calls left behind is overwritten.
+  // [0, 2*P*n_tiles) before the second one reads it; what earlier calls left behind is overwritten.
   cudaStream_t s = (cudaStream_t)stream;
   st = config == 0 ? launch_tile_solve<512, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
                                         w_out, rs, w_stride, s)
@@ -604,8 +609,7 @@ extern "C" int fvm_spike_local_static(int64_t n_tiles, int64_t P, int32_t config
                                         w_out, rs, w_stride, s);
   if (st) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
-  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, tile_threads(config), tile_cpt(config), sep, rs, w_out, w_stride,
-                                            rr, rr_stride, g_first);
+  fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, sep, rs, rr, rr_stride, g_first);
   return (int)cudaGetLastError();
 }
 
@@ -627,21 +631,19 @@ __global__ void rank_pack_kernel(int64_t P, int64_t nt, const double* __restrict
 }
 
 // After the gather (allp[rank][problem][4]): right-hand side and solution of the `world`-unknown
-// top system (dense inverse), this rank's separator values xs_ext[1..nt] with the previous rank's
-// separator in xs_ext[0], and the new value of the next rank's first cell (this rank's right ghost).
-// cst[problem][7][world]: sup of every rank's last tile, the separator rows' couplings (lo, up), the
-// rank spikes at every rank's first tile (vf, wf) and the tile spikes (V0, W0) of every rank's first tile.
+// top system (dense inverse), and this rank's separator values xs_ext[1..nt] with the previous rank's
+// separator in xs_ext[0].
+// cst[problem][3][world]: sup of every rank's last tile and the separator rows' couplings (lo, up).
 __global__ void __launch_bounds__(256) rank_top_kernel(int64_t P, int64_t nt, int world, int rank,
                                                        const double* __restrict__ allp,
                                                        const double* __restrict__ top_inv,
                                                        const double* __restrict__ cst,
                                                        const double* __restrict__ gr, const double* __restrict__ Vr,
-                                                       const double* __restrict__ Wr, double* __restrict__ xs_ext,
-                                                       double* __restrict__ next_first) {
+                                                       const double* __restrict__ Wr, double* __restrict__ xs_ext) {
   __shared__ double rhs[64], X[64];
   const int64_t pi = blockIdx.x;
   const int t = threadIdx.x;
-  const double* c = cst + pi * 7 * world;
+  const double* c = cst + pi * 3 * world;
   auto pk = [&](int r, int i) { return allp[((int64_t)r * P + pi) * 4 + i]; };
   if (t < world) {
     const bool has_next = t + 1 < world;
@@ -662,14 +664,7 @@ __global__ void __launch_bounds__(256) rank_top_kernel(int64_t P, int64_t nt, in
     const int64_t o = pi * nt + k;
     xe[1 + k] = (k == nt - 1) ? Xr : fma(-Wr[o], Xr, fma(-Vr[o], Xl, gr[o]));
   }
-  if (t == 0) {
-    xe[0] = Xl;
-    if (rank + 1 < world) {
-      const int n = rank + 1;
-      const double xs_n0 = fma(-c[4 * world + n], X[n], fma(-c[3 * world + n], Xr, pk(n, 0)));   // next rank's first separator
-      next_first[pi] = fma(-c[6 * world + n], xs_n0, fma(-c[5 * world + n], Xr, pk(n, 3)));
-    }
-  }
+  if (t == 0) xe[0] = Xl;
 }
 
 }  // namespace fvm
@@ -683,11 +678,11 @@ extern "C" int fvm_spike_rank_pack(int64_t P, int64_t nt, const double* gr, cons
 
 extern "C" int fvm_spike_rank_top(int64_t P, int64_t nt, int32_t world, int32_t rank, const double* allp,
                                   const double* top_inv, const double* cst, const double* gr, const double* Vr,
-                                  const double* Wr, double* xs_ext, double* next_first, void* stream) {
-  if (!allp || !top_inv || !cst || !gr || !Vr || !Wr || !xs_ext || !next_first) return FVM_ERR_INVALID_ARG;
+                                  const double* Wr, double* xs_ext, void* stream) {
+  if (!allp || !top_inv || !cst || !gr || !Vr || !Wr || !xs_ext) return FVM_ERR_INVALID_ARG;
   if (P < 1 || P > 0x7fffffffLL || nt < 2 || world < 2 || world > 64 || rank < 0 || rank >= world)
     return FVM_ERR_INVALID_ARG;
   fvm::rank_top_kernel<<<(unsigned)P, 256, 0, (cudaStream_t)stream>>>(P, nt, world, rank, allp, top_inv, cst, gr, Vr,
-                                                                     Wr, xs_ext, next_first);
+                                                                     Wr, xs_ext);
   return (int)cudaGetLastError();
 }

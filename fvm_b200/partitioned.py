@@ -1,9 +1,10 @@
 """Long systems: one huge mesh (or a batch of long ones) partitioned into tiles, optionally
 with the cells split in contiguous slabs over the ranks of a torch.distributed group
 (BASELINE.json cfg 4 and cfg 5).  Drives variant 3 of the C-ABI
-(fvm_spike_*): tile-local Thomas solves, a reduced tridiagonal over the tile separators that
-every rank solves redundantly after ONE all-gather per step, and a spike correction near
-the tile edges.
+(fvm_spike_*): tile-local Thomas solves, a reduced tridiagonal over the tile separators (itself
+partitioned over the ranks, ONE all-gather of 4 doubles per rank and step), and a spike correction
+near the tile edges.  A step has no right-hand side (w' = A^-1(w/theta + beta) - c w), so a tile
+needs nothing from its neighbours and the state carries no ghost cells.
 
 Semantics are those of the reference's loop (fvm_classes.py:373-377,408-411).
 """
@@ -16,7 +17,7 @@ import numpy as np
 from . import _lib
 from .batched import _alpha_ends, _bc_kinds
 
-SEP_LO, SEP_UP, SEP_BLO, SEP_BDI, SEP_BUP, SEP_BETA, SEP_RL, SEP_RDA, SEP_V0, SEP_W0, SEP_STRIDE = range(11)
+SEP_LO, SEP_UP, SEP_RL, SEP_RDA, SEP_V0, SEP_W0, SEP_STRIDE = range(7)
 
 
 def plan_partition(J, tile_cells, world):
@@ -269,12 +270,12 @@ class PartitionedAdvectionDiffusionModel(object):
         e = self.comm.all_reduce_max_int(ext.cpu().tolist())
         self.extents = (ctypes.c_int32 * 2)(min(e[0], T - 1), min(e[1], T - 1))
         # work arrays of a step
-        self.rs, self.rr, self.g_first = new(P, nt), new(P, nt), new(P)
+        self.rs, self.rr, self.g_first = new(P, nt, 2), new(P, nt), new(P)
         self.xs = new(P, self.nt_global)
-        self.w_stride = self.n_local + 2
+        self.w_stride = self.n_local
         self._wbuf = [torch.zeros((P, self.w_stride), dtype=torch.float64, device=dev) for _ in range(2)]
         jl = self.J - 1 - self.j0
-        self._last_local = jl if (self._has_rf and 0 <= jl < self.n_local and jl % T != T - 1) else -1
+        self._last_local = jl if (self._has_rf and 0 <= jl < self.n_local) else -1
         self._theta = theta
         self._ready = theta
 
@@ -332,16 +333,12 @@ class PartitionedAdvectionDiffusionModel(object):
         top = torch.diag_embed(TD) + torch.diag_embed(TL[:, 1:], offset=-1) + torch.diag_embed(TU[:, :-1], offset=1)
         self.top_inv = torch.linalg.inv(top).contiguous()                # (P, W, W)
         last = torch.arange(1, W + 1, device=dev) * nt - 1              # every rank's last (separator) tile
-        first = torch.arange(0, W, device=dev) * nt                      # every rank's first tile
-        # constants of fvm_spike_rank_top, (P, 7, W): up of the last tiles; lo, up of the rank separators'
-        # rows; rank spikes and tile spikes at the first tiles
-        self.top_cst = torch.stack([self.sup_all[:, last], sl_, su_, vf, wf, self.V0_all[:, first],
-                                    self.W0_all[:, first]], dim=1).contiguous()
+        # constants of fvm_spike_rank_top, (P, 3, W): up of the last tiles; lo, up of the rank separators' rows
+        self.top_cst = torch.stack([self.sup_all[:, last], sl_, su_], dim=1).contiguous()
         self.xs_ext = torch.zeros((P, nt + 1), dtype=torch.float64, device=dev)
         self.packet = torch.zeros((P, 4), dtype=torch.float64, device=dev)
         self._gr = torch.zeros((P, nt), dtype=torch.float64, device=dev)          # work arrays of a step: nothing is
         self._allp = torch.zeros((W, P, 4), dtype=torch.float64, device=dev)      # allocated inside the time loop
-        self.next_first = torch.zeros(P, dtype=torch.float64, device=dev)
 
     # ------------------------------------------------------------------ state
     def set_state(self, w):
@@ -359,21 +356,13 @@ class PartitionedAdvectionDiffusionModel(object):
         nat = torch.zeros((self.P, self.n_local), dtype=torch.float64, device=self.device)
         nat[:, :n_real] = w
         # natural -> tiled order inside every tile (include/fvm_b200.h: fvm_spike_tile_threads)
-        buf[:, 1:1 + self.n_local] = nat.view(self.P, self.nt, self.TPB, self.CPT).transpose(2, 3).reshape(self.P, -1)
-        edges = torch.stack([buf[:, 1], buf[:, self.n_local]], dim=1)          # first / last local cell
-        if self.comm.world > 1:
-            allv = self.comm.all_gather(edges)                                  # [world, P, 2]
-            r = self.comm.rank
-            if r > 0:
-                buf[:, 0] = allv[r - 1, :, 1]
-            if r < self.comm.world - 1:
-                buf[:, self.n_local + 1] = allv[r + 1, :, 0]
+        buf[:, :] = nat.view(self.P, self.nt, self.TPB, self.CPT).transpose(2, 3).reshape(self.P, -1)
         self._cur = 0
 
     def get_state(self):
         """This rank's cells, (P, j1-j0)."""
         self._materialise()
-        til = self._wbuf[self._cur][:, 1:1 + self.n_local].view(self.P, self.nt, self.CPT, self.TPB)
+        til = self._wbuf[self._cur].view(self.P, self.nt, self.CPT, self.TPB)
         return til.transpose(2, 3).reshape(self.P, -1)[:, :self.j1 - self.j0].contiguous()
 
     def _xs_index(self):
@@ -390,22 +379,17 @@ class PartitionedAdvectionDiffusionModel(object):
         xs, off, ng = self._xs_index()
         buf = self._wbuf[self._cur]
         with torch.cuda.device(self.device):
-            # the separators and ghosts are already in place: only the interior correction is left
             st = _lib.lib().fvm_spike_finalize(self.nt, self.P, self.config, self.extents, off, ng, _lib.ptr(self.Vt),
-                                               _lib.ptr(self.Wt), _lib.ptr(xs), ctypes.c_void_p(buf.data_ptr() + 8),
-                                               self.w_stride, _lib.ptr(self._ghost_right(buf)), _lib.stream_ptr())
+                                               _lib.ptr(self.Wt), _lib.ptr(xs), _lib.ptr(buf), self.w_stride,
+                                               _lib.stream_ptr())
         _lib.check(st, "fvm_spike_finalize")
         self._pending = False
 
-    def _ghost_right(self, buf):
-        """The right ghost as a (P,) tensor (fvm_spike_finalize rewrites it with what it is given)."""
-        return buf[:, self.n_local + 1].contiguous()
-
-    def _local(self, w_in, w_out, wptr):
+    def _local(self, w_in, w_out):
         """Step, part 1 (tile solves + reduced right-hand side), with the pending correction applied on read."""
         lib, P, nt, cfg, comm = _lib.lib(), self.P, self.nt, self.config, self.comm
         common = (nt, P, cfg, _lib.ptr(self.p), _lib.ptr(self.q), _lib.ptr(self.b), _lib.ptr(self.sep),
-                  _lib.ptr(self.bends), int(comm.rank == 0), self._last_local, self._theta, wptr(w_in), wptr(w_out),
+                  _lib.ptr(self.bends), int(comm.rank == 0), self._last_local, self._theta, _lib.ptr(w_in), _lib.ptr(w_out),
                   self.w_stride, _lib.ptr(self.rs), _lib.ptr(self.rr), nt, _lib.ptr(self.g_first))
         if self._pending:
             xs, off, ng = self._xs_index()
@@ -416,33 +400,27 @@ class PartitionedAdvectionDiffusionModel(object):
             st = lib.fvm_spike_local(*common, _lib.stream_ptr())
             _lib.check(st, "fvm_spike_local")
 
-    def _finalize(self, w_out, wptr, xs, off, ng, next_first):
-        """Step, part 3: separators and ghosts only when the correction is lazy, else the full correction."""
-        lib = _lib.lib()
+    def _finalize(self, w_out, xs, off, ng):
+        """Step, part 3: nothing when the correction is lazy (the next tile solve applies it), else the correction."""
         if self.lazy:
-            st = lib.fvm_spike_separators(self.nt, self.P, self.config, off, ng, _lib.ptr(xs), wptr(w_out),
-                                          self.w_stride, _lib.ptr(next_first), _lib.stream_ptr())
-            _lib.check(st, "fvm_spike_separators")
             self._pending = True
-        else:
-            st = lib.fvm_spike_finalize(self.nt, self.P, self.config, self.extents, off, ng, _lib.ptr(self.Vt),
-                                        _lib.ptr(self.Wt), _lib.ptr(xs), wptr(w_out), self.w_stride,
-                                        _lib.ptr(next_first), _lib.stream_ptr())
-            _lib.check(st, "fvm_spike_finalize")
+            return
+        st = _lib.lib().fvm_spike_finalize(self.nt, self.P, self.config, self.extents, off, ng, _lib.ptr(self.Vt),
+                                           _lib.ptr(self.Wt), _lib.ptr(xs), _lib.ptr(w_out), self.w_stride,
+                                           _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_finalize")
 
     # ------------------------------------------------------------------ stepping
     def step(self, nsteps=1):
         """``nsteps`` theta steps of the state set by :meth:`set_state` (theta of :meth:`prepare`)."""
         torch = _lib.require_cuda()
         lib, P, nt, cfg, comm = _lib.lib(), self.P, self.nt, self.config, self.comm
-        wptr = lambda t: ctypes.c_void_p(t.data_ptr() + 8)                      # skip the left ghost
         with torch.cuda.device(self.device):
             for _ in range(int(nsteps)):
                 w_in, w_out = self._wbuf[self._cur], self._wbuf[1 - self._cur]
-                self._local(w_in, w_out, wptr)
-                next_first = None
+                self._local(w_in, w_out)
                 if self.hier:
-                    self._step_rank_level(w_out, wptr)
+                    self._step_rank_level(w_out)
                     self._cur = 1 - self._cur
                     continue
                 if comm.world == 1:
@@ -458,14 +436,10 @@ class PartitionedAdvectionDiffusionModel(object):
                                                 _lib.ptr(self.rinv), _lib.ptr(rr_all), _lib.ptr(self.xs),
                                                 _lib.stream_ptr())
                 _lib.check(st, "fvm_spike_reduce_solve")
-                if comm.world > 1 and comm.rank < comm.world - 1:
-                    k1 = (comm.rank + 1) * nt                                               # next rank's first tile
-                    next_first = (gf[comm.rank + 1] - self.V0_all[:, k1] * self.xs[:, k1 - 1]
-                                  - self.W0_all[:, k1] * self.xs[:, k1]).contiguous()
-                self._finalize(w_out, wptr, self.xs, self.tile_offset, self.nt_global, next_first)
+                self._finalize(w_out, self.xs, self.tile_offset, self.nt_global)
                 self._cur = 1 - self._cur
 
-    def _step_rank_level(self, w_out, wptr):
+    def _step_rank_level(self, w_out):
         """Second half of a step with the rank-level hierarchy (see _prepare_rank_level): local block
         solve of the separator system, ONE all-gather of 4 doubles per problem, top system, finalize."""
         lib, P, nt, comm = _lib.lib(), self.P, self.nt, self.comm
@@ -476,10 +450,9 @@ class PartitionedAdvectionDiffusionModel(object):
         allp = comm.all_gather(self.packet, self._allp)                  # (W, P, 4), into a buffer kept across steps
         st = lib.fvm_spike_rank_top(P, nt, comm.world, comm.rank, _lib.ptr(allp), _lib.ptr(self.top_inv),
                                     _lib.ptr(self.top_cst), _lib.ptr(gr), _lib.ptr(self.Vr), _lib.ptr(self.Wr),
-                                    _lib.ptr(self.xs_ext), _lib.ptr(self.next_first), _lib.stream_ptr())
+                                    _lib.ptr(self.xs_ext), _lib.stream_ptr())
         _lib.check(st, "fvm_spike_rank_top")
-        nf = self.next_first if comm.rank < comm.world - 1 else None
-        self._finalize(w_out, wptr, self.xs_ext, 1, nt + 1, nf)
+        self._finalize(w_out, self.xs_ext, 1, nt + 1)
 
     def run(self, w, theta, nsteps):
         """set_state + prepare + step; returns this rank's cells of the final state."""

@@ -206,10 +206,12 @@ int fvm_theta_run_fused_ex(const fvm_problem* prob, const double* dt, double the
  * `tile_offset`.  The last cell of a tile is a separator; the separators of ALL tiles of ALL
  * slabs form one tridiagonal "reduced" system (n_global unknowns per problem) that every rank
  * solves redundantly after an all-gather of its right-hand side (the host layer owns the NCCL
- * call).  State arrays are ghosted: `w` points at the slab's first cell, w[-1] and w[n_tiles*T]
- * hold the neighbouring slabs' edge values, and w_stride >= n_tiles*T + 2 separates problems.
- * Work arrays (all caller-owned): p, q, b, Vt, Wt [P][n_tiles*T]; sep [P][n_tiles][10];
- * bends [P][2]; rs, rr [P][n_tiles]; g_first [P]; xs, rp, rq, rinv [P][n_global]. */
+ * call).  A step has no right-hand side: with B = I/theta - cA, c = (1-theta)/theta, it is
+ * w' = A^-1(w/theta + beta) - c w, so no cell needs its neighbours' old values, a tile needs nothing
+ * from the tiles next to it and the state carries no ghost cells: `w` points at the slab's first
+ * cell and w_stride >= n_tiles*T separates problems.
+ * Work arrays (all caller-owned): p, q, b, Vt, Wt [P][n_tiles*T]; sep [P][n_tiles][6];
+ * bends [P][2]; rs [P][n_tiles][2]; rr [P][n_tiles]; g_first [P]; xs, rp, rq, rinv [P][n_global]. */
 
 /* Cells per tile of a tile configuration, 0 if the configuration does not exist.
  *   0: 8192 cells (512 threads x 16 cells, one CTA per SM)
@@ -225,51 +227,54 @@ int64_t fvm_spike_tile_cells(int32_t config);
 int64_t fvm_spike_tile_threads(int32_t config);
 
 /* Once per model: rows of A = I - dt*theta*alpha*M for the slab (prob->faces / a / d are indexed
- * by GLOBAL cell, so pass base pointers shifted by the slab offset), tile-local LU (p, q, b),
- * tile spikes (Vt, Wt), per-tile separator rows and reduced-system contributions (sep), the
- * scaled beta entries (bends) and, in extents[0..1] (device int32), how many cells from the
- * left/right tile edge carry a spike larger than spike_tol. */
+ * by GLOBAL cell, so pass base pointers shifted by the slab offset), tile-local un-normalised LU
+ * restarted at every tile's first cell (p = l, q = s, b = kappa as fvm_theta_factor defines them; all
+ * three 0 at the separator), tile spikes (Vt, Wt; 0 and -1 at the separator), per-tile separator
+ * rows and reduced-system contributions (sep: lo, up, RL, RD less the next tile's term, V0, W0),
+ * theta*beta of the mesh's two end cells (bends) and, in extents[0..1] (device int32), how many
+ * cells from the left/right tile edge carry a spike larger than spike_tol.  Every elimination chain
+ * runs in double-double and every stored number is rounded once. */
 int fvm_spike_setup(const fvm_problem* prob, const double* dt, double theta, int64_t tile_offset,
                     int64_t n_tiles, int32_t config, double* p, double* q, double* b, double* Vt,
                     double* Wt, double* sep, double* bends, int32_t* extents, double spike_tol,
                     void* stream);
 
 /* Once per model: Thomas factors (rp, rq, rinv) of the reduced tridiagonal (RL, RD, RU), n
- * unknowns per problem. */
+ * unknowns per problem (pivot chain in double-double). */
 int fvm_spike_reduced_factor(int64_t n, int64_t P, const double* RL, const double* RD,
                              const double* RU, double* rp, double* rq, double* rinv, void* stream);
 
-/* Step, part 1: r~ = inv*(B w) and the tile-local solves (w_in -> w_out = g), the separators'
- * right-hand sides rs, the reduced right-hand side rr (the last tile of the slab leaves out the
- * term that needs the next slab's first cell) and g_first = g at the slab's first cell.
+/* Step, part 1: the tile-local solves g of A g = w/theta + beta (w_in -> w_out = z = g - c w, the new
+ * state up to the spike correction of part 3), the reduced right-hand side rr (the last tile of the
+ * slab leaves out the term that needs the next slab's first value) and g_first = g at the slab's
+ * first cell.  rs is scratch between the call's two kernels.
  * has_first_cell: the slab holds global cell 0; last_cell_local: local index of global cell J-1
- * if it is a tile-interior cell of this slab and carries a nonzero beta, else -1. */
+ * if this slab holds it and it carries a nonzero beta, else -1. */
 int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
                     const double* b, const double* sep, const double* bends,
                     int32_t has_first_cell, int64_t last_cell_local, double theta,
                     const double* w_in, double* w_out, int64_t w_stride, double* rs, double* rr,
                     int64_t rr_stride, double* g_first, void* stream);
 
-/* Step, part 2: solve the factored reduced system, rr -> xs, n_global unknowns per problem. */
+/* Step, part 2: solve the factored reduced system, rr -> xs (the separators' values of
+ * y = A^-1(w/theta + beta)), n_global unknowns per problem. */
 int fvm_spike_reduce_solve(int64_t n_global, int64_t P, const double* rp, const double* rq,
                            const double* rinv, const double* rr, double* xs, void* stream);
 
-/* Step, part 3: x = g - Vt*xs(k-1) - Wt*xs(k) over the spike extents (extents_host: the two
- * HOST integers read back from fvm_spike_setup), separators = xs, ghost cells refreshed
- * (next_first [P]: the next slab's new first value, NULL on the last slab).  In place on w. */
+/* Step, part 3: w' = z - Vt*xs(k-1) - Wt*xs(k) over the spike extents (extents_host: the two
+ * HOST integers read back from fvm_spike_setup), the separators included (Vt = 0, Wt = -1 there).
+ * In place on w, and NOT idempotent: exactly once per fvm_spike_local. */
 int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, const int32_t* extents_host,
                        int64_t tile_offset, int64_t n_tiles_global, const double* Vt,
-                       const double* Wt, const double* xs, double* w, int64_t w_stride,
-                       const double* next_first, void* stream);
+                       const double* Wt, const double* xs, double* w, int64_t w_stride, void* stream);
 
-/* Lazy correction for time loops: fvm_spike_local_lazy + fvm_spike_separators in place of
- * fvm_spike_local + fvm_spike_finalize.  The state then holds the UNCORRECTED tile solutions between
- * steps (true values only at the separators and in the ghosts, written by fvm_spike_separators), and
- * the next step's tile solve applies  x = g - Vt xs(k-1) - Wt xs(k)  while it loads the tile (xs = the
- * previous step's separator values, indexed like in fvm_spike_finalize).  This saves the separate
- * correction pass: 16 B instead of 32 B of HBM traffic per corrected cell.  The FIRST step after a
- * true state was stored uses fvm_spike_local; fvm_spike_finalize turns the buffer into the true
- * state whenever it is needed. */
+/* Lazy correction for time loops: fvm_spike_local_lazy in place of fvm_spike_local +
+ * fvm_spike_finalize.  The state then holds the UNCORRECTED z between steps, and the next step's tile
+ * solve applies  w = z - Vt xs(k-1) - Wt xs(k)  while it loads the tile (xs = the previous step's
+ * separator values, indexed like in fvm_spike_finalize; it must stay untouched until then).  This
+ * saves the separate correction pass: 16 B instead of 32 B of HBM traffic per corrected cell.  The
+ * FIRST step after a true state was stored uses fvm_spike_local; fvm_spike_finalize turns the buffer
+ * into the true state whenever it is needed. */
 int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
                          const double* b, const double* sep, const double* bends,
                          int32_t has_first_cell, int64_t last_cell_local, double theta,
@@ -277,29 +282,25 @@ int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, const doubl
                          int64_t rr_stride, double* g_first, const double* Vt, const double* Wt,
                          const double* xs, int64_t tile_offset, int64_t n_tiles_global,
                          const int32_t* extents_host, void* stream);
-int fvm_spike_separators(int64_t n_tiles, int64_t P, int32_t config, int64_t tile_offset,
-                         int64_t n_tiles_global, const double* xs, double* w, int64_t w_stride,
-                         const double* next_first, void* stream);
 
 /* Rank-level SPIKE over the separator system (cells split over GPUs; no counterpart in the
  * reference, which is single-process).  Each rank solves the block of its own nt tile separators
  * with fvm_spike_reduce_solve (couplings to the neighbouring ranks cut, its last separator
  * decoupled), then:
  *  fvm_spike_rank_pack: packet[P][4] = what the rank contributes to the per-step all-gather
- *    (first and last block value, its separator's right-hand side, its slab's first cell);
+ *    (first and last block value, its separator's right-hand side, its slab's first tile value);
  *  fvm_spike_rank_top: from the gathered packets allp[world][P][4], the dense inverse
- *    top_inv[P][world][world] of the rank-separator system and the constants cst[P][7][world]
- *    (rows: up of every rank's last tile; lo, up of the rank separators' rows; rank spikes Vr, Wr
- *    and tile spikes V0, W0 at every rank's first tile) it writes this rank's separator values
- *    xs_ext[P][nt+1] (entry 0 = the previous rank's separator) and next_first[P], the new value
- *    of the next rank's first cell. */
+ *    top_inv[P][world][world] of the rank-separator system and the constants cst[P][3][world]
+ *    (rows: up of every rank's last tile; lo, up of the rank separators' rows) it writes this rank's
+ *    separator values xs_ext[P][nt+1] (entry 0 = the previous rank's separator). */
 int fvm_spike_rank_pack(int64_t P, int64_t nt, const double* gr, const double* g_first, double* packet,
                         void* stream);
 int fvm_spike_rank_top(int64_t P, int64_t nt, int32_t world, int32_t rank, const double* allp,
                        const double* top_inv, const double* cst, const double* gr, const double* Vr,
-                       const double* Wr, double* xs_ext, double* next_first, void* stream);
+                       const double* Wr, double* xs_ext, void* stream);
 
-/* Largest P * n_tiles fvm_spike_local_static accepts (65536 tiles = 512 KiB of scratch). */
+/* Largest P * n_tiles fvm_spike_local_static accepts (32768 tiles, two doubles each = 512 KiB of
+ * scratch). */
 int64_t fvm_spike_static_max_tiles(void);
 
 /* fvm_spike_local without the `rs` work array.  NO COUNTERPART IN THE REFERENCE: it exists for

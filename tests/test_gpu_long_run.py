@@ -137,3 +137,30 @@ def test_full_run_length_on_the_other_on_chip_kernels(J, nprob):
         for v in got:
             err = _err(got[v][q], exact, w0[q])
             assert err <= 1e-11, (J, v, q, err)
+
+
+@pytest.mark.parametrize("config", [1, 2])
+def test_full_run_length_on_the_partitioned_variant(config):
+    """Variant 3 (tile SPIKE, the kernels cfg 4 and cfg 5 run on) over the same 10,000 Crank-Nicolson steps
+    with the reference's D: 256-cell tiles cut each 1,024-cell system into four (every step goes through
+    the reduced system and the lazy spike correction), the 4,096-cell production tile holds it whole with
+    3,072 padded cells behind it.  Same bars as the other variants."""
+    from fvm_b200 import PartitionedAdvectionDiffusionModel
+    g = np.load(GOLD)
+    P = len(g["problems"])
+    m = PartitionedAdvectionDiffusionModel(W.graded_faces(1024), g["a"], g["D_reference"], g["k"], "central", P=P,
+                                           config=config)
+    m.set_boundary_conditions(**BC)
+    m.prepare(0.5)
+    m.set_state(g["w0"])
+    done, worst = 0, [0.0, 0.0]
+    for i, snap in enumerate(g["snaps"]):
+        m.step(int(snap) - done)
+        done = int(snap)
+        got = m.get_state().cpu().numpy()
+        e_ref = _err(got, g["reference"][:, i], g["w0"])
+        e_exact = _err(got, g["exact"][:, i], g["w0"])
+        worst = [max(worst[0], e_ref.max()), max(worst[1], e_exact.max())]
+        assert e_ref.max() <= 1e-10, (config, snap, g["problems"][e_ref.argmax()], e_ref.max())
+        assert e_exact.max() <= 1e-11, (config, snap, g["problems"][e_exact.argmax()], e_exact.max())
+    print("partitioned (config %d), reference D: worst vs reference %.2e, vs exact %.2e" % (config, worst[0], worst[1]))

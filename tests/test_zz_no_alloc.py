@@ -3,7 +3,7 @@
 Some users of this library run the time loop where device memory cannot be requested: the host
 application took all of the GPU's memory for its own pool when it started, or the step runs in
 a section where cudaMalloc's device-wide synchronisation is not allowed.  For them the one work
-array fvm_spike_local needs from its caller (`rs`) sits in a fixed 512 KiB device array inside
+array fvm_spike_local needs from its caller (`rs`, two doubles per tile) sits in a fixed 512 KiB device array inside
 the library.  This test calls the entry point through the C-ABI, twice in a row on different
 states, and requires the same bits as fvm_spike_local produces with a caller-owned `rs`; it
 also checks that a request beyond the built-in capacity is refused without launching anything.
@@ -11,7 +11,6 @@ also checks that a request beyond the built-in capacity is refused without launc
 The file is named so that pytest collects it last: a run that stops at the first failure has
 then already executed every other test.
 """
-import ctypes
 
 import numpy as np
 import pytest
@@ -46,17 +45,17 @@ def _call(m, static, w_in):
     w_out = torch.full_like(w_in, float("nan"))
     rr = torch.full((m.P, m.nt), float("nan"), dtype=torch.float64, device=dev)
     gf = torch.full((m.P,), float("nan"), dtype=torch.float64, device=dev)
-    wptr = lambda t: ctypes.c_void_p(t.data_ptr() + 8)
+    wptr = _lib.ptr
     common = (m.nt, m.P, m.config, _lib.ptr(m.p), _lib.ptr(m.q), _lib.ptr(m.b), _lib.ptr(m.sep),
               _lib.ptr(m.bends), 1, m._last_local, m._theta, wptr(w_in), wptr(w_out), m.w_stride)
     if static:
         st = lib.fvm_spike_local_static(*common, _lib.ptr(rr), m.nt, _lib.ptr(gf), _lib.stream_ptr())
     else:
-        rs = torch.full((m.P, m.nt), float("nan"), dtype=torch.float64, device=dev)
+        rs = torch.full((m.P, m.nt, 2), float("nan"), dtype=torch.float64, device=dev)
         st = lib.fvm_spike_local(*common, _lib.ptr(rs), _lib.ptr(rr), m.nt, _lib.ptr(gf), _lib.stream_ptr())
     assert st == 0, lib.fvm_status_string(st)
     torch.cuda.synchronize()
-    return w_out[:, 1:1 + m.n_local].clone(), rr.clone(), gf.clone()
+    return w_out.clone(), rr.clone(), gf.clone()
 
 
 def test_static_scratch_matches_caller_scratch_twice_in_a_row():
@@ -85,7 +84,7 @@ def test_static_scratch_refuses_sizes_beyond_its_capacity():
     out = torch.zeros_like(buf)
     rr = torch.zeros((1, m.nt), dtype=torch.float64, device=m.device)
     gf = torch.zeros((1,), dtype=torch.float64, device=m.device)
-    wptr = lambda t: ctypes.c_void_p(t.data_ptr() + 8)
+    wptr = _lib.ptr
     before = out.clone()
     st = lib.fvm_spike_local_static(cap + 1, 1, m.config, _lib.ptr(m.p), _lib.ptr(m.q), _lib.ptr(m.b),
                                     _lib.ptr(m.sep), _lib.ptr(m.bends), 1, -1, 0.5, wptr(buf), wptr(out),
