@@ -80,9 +80,9 @@ _SIGNATURES = {
     "fvm_spike_local_lazy": (ctypes.c_int, [c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_i64,
                                             c_dbl, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr,
                                             c_ptr, c_i64, c_i64, ctypes.POINTER(c_i32), c_ptr]),
-    "fvm_spike_rank_pack": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr]),
-    "fvm_spike_rank_top": (ctypes.c_int, [c_i64, c_i64, c_i32, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
-                                          c_ptr, c_ptr]),
+    "fvm_spike_rank_pack": (ctypes.c_int, [c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "fvm_spike_rank_top": (ctypes.c_int, [c_i64, c_i64, c_i64, c_i32, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                          c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "fvm_spike_static_max_tiles": (c_i64, []),
     "fvm_spike_local_static": (ctypes.c_int, [c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_i64,
                                               c_dbl, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr]),

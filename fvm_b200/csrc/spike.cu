@@ -614,75 +614,102 @@ extern "C" int fvm_spike_local_static(int64_t n_tiles, int64_t P, int32_t config
 }
 
 // ------------------------------------------------------------------------------------------
-// Rank-level SPIKE over the separator system (partitioned.py: _prepare_rank_level): the two small
-// kernels around the per-step all-gather.
+// SPIKE once more over the separator system (partitioned.py: _prepare_block_level).  The reduced
+// tridiagonal (one unknown per tile) is cut into blocks of m consecutive unknowns -- B blocks per rank,
+// world*B in all -- whose last unknown is the BLOCK separator.  The blocks are solved in parallel
+// (fvm_spike_reduce_solve with the blocks as its batch: one CTA each instead of one CTA for the whole
+// system), the block separators satisfy a (world*B)-unknown tridiagonal that every CTA of the last
+// kernel solves for itself, and across GPUs a step exchanges 4 doubles per block.  The two small
+// kernels around the per-step all-gather:
 namespace fvm {
 
-// What a rank contributes to the gather, 4 doubles per problem: first and last value of its block
-// solution gr, its separator's right-hand side (the local solve passes it through: that row is
-// decoupled) and the first cell of its slab.
-__global__ void rank_pack_kernel(int64_t P, int64_t nt, const double* __restrict__ gr,
+// What a block contributes to the gather, 4 doubles: first and last interior value of its block
+// solution gr, its separator's right-hand side (the block solve passes it through: that row is
+// decoupled) and the first tile value of the rank's slab (used for block 0 only).
+__global__ void rank_pack_kernel(int64_t P, int64_t B, int64_t m, const double* __restrict__ gr,
                                  const double* __restrict__ g_first, double* __restrict__ packet) {
-  const int64_t pi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (pi >= P) return;
-  const double* g = gr + pi * nt;
-  double* o = packet + pi * 4;
-  o[0] = g[0]; o[1] = g[nt - 2]; o[2] = g[nt - 1]; o[3] = g_first[pi];
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P * B) return;
+  const double* g = gr + i * m;
+  double* o = packet + i * 4;
+  o[0] = g[0]; o[1] = g[m - 2]; o[2] = g[m - 1]; o[3] = g_first[i / B];
 }
 
-// After the gather (allp[rank][problem][4]): right-hand side and solution of the `world`-unknown
-// top system (dense inverse), and this rank's separator values xs_ext[1..nt] with the previous rank's
-// separator in xs_ext[0].
-// cst[problem][3][world]: sup of every rank's last tile and the separator rows' couplings (lo, up).
-__global__ void __launch_bounds__(256) rank_top_kernel(int64_t P, int64_t nt, int world, int rank,
-                                                       const double* __restrict__ allp,
-                                                       const double* __restrict__ top_inv,
-                                                       const double* __restrict__ cst,
-                                                       const double* __restrict__ gr, const double* __restrict__ Vr,
-                                                       const double* __restrict__ Wr, double* __restrict__ xs_ext) {
-  __shared__ double rhs[64], X[64];
+// After the gather (allp[rank][problem][block][4]): right-hand side and solution X of the top system
+// (factors tp, tq, tinv [problem][world*B], affine scans over the CTA), then this rank's separator
+// values xs_ext[1..nt] with the previous rank's last separator in xs_ext[0]:
+//   block separator = X(block),  others = gr - Vr X(block-1) - Wr X(block).
+// cst[problem][3][world*B]: coupling of a rank's last separator to the next rank's first tile value
+// (0 for the other blocks), and the block separator rows' couplings (lo, up) to the neighbouring block
+// interiors.  grid = (problems, shares): every CTA solves the small top system for itself and then
+// writes its share of the nt separators.
+constexpr int kTopTPB = 256, kTopCPT = 4;                  // world*B <= 1024
+
+__global__ void __launch_bounds__(kTopTPB) rank_top_kernel(int64_t P, int64_t B, int64_t m, int world, int rank,
+                                                           const double* __restrict__ allp,
+                                                           const double* __restrict__ tp, const double* __restrict__ tq,
+                                                           const double* __restrict__ tinv,
+                                                           const double* __restrict__ cst,
+                                                           const double* __restrict__ gr, const double* __restrict__ Vr,
+                                                           const double* __restrict__ Wr, double* __restrict__ xs_ext) {
+  __shared__ double X[kTopTPB * kTopCPT];
+  __shared__ double sm[66];
   const int64_t pi = blockIdx.x;
   const int t = threadIdx.x;
-  const double* c = cst + pi * 3 * world;
-  auto pk = [&](int r, int i) { return allp[((int64_t)r * P + pi) * 4 + i]; };
-  if (t < world) {
-    const bool has_next = t + 1 < world;
-    const double gfirst_n = has_next ? pk(t + 1, 0) : 0.0, cell_n = has_next ? pk(t + 1, 3) : 0.0;
-    rhs[t] = pk(t, 2) - c[0 * world + t] * cell_n - c[1 * world + t] * pk(t, 1) - c[2 * world + t] * gfirst_n;
+  const int NB = world * (int)B;
+  const double* c = cst + pi * 3 * NB;
+  auto pk = [&](int blk, int i) { return allp[((((int64_t)(blk / B)) * P + pi) * B + blk % B) * 4 + i]; };
+  double g[kTopCPT], pc[kTopCPT], qc[kTopCPT];
+#pragma unroll
+  for (int j = 0; j < kTopCPT; ++j) {
+    const int blk = t * kTopCPT + j;
+    g[j] = 0.0; pc[j] = 0.0; qc[j] = 0.0;
+    if (blk < NB) {
+      double r = pk(blk, 2) - c[NB + blk] * pk(blk, 1);
+      if (blk + 1 < NB) r -= c[blk] * pk(blk + 1, 3) + c[2 * NB + blk] * pk(blk + 1, 0);
+      g[j] = r * tinv[pi * NB + blk];
+      pc[j] = tp[pi * NB + blk]; qc[j] = tq[pi * NB + blk];
+    }
   }
+  cta_forward<kTopTPB, kTopCPT>(g, [&](int j) { return pc[j]; }, sm, 0.0, nullptr);
+  cta_backward<kTopTPB, kTopCPT>(g, [&](int j) { return qc[j]; }, sm, 0.0, nullptr);
+#pragma unroll
+  for (int j = 0; j < kTopCPT; ++j) X[t * kTopCPT + j] = g[j];
   __syncthreads();
-  if (t < world) {
-    const double* row = top_inv + (pi * world + t) * world;
-    double acc = 0.0;
-    for (int j = 0; j < world; ++j) acc = fma(row[j], rhs[j], acc);
-    X[t] = acc;
-  }
-  __syncthreads();
-  const double Xr = X[rank], Xl = rank > 0 ? X[rank - 1] : 0.0;
+  const int64_t nt = B * m;
+  const int64_t share = (nt + gridDim.y - 1) / gridDim.y;
+  const int64_t k0 = (int64_t)blockIdx.y * share, k1 = min(nt, k0 + share);
   double* xe = xs_ext + pi * (nt + 1);
-  for (int64_t k = t; k < nt; k += blockDim.x) {
+  for (int64_t k = k0 + t; k < k1; k += kTopTPB) {
+    const int blk = rank * (int)B + (int)(k / m);
+    const double Xr = X[blk], Xl = blk > 0 ? X[blk - 1] : 0.0;
     const int64_t o = pi * nt + k;
-    xe[1 + k] = (k == nt - 1) ? Xr : fma(-Wr[o], Xr, fma(-Vr[o], Xl, gr[o]));
+    xe[1 + k] = (k % m == m - 1) ? Xr : fma(-Wr[o], Xr, fma(-Vr[o], Xl, gr[o]));
   }
-  if (t == 0) xe[0] = Xl;
+  if (blockIdx.y == 0 && t == 0) xe[0] = rank > 0 ? X[rank * (int)B - 1] : 0.0;
 }
 
 }  // namespace fvm
 
-extern "C" int fvm_spike_rank_pack(int64_t P, int64_t nt, const double* gr, const double* g_first, double* packet,
-                                   void* stream) {
-  if (!gr || !g_first || !packet || P < 1 || nt < 2) return FVM_ERR_INVALID_ARG;
-  fvm::rank_pack_kernel<<<(unsigned)((P + 127) / 128), 128, 0, (cudaStream_t)stream>>>(P, nt, gr, g_first, packet);
+extern "C" int fvm_spike_rank_pack(int64_t P, int64_t B, int64_t m, const double* gr, const double* g_first,
+                                   double* packet, void* stream) {
+  if (!gr || !g_first || !packet || P < 1 || B < 1 || m < 2) return FVM_ERR_INVALID_ARG;
+  fvm::rank_pack_kernel<<<(unsigned)((P * B + 127) / 128), 128, 0, (cudaStream_t)stream>>>(P, B, m, gr, g_first, packet);
   return (int)cudaGetLastError();
 }
 
-extern "C" int fvm_spike_rank_top(int64_t P, int64_t nt, int32_t world, int32_t rank, const double* allp,
-                                  const double* top_inv, const double* cst, const double* gr, const double* Vr,
-                                  const double* Wr, double* xs_ext, void* stream) {
-  if (!allp || !top_inv || !cst || !gr || !Vr || !Wr || !xs_ext) return FVM_ERR_INVALID_ARG;
-  if (P < 1 || P > 0x7fffffffLL || nt < 2 || world < 2 || world > 64 || rank < 0 || rank >= world)
+extern "C" int fvm_spike_rank_top(int64_t P, int64_t B, int64_t m, int32_t world, int32_t rank, const double* allp,
+                                  const double* tp, const double* tq, const double* tinv, const double* cst,
+                                  const double* gr, const double* Vr, const double* Wr, double* xs_ext,
+                                  void* stream) {
+  if (!allp || !tp || !tq || !tinv || !cst || !gr || !Vr || !Wr || !xs_ext) return FVM_ERR_INVALID_ARG;
+  if (P < 1 || P > 0x7fffffffLL || B < 1 || m < 2 || world < 1 || rank < 0 || rank >= world)
     return FVM_ERR_INVALID_ARG;
-  fvm::rank_top_kernel<<<(unsigned)P, 256, 0, (cudaStream_t)stream>>>(P, nt, world, rank, allp, top_inv, cst, gr, Vr,
-                                                                     Wr, xs_ext);
+  if ((int64_t)world * B > fvm::kTopTPB * fvm::kTopCPT) return FVM_ERR_UNSUPPORTED;
+  int64_t shares = (B * m + 2047) / 2048;                  // ~2048 separators per CTA
+  if (shares > 64) shares = 64;
+  dim3 grid((unsigned)P, (unsigned)shares);
+  fvm::rank_top_kernel<<<grid, fvm::kTopTPB, 0, (cudaStream_t)stream>>>(P, B, m, world, rank, allp, tp, tq, tinv, cst,
+                                                                       gr, Vr, Wr, xs_ext);
   return (int)cudaGetLastError();
 }

@@ -100,7 +100,8 @@ class PartitionedAdvectionDiffusionModel(object):
     """
 
     def __init__(self, faces, a, d, k, discretisation="central", P=1, reaction=None, strict_bc=False,
-                 J=None, group=None, config=2, spike_tol=1e-30, device=None, hierarchical=True, lazy=True):
+                 J=None, group=None, config=2, spike_tol=1e-30, device=None, hierarchical=True, lazy=True,
+                 blocks=None):
         torch = _lib.require_cuda()
         lib = _lib.lib()
         if discretisation not in _lib.SCHEMES:
@@ -120,6 +121,7 @@ class PartitionedAdvectionDiffusionModel(object):
         self.P = int(P)
         self.discretisation, self.strict_bc, self.spike_tol = discretisation, strict_bc, float(spike_tol)
         self.hierarchical = bool(hierarchical)
+        self._blocks_wanted = blocks    # blocks per rank of the separator system (None: chosen from its size)
         self.lazy = bool(lazy)          # apply the spike correction inside the next step's tile solve
         self._pending = False           # the current buffer holds uncorrected tile solutions
         plan = plan_partition(self.J, self.T, self.comm.world)
@@ -256,7 +258,8 @@ class PartitionedAdvectionDiffusionModel(object):
         RL = sep_all[..., SEP_RL].contiguous()
         RD = (sep_all[..., SEP_RDA] - self.sup_all * nxt(self.V0_all)).contiguous()
         RU = (-self.sup_all * nxt(self.W0_all)).contiguous()
-        self.hier = self.comm.world > 1 and nt >= 2 and self.hierarchical
+        self.B = self._pick_blocks() if (self.hierarchical and nt >= 2) else 1
+        self.hier = self.hierarchical and nt >= 2 and (self.comm.world > 1 or self.B > 1)
         if not self.hier:
             # every rank factors (and later solves) the whole separator system
             self.rp, self.rq, self.rinv = new(P, self.nt_global), new(P, self.nt_global), new(P, self.nt_global)
@@ -266,7 +269,7 @@ class PartitionedAdvectionDiffusionModel(object):
                                                   _lib.stream_ptr())
             _lib.check(st, "fvm_spike_reduced_factor")
         else:
-            self._prepare_rank_level(RL, RD, RU)
+            self._prepare_block_level(RL, RD, RU)
         e = self.comm.all_reduce_max_int(ext.cpu().tolist())
         self.extents = (ctypes.c_int32 * 2)(min(e[0], T - 1), min(e[1], T - 1))
         # work arrays of a step
@@ -279,66 +282,91 @@ class PartitionedAdvectionDiffusionModel(object):
         self._theta = theta
         self._ready = theta
 
+    def _pick_blocks(self):
+        """Blocks per rank of the separator system: as many as keep a block at >= 256 unknowns (one pass of
+        the CTA-wide solver), divide the rank's tiles evenly and keep the top system within one CTA."""
+        nt, cap = self.nt, 1024 // self.comm.world
+        if self._blocks_wanted is not None:
+            B = int(self._blocks_wanted)
+            if B < 1 or nt % B or nt // B < 2 or B > cap:
+                raise ValueError("blocks=%d does not cut %d tiles per rank into equal blocks of >= 2 (at most %d)"
+                                 % (B, nt, cap))
+            return B
+        best = 1
+        for B in range(2, min(nt // 256, cap) + 1):
+            if nt % B == 0:
+                best = B
+        return best
+
     def _reduced_local_solve(self, rhs, out=None):
-        """Solve this rank's block of the separator system (its own nt unknowns, couplings to the
-        neighbouring ranks cut, last unknown = the rank's separator, decoupled): rhs (P, nt) -> (P, nt)."""
+        """Solve this rank's blocks of the separator system (m unknowns each, couplings to the neighbouring
+        blocks cut, last unknown = the block's separator, decoupled): rhs (P, nt) -> (P, nt)."""
         torch = _lib.require_cuda()
         out = torch.empty_like(rhs) if out is None else out
+        m = self.nt // self.B
         with torch.cuda.device(self.device):
-            st = _lib.lib().fvm_spike_reduce_solve(self.nt, self.P, _lib.ptr(self.rp), _lib.ptr(self.rq),
+            st = _lib.lib().fvm_spike_reduce_solve(m, self.P * self.B, _lib.ptr(self.rp), _lib.ptr(self.rq),
                                                    _lib.ptr(self.rinv), _lib.ptr(rhs), _lib.ptr(out),
                                                    _lib.stream_ptr())
         _lib.check(st, "fvm_spike_reduce_solve")
         return out
 
-    def _prepare_rank_level(self, RL, RD, RU):
+    def _prepare_block_level(self, RL, RD, RU):
         """SPIKE once more, one level up.  The separator system (one unknown per tile, all ranks) is
-        itself partitioned: every rank keeps the rows of its own tiles, its LAST tile separator is the
-        rank's separator, the nt-1 others form a block that is solved locally; the rank separators
-        satisfy a `world`-unknown tridiagonal whose (dense, tiny) inverse every rank holds.  A step
-        then all-gathers 4 numbers per problem and rank instead of the rank's whole right-hand side,
-        and solves nt unknowns instead of world*nt."""
+        itself partitioned into B blocks per rank of m = nt/B unknowns: the LAST tile separator of a block
+        is the block's separator, the m-1 others are solved block by block in parallel (one CTA each,
+        instead of one CTA for the whole system); the block separators satisfy a (world*B)-unknown
+        tridiagonal, factored here once, that the last kernel of a step solves.  Across GPUs a step then
+        all-gathers 4 numbers per problem and block instead of the rank's whole right-hand side."""
         torch = _lib.require_cuda()
-        lib, dev, P, nt, r, W = _lib.lib(), self.device, self.P, self.nt, self.comm.rank, self.comm.world
+        lib, dev, P, nt, r, W, B = _lib.lib(), self.device, self.P, self.nt, self.comm.rank, self.comm.world, self.B
+        m, NB = nt // B, self.comm.world * self.B
         sl = slice(r * nt, (r + 1) * nt)
-        rl, rd, ru = RL[:, sl].clone(), RD[:, sl].clone(), RU[:, sl].clone()
-        cut_lo, cut_up = rl[:, 0].clone(), ru[:, nt - 2].clone()       # couplings leaving the block
-        sep_l, sep_d, sep_u = rl[:, nt - 1].clone(), rd[:, nt - 1].clone(), ru[:, nt - 1].clone()
-        rl[:, 0] = 0.0
-        ru[:, nt - 2] = 0.0
-        rl[:, nt - 1], rd[:, nt - 1], ru[:, nt - 1] = 0.0, 1.0, 0.0     # the separator row: decoupled
+        rl, rd, ru = (x[:, sl].reshape(P, B, m).contiguous().clone() for x in (RL, RD, RU))
+        cut_lo, cut_up = rl[:, :, 0].clone(), ru[:, :, m - 2].clone()   # couplings leaving the block interiors
+        sep_l, sep_d, sep_u = rl[:, :, m - 1].clone(), rd[:, :, m - 1].clone(), ru[:, :, m - 1].clone()
+        rl[:, :, 0] = 0.0
+        ru[:, :, m - 2] = 0.0
+        rl[:, :, m - 1], rd[:, :, m - 1], ru[:, :, m - 1] = 0.0, 1.0, 0.0   # the separator rows: decoupled
         new = lambda *shape: torch.empty(shape, dtype=torch.float64, device=dev)
         self.rp, self.rq, self.rinv = new(P, nt), new(P, nt), new(P, nt)
         with torch.cuda.device(dev):
-            st = lib.fvm_spike_reduced_factor(nt, P, _lib.ptr(rl.contiguous()), _lib.ptr(rd.contiguous()),
-                                              _lib.ptr(ru.contiguous()), _lib.ptr(self.rp), _lib.ptr(self.rq),
-                                              _lib.ptr(self.rinv), _lib.stream_ptr())
+            st = lib.fvm_spike_reduced_factor(m, P * B, _lib.ptr(rl), _lib.ptr(rd), _lib.ptr(ru), _lib.ptr(self.rp),
+                                              _lib.ptr(self.rq), _lib.ptr(self.rinv), _lib.stream_ptr())
         _lib.check(st, "fvm_spike_reduced_factor")
-        e = torch.zeros((P, nt), dtype=torch.float64, device=dev)
-        e[:, 0] = cut_lo
-        self.Vr = self._reduced_local_solve(e)                           # response to the previous rank's separator
+        e = torch.zeros((P, B, m), dtype=torch.float64, device=dev)
+        e[:, :, 0] = cut_lo
+        self.Vr = self._reduced_local_solve(e.view(P, nt)).view(P, B, m)   # response to the previous block's separator
         e.zero_()
-        e[:, nt - 2] = cut_up
-        self.Wr = self._reduced_local_solve(e)                           # response to this rank's own separator
-        self.Vr[:, nt - 1] = 0.0
-        self.Wr[:, nt - 1] = 0.0
-        info = torch.stack([sep_l, sep_d, sep_u, self.Vr[:, 0], self.Wr[:, 0], self.Vr[:, nt - 2],
-                            self.Wr[:, nt - 2]], dim=1)                   # (P, 7)
-        allv = self.comm.all_gather(info)                                # (W, P, 7)
-        sl_, sd_, su_, vf, wf, vl, wlast = [allv[:, :, i].t().contiguous() for i in range(7)]   # (P, W)
+        e[:, :, m - 2] = cut_up
+        self.Wr = self._reduced_local_solve(e.view(P, nt)).view(P, B, m)   # response to the block's own separator
+        self.Vr[:, :, m - 1] = 0.0
+        self.Wr[:, :, m - 1] = 0.0
+        info = torch.stack([sep_l, sep_d, sep_u, self.Vr[:, :, 0], self.Wr[:, :, 0], self.Vr[:, :, m - 2],
+                            self.Wr[:, :, m - 2]], dim=2)                 # (P, B, 7)
+        allv = self.comm.all_gather(info).permute(1, 0, 2, 3).reshape(P, NB, 7)
+        sl_, sd_, su_, vf, wf, vl, wlast = [allv[:, :, i].contiguous() for i in range(7)]   # (P, NB)
         nxt = lambda x: torch.cat([x[:, 1:], torch.zeros_like(x[:, :1])], dim=1)
-        TL = -sl_ * vl
-        TD = sd_ - sl_ * wlast - su_ * nxt(vf)
-        TU = -su_ * nxt(wf)
-        top = torch.diag_embed(TD) + torch.diag_embed(TL[:, 1:], offset=-1) + torch.diag_embed(TU[:, :-1], offset=1)
-        self.top_inv = torch.linalg.inv(top).contiguous()                # (P, W, W)
-        last = torch.arange(1, W + 1, device=dev) * nt - 1              # every rank's last (separator) tile
-        # constants of fvm_spike_rank_top, (P, 3, W): up of the last tiles; lo, up of the rank separators' rows
-        self.top_cst = torch.stack([self.sup_all[:, last], sl_, su_], dim=1).contiguous()
+        TL = (-sl_ * vl).contiguous()
+        TD = (sd_ - sl_ * wlast - su_ * nxt(vf)).contiguous()
+        TU = (-su_ * nxt(wf)).contiguous()
+        self.tp, self.tq, self.tinv = new(P, NB), new(P, NB), new(P, NB)
+        with torch.cuda.device(dev):
+            st = lib.fvm_spike_reduced_factor(NB, P, _lib.ptr(TL), _lib.ptr(TD), _lib.ptr(TU), _lib.ptr(self.tp),
+                                              _lib.ptr(self.tq), _lib.ptr(self.tinv), _lib.stream_ptr())
+        _lib.check(st, "fvm_spike_reduced_factor")
+        # constants of fvm_spike_rank_top, (P, 3, NB): coupling of every rank's last separator to the next
+        # rank's first tile value (0 for the blocks inside a rank: reduced_rhs_kernel has that term); lo, up of
+        # the block separators' rows
+        c0 = torch.zeros((P, NB), dtype=torch.float64, device=dev)
+        last = torch.arange(1, W + 1, device=dev) * nt - 1              # every rank's last tile
+        c0[:, B - 1::B] = self.sup_all[:, last]
+        self.top_cst = torch.stack([c0, sl_, su_], dim=1).contiguous()
+        self.Vr, self.Wr = self.Vr.view(P, nt), self.Wr.view(P, nt)
         self.xs_ext = torch.zeros((P, nt + 1), dtype=torch.float64, device=dev)
-        self.packet = torch.zeros((P, 4), dtype=torch.float64, device=dev)
+        self.packet = torch.zeros((P, B, 4), dtype=torch.float64, device=dev)
         self._gr = torch.zeros((P, nt), dtype=torch.float64, device=dev)          # work arrays of a step: nothing is
-        self._allp = torch.zeros((W, P, 4), dtype=torch.float64, device=dev)      # allocated inside the time loop
+        self._allp = torch.zeros((W, P, B, 4), dtype=torch.float64, device=dev)   # allocated inside the time loop
 
     # ------------------------------------------------------------------ state
     def set_state(self, w):
@@ -440,17 +468,17 @@ class PartitionedAdvectionDiffusionModel(object):
                 self._cur = 1 - self._cur
 
     def _step_rank_level(self, w_out):
-        """Second half of a step with the rank-level hierarchy (see _prepare_rank_level): local block
-        solve of the separator system, ONE all-gather of 4 doubles per problem, top system, finalize."""
-        lib, P, nt, comm = _lib.lib(), self.P, self.nt, self.comm
-        gr = self._reduced_local_solve(self.rr, self._gr)   # block solution; the separator row passes its rhs through
-        st = lib.fvm_spike_rank_pack(P, nt, _lib.ptr(gr), _lib.ptr(self.g_first), _lib.ptr(self.packet),
+        """Second half of a step with the block-level hierarchy (see _prepare_block_level): block solves of
+        the separator system, ONE all-gather of 4 doubles per problem and block, top system, finalize."""
+        lib, P, nt, comm, B = _lib.lib(), self.P, self.nt, self.comm, self.B
+        gr = self._reduced_local_solve(self.rr, self._gr)   # block solutions; the separator rows pass their rhs through
+        st = lib.fvm_spike_rank_pack(P, B, nt // B, _lib.ptr(gr), _lib.ptr(self.g_first), _lib.ptr(self.packet),
                                      _lib.stream_ptr())
         _lib.check(st, "fvm_spike_rank_pack")
-        allp = comm.all_gather(self.packet, self._allp)                  # (W, P, 4), into a buffer kept across steps
-        st = lib.fvm_spike_rank_top(P, nt, comm.world, comm.rank, _lib.ptr(allp), _lib.ptr(self.top_inv),
-                                    _lib.ptr(self.top_cst), _lib.ptr(gr), _lib.ptr(self.Vr), _lib.ptr(self.Wr),
-                                    _lib.ptr(self.xs_ext), _lib.stream_ptr())
+        allp = comm.all_gather(self.packet, self._allp)                  # (W, P, B, 4), into a buffer kept across steps
+        st = lib.fvm_spike_rank_top(P, B, nt // B, comm.world, comm.rank, _lib.ptr(allp), _lib.ptr(self.tp),
+                                    _lib.ptr(self.tq), _lib.ptr(self.tinv), _lib.ptr(self.top_cst), _lib.ptr(gr),
+                                    _lib.ptr(self.Vr), _lib.ptr(self.Wr), _lib.ptr(self.xs_ext), _lib.stream_ptr())
         _lib.check(st, "fvm_spike_rank_top")
         self._finalize(w_out, self.xs_ext, 1, nt + 1)
 

@@ -283,21 +283,26 @@ int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, const doubl
                          const double* xs, int64_t tile_offset, int64_t n_tiles_global,
                          const int32_t* extents_host, void* stream);
 
-/* Rank-level SPIKE over the separator system (cells split over GPUs; no counterpart in the
- * reference, which is single-process).  Each rank solves the block of its own nt tile separators
- * with fvm_spike_reduce_solve (couplings to the neighbouring ranks cut, its last separator
- * decoupled), then:
- *  fvm_spike_rank_pack: packet[P][4] = what the rank contributes to the per-step all-gather
- *    (first and last block value, its separator's right-hand side, its slab's first tile value);
- *  fvm_spike_rank_top: from the gathered packets allp[world][P][4], the dense inverse
- *    top_inv[P][world][world] of the rank-separator system and the constants cst[P][3][world]
- *    (rows: up of every rank's last tile; lo, up of the rank separators' rows) it writes this rank's
- *    separator values xs_ext[P][nt+1] (entry 0 = the previous rank's separator). */
-int fvm_spike_rank_pack(int64_t P, int64_t nt, const double* gr, const double* g_first, double* packet,
-                        void* stream);
-int fvm_spike_rank_top(int64_t P, int64_t nt, int32_t world, int32_t rank, const double* allp,
-                       const double* top_inv, const double* cst, const double* gr, const double* Vr,
-                       const double* Wr, double* xs_ext, void* stream);
+/* SPIKE once more, over the separator system (no counterpart in the reference).  The reduced
+ * tridiagonal is cut into blocks of m consecutive unknowns, B blocks per rank (world*B <= 1024 in all),
+ * the last unknown of a block being the block's separator.  The caller factors the blocks with their
+ * couplings cut and the separator rows replaced by identity (fvm_spike_reduced_factor with n = m and the
+ * blocks as the batch), solves them every step with fvm_spike_reduce_solve (n = m, batch P*B: one CTA
+ * per block instead of one CTA for the whole system), then:
+ *  fvm_spike_rank_pack: packet[P][B][4] = what each block contributes to the per-step all-gather
+ *    (first and last interior value of the block solution gr, its separator's right-hand side, the
+ *    slab's first tile value);
+ *  fvm_spike_rank_top: from the gathered packets allp[world][P][B][4], the Thomas factors
+ *    tp, tq, tinv [P][world*B] of the block-separator system and the constants cst[P][3][world*B]
+ *    (rows: coupling of a rank's last separator to the next rank's first tile value, 0 for the other
+ *    blocks; lo, up of the block separators' rows) it writes this rank's separator values
+ *    xs_ext[P][B*m+1] (entry 0 = the previous rank's last separator).
+ * On one GPU (world = 1) there is no gather and `allp` is the packet itself. */
+int fvm_spike_rank_pack(int64_t P, int64_t B, int64_t m, const double* gr, const double* g_first,
+                        double* packet, void* stream);
+int fvm_spike_rank_top(int64_t P, int64_t B, int64_t m, int32_t world, int32_t rank, const double* allp,
+                       const double* tp, const double* tq, const double* tinv, const double* cst,
+                       const double* gr, const double* Vr, const double* Wr, double* xs_ext, void* stream);
 
 /* Largest P * n_tiles fvm_spike_local_static accepts (32768 tiles, two doubles each = 512 KiB of
  * scratch). */

@@ -7,7 +7,7 @@ from fvm_b200 import PartitionedAdvectionDiffusionModel, workloads as W
 
 J = 1 << 27
 sl = W.graded_slab(J, 0, J, "cuda")
-m = PartitionedAdvectionDiffusionModel(sl["faces"], 1.0, sl["d_pe2"], sl["dt"], "exponential", P=1, J=J, config=int(os.environ.get("TILE_CFG", 0)))
+m = PartitionedAdvectionDiffusionModel(sl["faces"], 1.0, sl["d_pe2"], sl["dt"], "exponential", P=1, J=J, config=int(os.environ.get("TILE_CFG", 2)))
 m.set_boundary_conditions(left_flux=0.0, right_flux=0.0)
 m.prepare(0.5)
 m.set_state(sl["w0"])

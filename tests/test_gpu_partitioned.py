@@ -112,7 +112,7 @@ def _free_port():
     return port
 
 
-def _two_rank_worker(rank, world, port, J, out_dir):
+def _two_rank_worker(rank, world, port, J, out_dir, blocks):
     import torch.distributed as dist
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -125,7 +125,8 @@ def _two_rank_worker(rank, world, port, J, out_dir):
     k = np.array([5.0, 3.0]) * h.min()
     w0 = 0.2 + np.exp(-((c[None, :] - np.array([[0.4], [0.6]])) / 0.1) ** 2)
     bc = dict(left_flux=0.3, right_flux=-0.2)
-    m = PartitionedAdvectionDiffusionModel(f, a, d, k, "exponential", P=2, config=1, group=dist.group.WORLD)
+    m = PartitionedAdvectionDiffusionModel(f, a, d, k, "exponential", P=2, config=1, group=dist.group.WORLD,
+                                           blocks=blocks)
     m.set_boundary_conditions(**bc)
     got = m.run(w0, 0.5, 30).cpu().numpy()
     np.save(os.path.join(out_dir, "rank%d.npy" % rank), got)
@@ -134,12 +135,13 @@ def _two_rank_worker(rank, world, port, J, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,J", [(2, 2000), (3, 1500)])
-def test_cells_split_over_ranks(tmp_path, world, J):
+@pytest.mark.parametrize("world,J,blocks", [(2, 2000, None), (3, 1500, None), (2, 2000, 2), (2, 3000, 3)])
+def test_cells_split_over_ranks(tmp_path, world, J, blocks):
     """The multi-GPU path with the ranks sharing this one GPU (collectives over gloo): the slabs'
-    results, put side by side, equal the single-rank run and the oracle."""
+    results, put side by side, equal the single-rank run and the oracle.  `blocks`: every rank's part of
+    the separator system cut into that many blocks (4 or 6 tiles per rank here: 2 unknowns per block)."""
     import torch.multiprocessing as mp
-    mp.spawn(_two_rank_worker, args=(world, _free_port(), J, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_two_rank_worker, args=(world, _free_port(), J, str(tmp_path), blocks), nprocs=world, join=True)
     f = W.graded_faces(J, 30.0)
     c = 0.5 * (f[1:] + f[:-1])
     h = np.diff(f)
@@ -187,3 +189,28 @@ def test_lazy_and_eager_correction_agree():
         res[lazy] = (mid, m.get_state())
     for a, b in zip(res[True], res[False]):
         assert float((a - b).abs().max()) <= 1e-14 * float(b.abs().max())
+
+
+@pytest.mark.parametrize("blocks", [2, 3, 6])
+def test_separator_system_in_blocks(blocks):
+    """One GPU, the separator system cut into blocks that are solved in parallel (what cfg 5 runs with
+    128 blocks of 256 separators): same result as the one-CTA solve of the whole system and as the oracle,
+    with spikes that do not decay (every block separator is coupled to its neighbours)."""
+    wl = W.stiff_reaction(P=3, J=12 * 256 - 7, seed=11)
+    res = {}
+    for b in (1, blocks):
+        m = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=3,
+                                               reaction=wl["reaction"], config=1, blocks=b)
+        m.set_boundary_conditions(**wl["bc"])
+        res[b] = m.run(wl["w0"], 1.0, 12).cpu().numpy()
+        assert m.hier == (b > 1) and m.nt == 12
+    assert np.max(np.abs(res[blocks] - res[1])) <= 1e-13 * np.max(np.abs(res[1]))
+    for p in range(3):
+        want = oracle_run(wl["faces"], wl["a"][p], wl["d"][p], wl["k"][p], "exponential", wl["bc"], 1.0,
+                          wl["w0"][p], 12, reaction=wl["reaction"][p])
+        assert step_error(res[blocks][p], want, 1.1) < TOL
+    bad = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=3,
+                                             reaction=wl["reaction"], config=1, blocks=5)
+    bad.set_boundary_conditions(**wl["bc"])
+    with pytest.raises(ValueError):
+        bad.prepare(1.0)
