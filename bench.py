@@ -30,9 +30,10 @@ METRIC = "fp64 cell-updates/sec (theta-step)"
 UNIT = "cell-updates/s"
 # algorithmic work per cell-update of the fused on-chip variant
 FLOP_PER_CELL_UPDATE = 11.0          # RHS 3 FMA, forward 1 FMA, backward 1 FMA + 1 MUL
-FP64_INSTR_PER_CELL_UPDATE = 6.0     # what the on-chip Crank-Nicolson solver issues: 4 for the sweeps + 2 spike-correction FMAs
+FP64_INSTR_PER_CELL_UPDATE = 167.0 / 32.0   # what the on-chip Crank-Nicolson solver issues per lane and step (SASS of the loop): 3 per
+                                            # cell for the sweeps + 2 spike-correction FMAs (31 cells), 10 for the separator system, 2 for its rhs
 DFMA_DISTINCT_OPERANDS_PER_CLK_SM = 44.0   # measured: profiles/microbench/r01_fp64_operands_b200.txt
-ONCHIP_B_PER_CELL_UPDATE = 40.0      # five factored coefficients read once per step (32 B TMEM + 8 B registers)
+ONCHIP_B_PER_CELL_UPDATE = 40.0      # five factored coefficients read once per step (32 B TMEM + 8 B registers / shared memory)
 HBM_B_PER_CELL_UPDATE_THOMAS = 40.0  # three per-cell-per-problem arrays streamed (24 B) + state in/out (16 B)
 HBM_B_MOVED_THOMAS = 64.0            # what thomas_steps_kernel really moves: w, l, kappa, s in, t out (40) + t, s in, w out (24)
 HBM_B_PER_CELL_UPDATE_SPIKE = 40.0   # variant 3: w, p, q, b in; g out (three per-cell arrays streamed)
@@ -182,7 +183,7 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-FUSED_SUMMARY = "r02_fused_cfg3_full.summary.txt"     # ncu --set full of the default command's dominant kernel
+FUSED_SUMMARY = "r02b_fused_cfg3_full.summary.txt"     # ncu --set full of the default command's dominant kernel
 
 
 def ncu_traffic(summary_name):
@@ -681,7 +682,8 @@ def run_b200(args):
                     "note": "a DFMA whose three operands are distinct registers (every FMA of the sweeps) sustains "
                             "42-45 per clk per SM on this GPU, not 64: register-file operand bandwidth "
                             "(profiles/microbench/fp64_operands.cu, r01_fp64_operands_b200.txt); roofline.frac above is "
-                            "still quoted against the 64/clk/SM pipe peak"},
+                            "still quoted against the 64/clk/SM pipe peak and SURVEY's 11 flop per cell-update, "
+                            "although the loop issues 5.2 DFMA (10.4 flop) per cell-update"},
                 "flop_per_cell_update": FLOP_PER_CELL_UPDATE,
                 "fp64_pipe_issue_frac": issue_frac,
                 "fp64_instr_per_cell_update": FP64_INSTR_PER_CELL_UPDATE,

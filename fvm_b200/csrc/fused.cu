@@ -302,11 +302,17 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
 //    and substitution runs outwards from there: two independent chains of half the length.
 // 2. NO RIGHT-HAND SIDE.  B = I/theta - c A (c = (1-theta)/theta) gives A^-1 B = (1/theta) A^-1 - c I.
 //    With the un-normalised factors l_c = A_c,prev / pivot_prev, kappa_c = 1 / (theta pivot_c),
-//    s_c = A_c,next / pivot_c and z = yhat - c g, where yhat = (1/theta) T^-1 g:
-//        elimination   h_c = g_c - l_c h_prev                          (1 FMA, the chain)
-//                      t_c = h_c kappa_c - c g_c - c s_c g_next        (off the chain, written over g_c)
-//        substitution  z_c = t_c - s_c z_next                          (1 FMA, the chain)
-//    4 operations per cell for Crank-Nicolson, 3 for implicit Euler, 5 in general.
+//    s_c = A_c,next / pivot_c, yhat = (1/theta) T^-1 g, and the substitution run on u = yhat / kappa
+//    (so that its inhomogeneous term is h itself):
+//        elimination   h_c = g_c - l_c h_prev                          (1 FMA, the chain; h kept beside g)
+//        substitution  u_c = h_c - s"_c u_next ,  s"_c = s_c kappa_next / kappa_c     (1 FMA, the chain)
+//                      z_c = kappa_c u_c - c g_c                       (1 FMA off the chain, written over g_c)
+//    3 operations per cell for Crank-Nicolson and implicit Euler, 4 in general (c g_c needs a product).
+//    The price is a second register array (h) where round 1 kept s; the five coefficient arrays
+//    (l, kappa, s", P1, P2) are split between tensor memory (the four the substitution reads, 128
+//    doubles per lane: all of it) and shared memory (l).  Writing t_c = h_c kappa_c - c g_c - c s_c g_next
+//    over g_c, as before, needs no second array but one more operation per cell: measured on cfg 3,
+//    the operation count is what the step time follows (profiles/microbench/r02_theta_modes_b200.txt).
 // 3. DELAYED CORRECTION.  The separator PCR is a pure latency chain.  The step is linear with
 //    constant coefficients, so the kernel keeps, between steps, the UNCORRECTED block solutions g
 //    (true state x = g - V xsl - U xs) and advances
@@ -330,12 +336,15 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
 //    (dt d/h^2) x instead of on the small uncorrected block solutions.  (c) P1, P2 = -Lhat(V, U)
 //    use the loop's own rounded factors with dd chains.
 //
-// TMEM layout per warp (256 columns of its lane quadrant), in the order the loop consumes it:
+// TMEM layout per warp (256 columns of its lane quadrant) DURING SET-UP (pipe_setup):
 //   columns [0,128)  : slot i < 15 = (l, kappa) of left cell i, then of right cell 30-i  (8 columns);
 //                      slot 15 = (l_down, kappa) and (l_up, -) of the middle cell
 //   columns [128,256): slot 0 = (P1, P2) of the middle cell; slot j = (P1, P2) of left cell 15-j,
 //                      then of right cell 15+j                                         (substitution order)
-// s lives in registers (it is read twice per step); loads are .x16 chunks, double-buffered.
+// and IN THE LOOP (pipe_relayout), in the order the substitution consumes it, one .x16 chunk per slot:
+//   slot j (16 columns) = (kappa, P1, P2, s") of left cell 15-j, then of right cell 15+j; slot 0 = the
+//   middle cell.  l moves to shared memory (the slots s occupied; l_up of the middle cell in slot 0,
+//   whose own l is never read).  Chunks are double-buffered.
 // MODE 0: any theta in (0,1];  1: Crank-Nicolson;  2: implicit Euler.
 struct TmemChunk {
   static constexpr int REGS = 16;
@@ -557,6 +566,39 @@ __device__ __forceinline__ void pipe_setup(const fvm_problem& pr, int64_t p, int
   }
 }
 
+// From the set-up layout to the loop's (see above).  In: (l, kappa) and (P1, P2) in tensor memory, s in sS.
+// Out: (kappa, P1, P2, s") per substitution slot in tensor memory, l in sS.  s" = s kappa_next / kappa with
+// `next` the neighbour towards the middle cell, from the rounded factors in double-double, rounded once.
+// New slot j overwrites old columns that have been read by then: [0,128) is read in full first, and the
+// old (P1, P2) slots 2(j-8), 2(j-8)+1 that new slot j >= 8 covers are <= j.
+__device__ __forceinline__ void pipe_relayout(uint32_t t_lk, uint32_t t_pp, double* sS) {
+  constexpr int N = kPipeN, MID = kPipeMid;
+  double lA[N], kA[N], l_up, unused;
+#pragma unroll 1
+  for (int c = 0; c < N; ++c) tmem_ld_2d(t_lk + pipe_col_lk(c), lA[c], kA[c]);
+  tmem_ld_2d(t_lk + pipe_col_lk(MID) + 4, l_up, unused);
+#pragma unroll 1
+  for (int j = 0; j <= MID; ++j) {
+    const int cl = MID - j, cr = MID + j;
+    double p1l, p2l, p1r = 0.0, p2r = 0.0, s2l = 0.0, s2r = 0.0;
+    tmem_ld_2d(t_pp + pipe_col_pp(cl), p1l, p2l);
+    if (j > 0) {
+      tmem_ld_2d(t_pp + pipe_col_pp(cr), p1r, p2r);
+      s2l = dd_round(dd_div(two_prod(sS[cl * 32], kA[cl + 1]), dd_make(kA[cl])));
+      s2r = dd_round(dd_div(two_prod(sS[cr * 32], kA[cr - 1]), dd_make(kA[cr])));
+    }
+    const uint32_t t = t_lk + 16 * j;
+    tmem_st_2d(t, kA[cl], p1l); tmem_st_2d(t + 4, p2l, s2l);
+    tmem_st_2d(t + 8, kA[cr], p1r); tmem_st_2d(t + 12, p2r, s2r);
+    tmem_wait_st();
+  }
+  __syncwarp();
+#pragma unroll 1
+  for (int c = 0; c < N; ++c) sS[c * 32] = lA[c];
+  sS[0] = l_up;                                     // cell 0 starts its chain: its own l is never read
+  __syncwarp();
+}
+
 // EXT: 0 = constant coefficients; 1 = per-step boundary-flux scales; 2 = scales and runs of different time
 // steps (the run loop costs the steady-state loop its uniform registers, ~8 %, so it has its own instance).
 template <int MODE, int EXT_>
@@ -565,19 +607,21 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
                        int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt, FusedExtras ex) {
   constexpr int C = 32, N = kPipeN, MID = kPipeMid;
   constexpr bool EXT = EXT_ >= 1, RUNS = EXT_ == 2;
-  constexpr int IT = 2;                              // slots per chunk (.x16): a slot = a left and a right cell
+  constexpr int IT = 2;                              // slots per elimination group: a slot = a left and a right cell
   constexpr int NCH = (MID + 1) / IT;                // 16 slots: 15 cell pairs and the middle cell
   using TC = TmemChunk;
-  // shared-memory slots (per lane) of the constants of a step, in the place s occupied during set-up
-  enum { K_OML = 0, K_OMR = 1, K_AL = 2, K_GA = 7, K_INVD = 12, K_SLO = 13, K_SUP = 14, K_BSEP = 15, K_BFIRST = 16 };
+  // shared-memory slots (per lane) of the constants of a step
+  enum { K_OML = 0, K_OMR = 1, K_AL = 2, K_GA = 7, K_INVD = 12, K_SLO = 13, K_SUP = 14, K_BSEP = 15, K_BFIRST = 16,
+         K_SLOTS = 17 };
   extern __shared__ double smem[];
   __shared__ uint32_t tmem_base_slot;
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps = blockDim.x >> 5;
-  double* sS = smem + (size_t)warp * (3 * N * 32) + lane;        // s during set-up, then the constants; V; U
+  double* sS = smem + (size_t)warp * ((3 * N + K_SLOTS) * 32) + lane;   // s during set-up, then l; V; U; constants
   double* sv = sS + N * 32;
   double* su = sv + N * 32;
+  double* sK = su + N * 32;
   const int64_t J = pr.J;
   const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
 
@@ -587,7 +631,7 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
   tmem_fence_after_sync();
   const uint32_t tmem_base = tmem_base_slot;
   const uint32_t t_lk = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(warp >> 2) * 256;
-  const uint32_t t_pp = t_lk + 128;                  // (P1, P2) pairs in substitution order
+  const uint32_t t_pp = t_lk + 128;                  // set-up only: (P1, P2) pairs in substitution order
 
   const int64_t n_ck_total = (ckpt != nullptr && ckpt_every > 0) ? nsteps / ckpt_every : 0;
   for (int64_t p = (int64_t)blockIdx.x * warps + warp; p < pr.P; p += (int64_t)gridDim.x * warps) {
@@ -602,22 +646,28 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       dt_run = ex.dt_hist[s0 * ex.dt_ss + p * ex.dt_ps];
     }
     // ------------------------------------------------------------------ set-up (once per run)
-    double sr[N];                                    // sr[MID] is unused (the middle cell has no substitution link)
     {
       PipeConsts Kc;
       pipe_setup(pr, p, lane, dt_run, theta, t_lk, t_pp, sS, sv, su, Kc);
+      pipe_relayout(t_lk, t_pp, sS);
+      // the per-lane constants of a step live in shared memory, so that the registers they would
+      // occupy can hold the second tensor-memory chunk buffer
+      sK[K_OML * 32] = Kc.om_l; sK[K_OMR * 32] = Kc.om_r;
 #pragma unroll
-      for (int c = 0; c < N; ++c) sr[c] = sS[c * 32];
+      for (int l2 = 0; l2 < 5; ++l2) { sK[(K_AL + l2) * 32] = Kc.al[l2]; sK[(K_GA + l2) * 32] = Kc.ga[l2]; }
+      sK[K_INVD * 32] = Kc.invD; sK[K_SLO * 32] = Kc.slo; sK[K_SUP * 32] = Kc.sup;
+      sK[K_BSEP * 32] = Kc.bsep; sK[K_BFIRST * 32] = Kc.bfirst;
       __syncwarp();
-      // s is in registers now: its shared-memory slots take the per-lane constants of a step, so
-      // that the registers they would occupy can hold the second tensor-memory chunk buffer
-      sS[K_OML * 32] = Kc.om_l; sS[K_OMR * 32] = Kc.om_r;
-#pragma unroll
-      for (int l2 = 0; l2 < 5; ++l2) { sS[(K_AL + l2) * 32] = Kc.al[l2]; sS[(K_GA + l2) * 32] = Kc.ga[l2]; }
-      sS[K_INVD * 32] = Kc.invD; sS[K_SLO * 32] = Kc.slo; sS[K_SUP * 32] = Kc.sup;
-      sS[K_BSEP * 32] = Kc.bsep; sS[K_BFIRST * 32] = Kc.bfirst;
     }
-    auto K = [&](int slot) { return sS[slot * 32]; };
+    auto K = [&](int slot) { return sK[slot * 32]; };
+    // l of cell c (c = MID: l_down; slot 0: l_up of the middle cell): the left chain's and the first NRL of the
+    // right chain's from registers, the others from shared memory (all from shared memory, the pipe that also
+    // carries the shuffles is 70 % busy and the step 2 % slower; NRL >= 4 spills inside the loop)
+    constexpr int NRL = 0;
+    double lreg[MID + 1 + NRL];
+#pragma unroll
+    for (int c = 1; c <= MID + NRL; ++c) lreg[c] = sS[c * 32];
+    auto Lc = [&](int c) { return (c >= 1 && c <= MID + NRL) ? lreg[c] : sS[c * 32]; };
     // x' = yhat - c x at a separator
     auto from_yhat = [&](double ys, double x_old) {
       return (MODE == 2) ? ys : ((MODE == 1) ? ys - x_old : fma(-cth, x_old, ys));
@@ -632,31 +682,23 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
 
     // ------------------------------------------------------------------ time loop
     uint32_t ra[TC::REGS], rb[TC::REGS];
-    // t_c of one cell (see the header): MODE 1 takes g, g_next as they are, MODE 0 their c-multiples
-    auto tval = [&](double hk_minus, double s, double cg_next) {
-      return (MODE == 2) ? hk_minus : fma(-s, cg_next, hk_minus);
-    };
+    double hh[N];                                    // h of the step being swept (hh[MID] is unused)
     // One step on w[0..N-1] in place; the cells outside the block that the end cells couple to
     // contribute oldL0 / oldR0 (first step of a segment only).  With PIPE the five PCR levels of
-    // the previous step's separator system (rr in) are issued between the elimination chunks, the
+    // the previous step's separator system (rr in) are issued between the elimination groups, the
     // new separator values xs (and xsl = the left neighbour's) follow as soon as the last level is
-    // done, and the substitution applies the delayed correction link by link.  base returns the
+    // done, and the substitution applies the delayed correction cell by cell.  base returns the
     // part of the next reduced right-hand side that does not depend on this step's sweeps.
-    auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, uint32_t next_region, double rr,
-                      double& xs, double& base, double sc) {
+    auto sweeps = [&](auto pipe_tag, double oldL0, double oldR0, double rr, double& xs, double& base, double sc) {
       constexpr bool PIPE = decltype(pipe_tag)::value;
-      double hL = 0.0, hR = 0.0, zM = 0.0;
-      double cgL = 0.0, cgR = 0.0;                    // MODE 0: c * g of the cell the chain is at
+      double hL = 0.0, hR = 0.0, uM = 0.0;
       double xsl = 0.0;
 #pragma unroll
       for (int k = 0; k < NCH; ++k) {
-        uint32_t* cur = (k & 1) ? rb : ra;
-        // prefetch of the next chunk, pinned ahead of this chunk's arithmetic (chunk_ld_after)
-        if (k == 0) { TC::wait(ra); chunk_ld_after(t_lk + 8 * IT, rb, w[0]); }
-        else if (k & 1) { TC::wait(rb); chunk_ld_after(k + 1 < NCH ? t_lk + 8 * IT * (k + 1) : next_region, ra, hL); }
-        else            { TC::wait(ra); chunk_ld_after(k + 1 < NCH ? t_lk + 8 * IT * (k + 1) : next_region, rb, hL); }
-        // One PCR level per chunk.  Warps issue in order, so the level's shuffles are issued HERE and
-        // their consumer sits after the chunk's cell work: the ~26-cycle shuffle latency is covered.
+        // the first two substitution chunks are fetched behind the last elimination group
+        if (k == NCH - 1) { chunk_ld_after(t_lk, ra, hL); chunk_ld_after(t_lk + 16, rb, hR); }
+        // One PCR level per group.  Warps issue in order, so the level's shuffles are issued HERE and
+        // their consumer sits after the group's cell work: the ~26-cycle shuffle latency is covered.
         double rm = 0.0, rp = 0.0, fa = 0.0, fg = 0.0;
         const bool lvl = PIPE && k < 5;
         if (lvl) { rm = shfl_up(rr, 1 << k); rp = shfl_dn(rr, 1 << k); fa = K(K_AL + k); fg = K(K_GA + k); }
@@ -668,85 +710,85 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
           if (i < MID) {
             {
               const int c = i;                        // left cell, eliminated top-down
-              const double l = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1);
-              const double gc = w[c], gn = w[c + 1];
+              const double gc = w[c];
               if (i == 0) {
                 hL = EXT ? fma(K(K_BFIRST), sc, gc) : gc + K(K_BFIRST);
                 if (!PIPE) hL = fma(-K(K_OML), oldL0, hL);
-                if (MODE == 0) cgL = cth * gc;
               } else {
-                hL = fma(-l, hL, gc);
+                hL = fma(-Lc(c), hL, gc);
               }
-              const double cg = (MODE == 0) ? cgL : gc, cgn = (MODE == 0) ? cth * gn : gn;
-              w[c] = tval(MODE == 2 ? hL * kap : fma(hL, kap, -cg), sr[c], cgn);
-              cgL = cgn;
+              hh[c] = hL;
+              if (MODE == 0) w[c] = cth * gc;
             }
             {
               const int c = N - 1 - i;                // right cell, eliminated bottom-up
-              const double l = chunk_dbl(cur, 4 * ii + 2), kap = chunk_dbl(cur, 4 * ii + 3);
-              const double gc = w[c], gp = w[c - 1];
+              const double gc = w[c];
               if (i == 0) {
                 hR = gc;
                 if (!PIPE) hR = fma(-K(K_OMR), oldR0, hR);
-                if (MODE == 0) cgR = cth * gc;
               } else {
-                hR = fma(-l, hR, gc);
+                hR = fma(-Lc(c), hR, gc);
               }
-              const double cg = (MODE == 0) ? cgR : gc, cgp = (MODE == 0) ? cth * gp : gp;
-              w[c] = tval(MODE == 2 ? hR * kap : fma(hR, kap, -cg), sr[c], cgp);
-              cgR = cgp;
+              hh[c] = hR;
+              if (MODE == 0) w[c] = cth * gc;
             }
           } else {
-            // the middle cell takes both sweeps: h = g - l_dn h_{m-1} - l_up h_{m+1};  z = h kappa - c g
-            const double l_dn = chunk_dbl(cur, 4 * ii), kap = chunk_dbl(cur, 4 * ii + 1), l_up = chunk_dbl(cur, 4 * ii + 2);
+            // the middle cell takes both sweeps: h = g - l_dn h_{m-1} - l_up h_{m+1}
             const double gc = w[MID];
-            const double hM = fma(-l_up, hR, fma(-l_dn, hL, gc));
-            zM = (MODE == 2) ? hM * kap : ((MODE == 1) ? fma(hM, kap, -gc) : fma(hM, kap, -cth * gc));
+            uM = fma(-Lc(0), hR, fma(-Lc(MID), hL, gc));
+            if (MODE == 0) w[MID] = cth * gc;
           }
         }
         if (lvl) rr = fma(fg, rp, fma(fa, rm, rr));
       }
-      if (PIPE) {
-        // substitution outwards with the delayed correction riding on every link: the chain runs on
-        // the uncorrected values zL / zR, the corrected ones go to w
-        double zL = zM, zR = zM;
+      // substitution outwards from the middle on u = yhat / kappa, one chunk (kappa, P1, P2, s" of a left
+      // and a right cell) per link; z = kappa u - c g and the delayed correction follow off the chain
+      double uL = uM, uR = uM;
 #pragma unroll
-        for (int k = 0; k < NCH; ++k) {
-          uint32_t* cur = (k & 1) ? rb : ra;
-          if (k & 1) { TC::wait(rb); chunk_ld_after(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_lk, ra, zL); }
-          else       { TC::wait(ra); chunk_ld_after(k + 1 < NCH ? t_pp + 8 * IT * (k + 1) : t_lk, rb, zL); }
-          // links first, then the xsl products of the whole chunk, then the xs products: consecutive
-          // FMAs that share an operand can take it from the operand-reuse cache instead of the
-          // register file, whose bandwidth is what bounds these loops (fp64_operands.cu)
-          double zl[IT], zr[IT];
+      for (int jj = 0; jj < NCH; ++jj) {              // two links (slots 2jj in ra, 2jj+1 in rb) per group
+        TC::wait(ra);
+        // chains first, then kappa u - c g, then the xsl products of the group, then the xs products:
+        // consecutive FMAs that share an operand can take it from the operand-reuse cache instead of
+        // the register file, whose bandwidth is what bounds these loops (fp64_operands.cu)
+        double al[IT], ar[IT];
+#pragma unroll
+        for (int ii = 0; ii < IT; ++ii) {
+          const uint32_t* cur = ii ? rb : ra;
+          const int j = jj * IT + ii;
+          if (j == 0) { al[ii] = uM; ar[ii] = 0.0; continue; }
+          uL = fma(-chunk_dbl(cur, 3), uL, hh[MID - j]); al[ii] = uL;
+          uR = fma(-chunk_dbl(cur, 7), uR, hh[MID + j]); ar[ii] = uR;
+        }
+#pragma unroll
+        for (int ii = 0; ii < IT; ++ii) {
+          const uint32_t* cur = ii ? rb : ra;
+          const int j = jj * IT + ii;
+          al[ii] = (MODE == 2) ? chunk_dbl(cur, 0) * al[ii] : fma(chunk_dbl(cur, 0), al[ii], -w[MID - j]);
+          if (j > 0) ar[ii] = (MODE == 2) ? chunk_dbl(cur, 4) * ar[ii] : fma(chunk_dbl(cur, 4), ar[ii], -w[MID + j]);
+        }
+        if (PIPE) {
 #pragma unroll
           for (int ii = 0; ii < IT; ++ii) {
-            const int j = k * IT + ii;
-            if (j == 0) { zl[ii] = zM; zr[ii] = 0.0; continue; }
-            const int cl = MID - j, cr = MID + j;
-            zL = fma(-sr[cl], zL, w[cl]); zl[ii] = zL;
-            zR = fma(-sr[cr], zR, w[cr]); zr[ii] = zR;
+            const uint32_t* cur = ii ? rb : ra;
+            al[ii] = fma(chunk_dbl(cur, 1), xsl, al[ii]);
+            if (jj * IT + ii > 0) ar[ii] = fma(chunk_dbl(cur, 5), xsl, ar[ii]);
           }
 #pragma unroll
           for (int ii = 0; ii < IT; ++ii) {
-            const int j = k * IT + ii;
-            zl[ii] = fma(chunk_dbl(cur, 4 * ii), xsl, zl[ii]);
-            if (j > 0) zr[ii] = fma(chunk_dbl(cur, 4 * ii + 2), xsl, zr[ii]);
-          }
-#pragma unroll
-          for (int ii = 0; ii < IT; ++ii) {
-            const int j = k * IT + ii;
-            w[MID - j] = fma(chunk_dbl(cur, 4 * ii + 1), xs, zl[ii]);
-            if (j > 0) w[MID + j] = fma(chunk_dbl(cur, 4 * ii + 3), xs, zr[ii]);
+            const uint32_t* cur = ii ? rb : ra;
+            al[ii] = fma(chunk_dbl(cur, 2), xs, al[ii]);
+            if (jj * IT + ii > 0) ar[ii] = fma(chunk_dbl(cur, 6), xs, ar[ii]);
           }
         }
-      } else {
-        w[MID] = zM;
 #pragma unroll
-        for (int j = 1; j <= MID; ++j) {
-          const int cl = MID - j, cr = MID + j;
-          w[cl] = fma(-sr[cl], w[cl + 1], w[cl]);
-          w[cr] = fma(-sr[cr], w[cr - 1], w[cr]);
+        for (int ii = 0; ii < IT; ++ii) {
+          const int j = jj * IT + ii;
+          w[MID - j] = al[ii];
+          if (j > 0) w[MID + j] = ar[ii];
+        }
+        if (jj + 1 < NCH) {
+          chunk_ld_after(t_lk + 16 * (IT * jj + 2), ra, uL);
+          chunk_ld_after(t_lk + 16 * (IT * jj + 3), rb, uR);
         }
       }
     };
@@ -770,7 +812,6 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
     const double* const hist_last = EXT ? hist + (nsteps - 1 - s_glob) * hist_step : nullptr;
     auto advance = [&]() { if (hist != hist_last) hist += hist_step; };
     int64_t remaining = run_len;
-    TC::ld(t_lk, ra);                               // first (l, kappa) chunk
     while (remaining > 0) {
       // steps until the true state is needed again: the next checkpoint or the end of the run
       int64_t L = remaining;
@@ -788,13 +829,13 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       double g0_old = fma(su[0], xs, fma(sv[0], wl, w[0]));
       double gl_old = fma(su[(N - 1) * 32], xs, fma(sv[(N - 1) * 32], wl, w[N - 1]));
       double base = fma(xs, rth, EXT ? K(K_BSEP) * sc : K(K_BSEP));
-      sweeps(std::false_type{}, wl, xs, t_lk, 0.0, xs, base, sc);
+      sweeps(std::false_type{}, wl, xs, 0.0, xs, base, sc);
       double rr = reduced_rhs(base, g0_old, gl_old);
       // -------- pipelined steps: PCR of step n overlaps the sweeps of step n+1
       for (int64_t i = 1; i < L; ++i) {
         if (EXT) { sc = sc_n; advance(); sc_n = *hist; }
         g0_old = w[0]; gl_old = w[N - 1];
-        sweeps(std::true_type{}, 0.0, 0.0, t_pp, rr, xs, base, sc);
+        sweeps(std::true_type{}, 0.0, 0.0, rr, xs, base, sc);
         rr = reduced_rhs(base, g0_old, gl_old);
       }
       // -------- end of the segment: finish the last step and materialise the true state
@@ -816,7 +857,6 @@ fused_tmem_pipe_kernel(fvm_problem pr, const double* __restrict__ dt, double the
       if (n_ck_total > 0 && s_glob % ckpt_every == 0 && s_glob / ckpt_every <= n_ck_total)
         store_state<C>(ckpt + ((s_glob / ckpt_every - 1) * pr.P + p) * J, J, lane, w);
     }
-    TC::wait(ra);                                   // drain the prefetch of the step that never comes
     store_state<C>(w_io + p * J, J, lane, w);
     __syncwarp();
    }
@@ -868,7 +908,7 @@ template <int MODE, int EXT>
 static int launch_fused_tmem(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps,
                              int64_t ckpt_every, double* w, double* ckpt, const FusedExtras& ex, cudaStream_t stream) {
   constexpr int warps = kFusedThreads / 32;
-  constexpr size_t smem = (size_t)warps * 3 * 31 * 32 * sizeof(double);
+  constexpr size_t smem = (size_t)warps * (3 * 31 + 17) * 32 * sizeof(double);   // s/l, V, U and the constants
   int sms = 0, max_smem = 0;
   int st = device_limits(sms, max_smem);
   if (st) return st;
