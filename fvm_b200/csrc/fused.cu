@@ -573,11 +573,13 @@ __device__ __forceinline__ void pipe_setup(const fvm_problem& pr, int64_t p, int
 // old (P1, P2) slots 2(j-8), 2(j-8)+1 that new slot j >= 8 covers are <= j.
 __device__ __forceinline__ void pipe_relayout(uint32_t t_lk, uint32_t t_pp, double* sS) {
   constexpr int N = kPipeN, MID = kPipeMid;
+  // fully unrolled: lA, kA stay in registers (with run-time indices they go to local memory, 1 GB of
+  // DRAM writes per cfg 3 launch)
   double lA[N], kA[N], l_up, unused;
-#pragma unroll 1
+#pragma unroll
   for (int c = 0; c < N; ++c) tmem_ld_2d(t_lk + pipe_col_lk(c), lA[c], kA[c]);
   tmem_ld_2d(t_lk + pipe_col_lk(MID) + 4, l_up, unused);
-#pragma unroll 1
+#pragma unroll
   for (int j = 0; j <= MID; ++j) {
     const int cl = MID - j, cr = MID + j;
     double p1l, p2l, p1r = 0.0, p2r = 0.0, s2l = 0.0, s2r = 0.0;
@@ -593,8 +595,8 @@ __device__ __forceinline__ void pipe_relayout(uint32_t t_lk, uint32_t t_pp, doub
     tmem_wait_st();
   }
   __syncwarp();
-#pragma unroll 1
-  for (int c = 0; c < N; ++c) sS[c * 32] = lA[c];
+#pragma unroll
+  for (int c = 1; c < N; ++c) sS[c * 32] = lA[c];
   sS[0] = l_up;                                     // cell 0 starts its chain: its own l is never read
   __syncwarp();
 }
