@@ -308,8 +308,9 @@ def long_system_legs(world, rank, local, dev, peaks, peak_src, group):
            "single_gpu": {"cells": Jr, "ms_per_theta_step": ms1, "steps_timed": n1, "clocks": clocks1,
                           "cell_updates_per_s": Jr / (ms1 * 1e-3),
                           "achieved": HBM_B_PER_CELL_UPDATE_SPIKE * Jr / (ms1 * 1e-3) / 1e9},
-           "traffic": ncu_traffic("r01_spike_tile_solve.summary.txt"),
-           "traffic_note": "tile_solve_kernel only, one launch at 2^26 cells (algorithmic 40 B x 2^26 = 2.68e9)"}
+           "traffic": ncu_traffic("r02b_tile_solve_cfg5.summary.txt"),
+           "traffic_note": "tile_solve_kernel only, one launch at 2^27 cells: algorithmic 40 B x 2^27 = 5.37e9, plus 16 B of "
+                           "spike vectors for the 34 % of the cells inside the spike extents = 0.73e9"}
     # ---- cfg 5 proper: one mesh over all ranks
     J = world * Jr
     j0, j1 = plan_partition(J, T, world)["ranges"][rank]
@@ -328,8 +329,10 @@ def long_system_legs(world, rank, local, dev, peaks, peak_src, group):
                 "cell_updates_per_s": J / (msN * 1e-3), "achieved": gbs, "frac": gbs / peaks["hbm_gbs"],
                 "achieved_note": "per GPU: 40 B x 2^27 cells / ms_per_theta_step (whole step incl. the collective)",
                 "weak_efficiency_vs_n1": ms1 / msN,
-                "collective": {"name": "ncclAllGather (torch.distributed.all_gather_into_tensor), 4 doubles per rank "
-                                       "and step (fvm_b200/partitioned.py: _step_rank_level)",
+                "collective": {"name": "ncclAllGather (torch.distributed.all_gather_into_tensor), 4 doubles per block of the "
+                                       "separator system and step: %d blocks of %d separators per rank, %d B per rank "
+                                       "(fvm_b200/partitioned.py: _step_rank_level)"
+                                       % (m.B, m.nt // m.B, 32 * m.B),
                                "us_per_step": gather_us,
                                "share_of_step": None if gather_us is None else gather_us * 1e-3 / msN}})
     # ---- residual of ONE theta step at full size: || A w_new - B w_old ||_inf / || B w_old ||_inf

@@ -47,7 +47,7 @@ struct Reduced {
 // that a step only applies them to its right-hand side (pcr_solve).  K: any struct with al, ga, invD.
 template <class KT>
 __device__ __forceinline__ void pcr_factor_dd(int lane, dd RL, dd RD, dd RU, KT& K) {
-#pragma unroll 1
+#pragma unroll                                      // K.al[l], K.ga[l] with a run-time l would put K in local memory
   for (int l = 0; l < 5; ++l) {
     const int s = 1 << l;
     const bool hm = lane >= s, hp = lane + s < 32;

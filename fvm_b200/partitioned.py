@@ -2,7 +2,7 @@
 with the cells split in contiguous slabs over the ranks of a torch.distributed group
 (BASELINE.json cfg 4 and cfg 5).  Drives variant 3 of the C-ABI
 (fvm_spike_*): tile-local Thomas solves, a reduced tridiagonal over the tile separators (itself
-partitioned over the ranks, ONE all-gather of 4 doubles per rank and step), and a spike correction
+partitioned into blocks, ONE all-gather of 4 doubles per block and step across ranks), and a spike correction
 near the tile edges.  A step has no right-hand side (w' = A^-1(w/theta + beta) - c w), so a tile
 needs nothing from its neighbours and the state carries no ghost cells.
 
