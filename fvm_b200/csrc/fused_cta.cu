@@ -6,12 +6,14 @@
 // step WITHOUT a right-hand side as the other kernels, A^-1 B = A^-1/theta - c I) live in shared
 // memory in tiled order ([c][t]: conflict-free), for CPT = 8 also in registers.  A step is
 //   h_c = g_c + theta*beta_c - l_c h_{c-1}        forward recurrence over all TPB*CPT cells
-//   t_c = h_c kappa_c - c g_c - c s_c g_{c+1}
-//   z_c = t_c - s_c z_{c+1}                        backward recurrence;  w' = z
-// with both recurrences as CTA-wide scans of affine maps x -> A x + B.  The A halves of those maps are
-// products of l (of s) and do not change from step to step: they are scanned ONCE at set-up (in
-// double-double, rounded once), so a step only scans the B halves -- one shuffle and one FMA per level,
-// one barrier per scan (every warp folds the warp totals itself), three barriers per step in all.
+//   u_c = h_c - s"_c u_{c+1}                       backward recurrence on u = yhat / kappa,
+//                                                  s"_c = s_c kappa_{c+1} / kappa_c
+//   w'_c = kappa_c u_c - c g_c
+// (five operations per cell, and no cell needs its neighbour's old value) with both recurrences as
+// CTA-wide scans of affine maps x -> A x + B.  The A halves of those maps are products of l (of s") and
+// do not change from step to step: they are scanned ONCE at set-up (in double-double, rounded once), so
+// a step only scans the B halves -- one shuffle and one FMA per level, one barrier per scan (every warp
+// folds the warp totals itself), two barriers per step in all.
 //
 // Set-up inside the launch: rows of A (fvm_device.cuh), then the pivot recurrence
 // s_j = A_j,j+1 / (A_jj - A_j,j-1 s_{j-1}) in double-double.  It is a Moebius recurrence, i.e. a product
@@ -99,9 +101,11 @@ __device__ __forceinline__ dd scan_consts(dd a_t, ScanConsts& K) {
 
 // One step's scan of the B halves: b_t = this thread's value with a zero carry-in.  Returns the value
 // entering this thread.  tot: shared array of NW doubles for this direction (warp totals of B);
-// aw: shared array of the warps' A totals.  ONE barrier.
+// k2: the step-invariant halves of the SECOND level (the scan over the warp totals, lane i standing for
+// warp i, identity beyond NW), [6][32] in shared memory: every warp scans the totals itself, in five
+// shuffle levels instead of a serial fold over up to NW-1 warps.  ONE barrier.
 template <int NW, bool REVERSE>
-__device__ __forceinline__ double scan_values(double b_t, const ScanConsts& K, double* tot, const double* aw) {
+__device__ __forceinline__ double scan_values(double b_t, const ScanConsts& K, double* tot, const double* k2) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int pos = REVERSE ? 31 - lane : lane;
   double inc = b_t;
@@ -115,19 +119,24 @@ __device__ __forceinline__ double scan_values(double b_t, const ScanConsts& K, d
   if (pos == 0) exc = 0.0;
   if (pos == 31) tot[warp] = inc;
   __syncthreads();
-  double cw = 0.0;                                  // value entering this warp: fold the warps before it
-  if (!REVERSE) {
-    for (int i = 0; i < warp; ++i) cw = fma(aw[i], cw, tot[i]);
-  } else {
-    for (int i = NW - 1; i > warp; --i) cw = fma(aw[i], cw, tot[i]);
+  double inc2 = (lane < NW) ? tot[lane] : 0.0;
+  li = 0;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1, ++li) {
+    const double o = REVERSE ? __shfl_down_sync(kAllLanes, inc2, d) : __shfl_up_sync(kAllLanes, inc2, d);
+    if (pos >= d) inc2 = fma(k2[li * 32 + lane], o, inc2);
   }
+  // value entering warp `warp` = inclusive result of the warp before it in scan order
+  const int src = REVERSE ? warp + 1 : warp - 1;
+  double cw = __shfl_sync(kAllLanes, inc2, src & 31);
+  if (REVERSE ? (warp == NW - 1) : (warp == 0)) cw = 0.0;
   return fma(K.exc, cw, exc);
 }
 
 }  // namespace
 
 template <int TPB, int CPT, int MODE>
-__global__ void __launch_bounds__(TPB, 1)
+__global__ void __launch_bounds__(TPB, (TPB == 256 && CPT == 16) ? 2 : 1)
 fused_cta_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
                  int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
   constexpr int T = TPB * CPT;
@@ -137,17 +146,19 @@ fused_cta_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, in
   double* sl = smem;                 // [c*TPB + t]: rows of A (lo, di, up) during set-up, then l, kappa, s
   double* sk = sl + T;
   double* ss = sk + T;
-  double* sfirst = ss + T;           // [TPB] first cell of every thread
-  double* totf = sfirst + TPB;       // [NW] warp totals of the forward scan (B halves), per step
+  double* totf = ss + T;             // [NW] warp totals of the forward scan (B halves), per step
   double* totb = totf + NW;          // [NW] ... of the backward scan
   double* awf = totb + NW;           // [NW] warp totals of the A halves, fixed
   double* awb = awf + NW;            // [NW]
-  double* sbeta = awb + NW;          // [2] theta*beta[0], theta*beta[J-1]
+  double* k2f = awb + NW;            // [6][32] second-level scan constants, forward
+  double* k2b = k2f + 6 * 32;        // [6][32] ... backward
+  double* sbeta = k2b + 6 * 32;      // [2] theta*beta[0], theta*beta[J-1]
   double* sscr = sbeta + 2;          // [max(8*NW, 2*TPB)] set-up scratch: matrix totals of the warps, then 1/pivot of every thread's last cell
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t J = pr.J;
   const double rth = 1.0 / theta, cth = (1.0 - theta) / theta;
   auto cmul = [&](double x) { return (MODE == 1) ? x : cth * x; };
+  (void)rth;
 
   for (int64_t p = blockIdx.x; p < pr.P; p += gridDim.x) {
     // ---------------------------------------------------------------- set-up: rows of A
@@ -230,6 +241,15 @@ fused_cta_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, in
       sscr[2 * tid] = inv_prev.hi; sscr[2 * tid + 1] = inv_prev.lo;
       __syncthreads();
       if (tid > 0) sl[tid] = dd_round(dd_mul_d(dd_make(sscr[2 * (tid - 1)], sscr[2 * (tid - 1) + 1]), lo_first));
+      // s -> s" = s kappa_next / kappa (the substitution runs on u = yhat / kappa), from the rounded factors
+      // in double-double, rounded once; kappa_next of a thread's last cell is the next thread's first
+#pragma unroll
+      for (int c = 0; c < CPT; ++c) {
+        const int o = c * TPB + tid;
+        const bool last = (c == CPT - 1);
+        const double kn = !last ? sk[o + TPB] : (tid < TPB - 1 ? sk[tid + 1] : 0.0);
+        ss[o] = dd_round(dd_div(two_prod(ss[o], kn), dd_make(sk[o])));
+      }
       // products of the ROUNDED factors, as the sweeps apply them
 #pragma unroll
       for (int c = 0; c < CPT; ++c) {
@@ -248,6 +268,16 @@ fused_cta_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, in
       if (lane == 0) awb[warp] = dd_round(tb);
     }
     __syncthreads();
+    if (warp == 0) {                                         // second level: scan over the warps' A totals
+      ScanConsts K2;
+      scan_consts<false>(dd_make(lane < NW ? awf[lane] : 1.0), K2);
+#pragma unroll
+      for (int i = 0; i < 5; ++i) k2f[i * 32 + lane] = K2.lvl[i];
+      scan_consts<true>(dd_make(lane < NW ? awb[lane] : 1.0), K2);
+#pragma unroll
+      for (int i = 0; i < 5; ++i) k2b[i * 32 + lane] = K2.lvl[i];
+    }
+    __syncthreads();
     const double bfirst = sbeta[0], blast = sbeta[1];
     const int c_last = (J - 1 >= jl0 && J - 1 < jl0 + CPT) ? (int)(J - 1 - jl0) : -1;
     auto L = [&](int c) { return REGC ? lreg[c] : sl[c * TPB + tid]; };
@@ -264,34 +294,29 @@ fused_cta_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, in
     // ---------------------------------------------------------------- time loop
     int64_t until_ckpt = ckpt_every, n_ckpt = 0;
     for (int64_t n = 0; n < nsteps; ++n) {
-      sfirst[tid] = w[0];
-      __syncthreads();
-      const double g_edge = (tid < TPB - 1) ? sfirst[tid + 1] : 0.0;   // first cell of the next thread (old state)
-      double r[CPT], h[CPT];
+      double h[CPT];
       double prev = 0.0;
 #pragma unroll
       for (int c = 0; c < CPT; ++c) {                        // forward recurrence with a zero carry-in
         double rc = w[c];
         if (c == c_last) rc += blast;
         if (c == 0 && tid == 0) rc += bfirst;
-        r[c] = rc;
+        h[c] = rc;
         prev = fma(-L(c), prev, rc);
       }
-      prev = scan_values<NW, false>(prev, Kf, totf, awf);
+      prev = scan_values<NW, false>(prev, Kf, totf, k2f);
 #pragma unroll
-      for (int c = 0; c < CPT; ++c) { prev = fma(-L(c), prev, r[c]); h[c] = prev; }
-#pragma unroll
-      for (int c = 0; c < CPT; ++c) {                        // t over h
-        const double gn = (c + 1 < CPT) ? w[c + 1 < CPT ? c + 1 : c] : g_edge;
-        const double kap = sk[c * TPB + tid];
-        h[c] = (MODE == 2) ? h[c] * kap : fma(-S(c), cmul(gn), fma(h[c], kap, -cmul(w[c])));
-      }
+      for (int c = 0; c < CPT; ++c) { prev = fma(-L(c), prev, h[c]); h[c] = prev; }
       double nxt = 0.0;
 #pragma unroll
-      for (int c = CPT - 1; c >= 0; --c) nxt = fma(-S(c), nxt, h[c]);     // backward recurrence, zero carry-in
-      nxt = scan_values<NW, true>(nxt, Kb, totb, awb);
+      for (int c = CPT - 1; c >= 0; --c) nxt = fma(-S(c), nxt, h[c]);     // backward recurrence on u, zero carry-in
+      nxt = scan_values<NW, true>(nxt, Kb, totb, k2b);
 #pragma unroll
-      for (int c = CPT - 1; c >= 0; --c) { nxt = fma(-S(c), nxt, h[c]); w[c] = nxt; }
+      for (int c = CPT - 1; c >= 0; --c) {
+        nxt = fma(-S(c), nxt, h[c]);
+        const double kap = sk[c * TPB + tid];
+        w[c] = (MODE == 2) ? kap * nxt : fma(kap, nxt, -cmul(w[c]));
+      }
 
       if (ckpt != nullptr && ckpt_every > 0 && --until_ckpt == 0) {
         until_ckpt = ckpt_every;
@@ -312,7 +337,7 @@ static int launch_cta(const fvm_problem& pr, const double* dt, double theta, int
                       double* w, double* ckpt, cudaStream_t stream) {
   constexpr int NW = TPB / 32;
   constexpr size_t scr = (8 * NW > 2 * TPB) ? 8 * NW : 2 * TPB;
-  constexpr size_t smem = (size_t)(3 * TPB * CPT + TPB + 4 * NW + 2 + scr) * sizeof(double);
+  constexpr size_t smem = (size_t)(3 * TPB * CPT + 4 * NW + 12 * 32 + 2 + scr) * sizeof(double);
   int dev = 0, sms = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return (int)e;
@@ -342,7 +367,15 @@ static int dispatch_cta(const fvm_problem& pr, const double* dt, double theta, i
 int run_fused_cta(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps, int64_t ckpt_every,
                   double* w, double* ckpt, cudaStream_t stream) {
   if (pr.J <= 2048) return dispatch_cta<256, 8>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
-  if (pr.J <= 4096) return dispatch_cta<512, 8>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  if (pr.J <= 4096) {
+    // A step is a chain of latencies (two scans, two barriers): with more systems than SMs, two CTAs of half
+    // the threads share an SM and fill each other's waits; with fewer, the wider CTA finishes a system sooner.
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return (int)cudaGetLastError();
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (pr.P > sms) return dispatch_cta<256, 16>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    return dispatch_cta<512, 8>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  }
   return dispatch_cta<512, 16>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
 }
 

@@ -94,6 +94,32 @@ def test_cta_per_system_sizes(J):
             assert step_error(ck[:, p], want, np.max(np.abs(w0[p]))) < TOL, (J, bc, theta, p)
 
 
+@pytest.mark.parametrize("J", [2100, 4096])
+def test_cta_per_system_more_systems_than_sms(J):
+    """2048 < J <= 4096 with more systems than SMs: the configuration of 256 threads x 16 cells, two CTAs per
+    SM (fused_cta.cu: run_fused_cta).  All BC kinds, three values of theta, a sample against the oracle and
+    every system against the one-thread-per-system kernel."""
+    P = torch.cuda.get_device_properties(0).multi_processor_count + 13
+    rng = np.random.default_rng(J)
+    f = W.graded_faces(J, 50.0)
+    c = 0.5 * (f[1:] + f[:-1])
+    h = np.diff(f)
+    a = rng.uniform(0.5, 2.0, P) * rng.choice([1.0, -1.0], P)
+    d = np.abs(a) * h.max() / rng.uniform(0.3, 1.5, P)
+    k = rng.uniform(2.0, 10.0, P) * h.min()
+    w0 = 0.2 + np.exp(-((c[None, :] - rng.uniform(0.3, 0.7, (P, 1))) / 0.1) ** 2)
+    bcs = [dict(left_flux=0.3, right_flux=-0.2), dict(left_value=1., right_value=0.),
+           dict(left_value=1., right_flux=0.1)]
+    for bc, theta, scheme in zip(bcs, (0.5, 1.0, 0.7), ("exponential", "upwind", "central")):
+        wf, ck = run_gpu(f, a, d, k, scheme, bc, theta, w0, 20, 10, "fused")
+        wt, _ = run_gpu(f, a, d, k, scheme, bc, theta, w0, 20, 10, "thomas")
+        assert np.max(np.abs(wf - wt)) < 1e-12 * np.max(np.abs(wt))
+        for p in (0, P // 2, P - 1):
+            asm = O.assemble(f, a[p], d[p], scheme, **bc)
+            want = O.theta_run_scipy(asm, k[p], theta, w0[p], 20, every=10)
+            assert step_error(ck[:, p], want, np.max(np.abs(w0[p]))) < TOL, (J, bc, theta, p)
+
+
 @pytest.mark.parametrize("variant", VARIANTS)
 def test_cfg2_full_sweep_2000_steps(variant):
     """cfg 2 in full (J=4096, Dirichlet flags, all 29 Peclet numbers x 3 schemes = 87 problems, 2000
