@@ -15,6 +15,7 @@ FVM_OK = 0
 FVM_ERR_INVALID_ARG = -1
 FVM_ERR_UNSUPPORTED = -2
 FVM_ERR_SCRATCH_LIMIT = -3
+FVM_ERR_COLLECTIVE = -4
 CENTRAL, UPWIND, EXPONENTIAL = 0, 1, 2
 SCHEMES = {"central": CENTRAL, "upwind": UPWIND, "exponential": EXPONENTIAL}
 BC_DIRICHLET, BC_ROBIN = 0, 1
@@ -36,6 +37,24 @@ class FvmProblem(ctypes.Structure):
         ("scheme", c_i32), ("left_kind", c_i32), ("right_kind", c_i32),
         ("alpha_left", c_i32), ("alpha_right", c_i32),
         ("left_flux", c_ptr), ("right_flux", c_ptr),
+    ]
+
+
+class FvmSpikePlan(ctypes.Structure):
+    """struct fvm_spike_plan (include/fvm_b200.h)."""
+    _fields_ = [
+        ("n_tiles", c_i64), ("P", c_i64),
+        ("config", c_i32), ("lazy", c_i32), ("has_first_cell", c_i32), ("world", c_i32), ("rank", c_i32),
+        ("extents", c_i32 * 2),
+        ("last_cell_local", c_i64), ("B", c_i64), ("m", c_i64),
+        ("theta", c_dbl), ("w_stride", c_i64),
+        ("p", c_ptr), ("q", c_ptr), ("b", c_ptr), ("Vt", c_ptr), ("Wt", c_ptr), ("sep", c_ptr), ("bends", c_ptr),
+        ("rp", c_ptr), ("rq", c_ptr), ("rinv", c_ptr),
+        ("Vr", c_ptr), ("Wr", c_ptr),
+        ("tp", c_ptr), ("tq", c_ptr), ("tinv", c_ptr), ("cst", c_ptr),
+        ("rs", c_ptr), ("rr", c_ptr), ("g_first", c_ptr),
+        ("gr", c_ptr), ("packet", c_ptr), ("allp", c_ptr),
+        ("xs", c_ptr),
     ]
 
 
@@ -84,6 +103,8 @@ _SIGNATURES = {
     "fvm_spike_rank_top": (ctypes.c_int, [c_i64, c_i64, c_i64, c_i32, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                           c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "fvm_spike_static_max_tiles": (c_i64, []),
+    "fvm_spike_steps": (ctypes.c_int, [ctypes.POINTER(FvmSpikePlan), c_ptr, c_ptr, c_i32, c_i32, c_i64, c_ptr, c_ptr,
+                                       c_ptr]),
     "fvm_spike_local_static": (ctypes.c_int, [c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_i64,
                                               c_dbl, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_ptr, c_ptr]),
     "fvm_spike_reduce_solve": (ctypes.c_int, [c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),

@@ -2,7 +2,7 @@
 #include <cuda_runtime.h>
 #include "../../include/fvm_b200.h"
 
-extern "C" int fvm_version(void) { return 100; }  // 0.1.0
+extern "C" int fvm_version(void) { return 200; }  // 0.2.0
 
 extern "C" const char* fvm_status_string(int status) {
   switch (status) {
@@ -11,6 +11,7 @@ extern "C" const char* fvm_status_string(int status) {
     case FVM_ERR_UNSUPPORTED: return "size not supported by this entry point";
     case FVM_ERR_SCRATCH_LIMIT: return "P * n_tiles exceeds the library's built-in scratch (fvm_spike_static_max_tiles); "
                                        "use fvm_spike_local with a caller-provided rs array";
+    case FVM_ERR_COLLECTIVE: return "the caller's all-gather (fvm_spike_steps) reported an error";
     default: break;
   }
   if (status > 0) return cudaGetErrorString((cudaError_t)status);

@@ -713,3 +713,62 @@ extern "C" int fvm_spike_rank_top(int64_t P, int64_t B, int64_t m, int32_t world
                                                                        gr, Vr, Wr, xs_ext);
   return (int)cudaGetLastError();
 }
+
+// ------------------------------------------------------------------------------------------
+// fvm_spike_steps: a whole time loop in one host call (see the header).  Only sequences the entry
+// points above on the caller's stream; nothing is allocated, nothing synchronises.
+extern "C" int fvm_spike_steps(const fvm_spike_plan* pl, double* w0, double* w1, int32_t cur, int32_t pending,
+                               int64_t nsteps, fvm_allgather_fn allgather, void* comm, void* stream) {
+  if (!pl || !w0 || !w1 || nsteps < 0 || cur < 0 || cur > 1) return FVM_ERR_INVALID_ARG;
+  if (pl->world < 1 || pl->rank < 0 || pl->rank >= pl->world || pl->B < 1) return FVM_ERR_INVALID_ARG;
+  const bool blocks = pl->B > 1 || pl->world > 1;
+  if (blocks && (pl->B * pl->m != pl->n_tiles || pl->m < 2)) return FVM_ERR_INVALID_ARG;
+  if (blocks && (!pl->Vr || !pl->Wr || !pl->tp || !pl->tq || !pl->tinv || !pl->cst || !pl->gr || !pl->packet || !pl->allp))
+    return FVM_ERR_INVALID_ARG;
+  if (pl->world > 1 && !allgather) return FVM_ERR_INVALID_ARG;
+  if (!pl->xs || !pl->rp || !pl->rq || !pl->rinv) return FVM_ERR_INVALID_ARG;
+  double* w[2] = {w0, w1};
+  const int64_t xs_off = blocks ? 1 : 0, xs_n = blocks ? pl->n_tiles + 1 : pl->n_tiles;
+  for (int64_t i = 0; i < nsteps; ++i) {
+    const double* w_in = w[cur];
+    double* w_out = w[1 - cur];
+    int st;
+    if (pending)
+      st = fvm_spike_local_lazy(pl->n_tiles, pl->P, pl->config, pl->p, pl->q, pl->b, pl->sep, pl->bends,
+                                pl->has_first_cell, pl->last_cell_local, pl->theta, w_in, w_out, pl->w_stride, pl->rs,
+                                pl->rr, pl->n_tiles, pl->g_first, pl->Vt, pl->Wt, pl->xs, xs_off, xs_n, pl->extents,
+                                stream);
+    else
+      st = fvm_spike_local(pl->n_tiles, pl->P, pl->config, pl->p, pl->q, pl->b, pl->sep, pl->bends, pl->has_first_cell,
+                           pl->last_cell_local, pl->theta, w_in, w_out, pl->w_stride, pl->rs, pl->rr, pl->n_tiles,
+                           pl->g_first, stream);
+    if (st) return st;
+    if (!blocks) {
+      st = fvm_spike_reduce_solve(pl->n_tiles, pl->P, pl->rp, pl->rq, pl->rinv, pl->rr, pl->xs, stream);
+      if (st) return st;
+    } else {
+      st = fvm_spike_reduce_solve(pl->m, pl->P * pl->B, pl->rp, pl->rq, pl->rinv, pl->rr, pl->gr, stream);
+      if (st) return st;
+      st = fvm_spike_rank_pack(pl->P, pl->B, pl->m, pl->gr, pl->g_first, pl->packet, stream);
+      if (st) return st;
+      const double* allp = pl->packet;
+      if (pl->world > 1) {
+        const int rc = allgather(pl->packet, pl->allp, (size_t)(pl->P * pl->B * 4), 8 /* ncclDouble */, comm, stream);
+        if (rc != 0) return FVM_ERR_COLLECTIVE;
+        allp = pl->allp;
+      }
+      st = fvm_spike_rank_top(pl->P, pl->B, pl->m, pl->world, pl->rank, allp, pl->tp, pl->tq, pl->tinv, pl->cst, pl->gr,
+                              pl->Vr, pl->Wr, pl->xs, stream);
+      if (st) return st;
+    }
+    if (pl->lazy) {
+      pending = 1;
+    } else {
+      st = fvm_spike_finalize(pl->n_tiles, pl->P, pl->config, pl->extents, xs_off, xs_n, pl->Vt, pl->Wt, pl->xs, w_out,
+                              pl->w_stride, stream);
+      if (st) return st;
+    }
+    cur = 1 - cur;
+  }
+  return FVM_OK;
+}

@@ -33,6 +33,37 @@ def plan_partition(J, tile_cells, world):
     return dict(tiles_per_rank=per_rank, tiles_global=per_rank * world, ranges=ranges)
 
 
+class _NcclUniqueId(ctypes.Structure):
+    _fields_ = [("internal", ctypes.c_byte * 128)]
+
+
+class OwnNccl(object):
+    """An NCCL communicator of our own over the ranks of a torch.distributed NCCL group, made with the NCCL
+    library the process already has loaded.  fvm_spike_steps enqueues the per-step all-gather itself and
+    needs the address of ncclAllGather and an ncclComm_t for that; torch does not hand out its own."""
+
+    def __init__(self, group, rank, world, device):
+        import torch
+        import torch.distributed as dist
+        self.lib = ctypes.CDLL("libnccl.so.2")
+        uid = _NcclUniqueId()
+        if rank == 0:
+            self._check(self.lib.ncclGetUniqueId(ctypes.byref(uid)), "ncclGetUniqueId")
+        t = torch.tensor(list(bytes(uid)), dtype=torch.uint8, device=device)
+        dist.broadcast(t, src=dist.get_global_rank(group, 0), group=group)
+        ctypes.memmove(ctypes.byref(uid), bytes(t.cpu().tolist()), 128)
+        self.comm = ctypes.c_void_p()
+        self.lib.ncclCommInitRank.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, _NcclUniqueId, ctypes.c_int]
+        with torch.cuda.device(device):
+            self._check(self.lib.ncclCommInitRank(ctypes.byref(self.comm), world, uid, rank), "ncclCommInitRank")
+        self.allgather = ctypes.cast(self.lib.ncclAllGather, ctypes.c_void_p)
+
+    @staticmethod
+    def _check(rc, what):
+        if rc != 0:
+            raise RuntimeError("%s failed with ncclResult %d" % (what, rc))
+
+
 class Comm(object):
     """The one collective the data path needs: all-gather of a small tensor over the ranks.
     world == 1: no-op.  NCCL groups gather on the device; a gloo group (tests: several ranks
@@ -41,6 +72,7 @@ class Comm(object):
     def __init__(self, group=None):
         self.group = group
         self.timing = None          # set to a list to collect (start, end) CUDA events of every gather
+        self.own = None             # OwnNccl, made on first use (NCCL groups only)
         if group is None:
             self.rank, self.world, self.backend = 0, 1, None
         else:
@@ -71,6 +103,14 @@ class Comm(object):
             return out
         dist.all_gather_into_tensor(out, t, group=self.group)
         return out
+
+    def own_nccl(self, device):
+        """Our own communicator over the group's ranks (None unless the group's backend is NCCL)."""
+        if self.backend != "nccl":
+            return None
+        if self.own is None:
+            self.own = OwnNccl(self.group, self.rank, self.world, device)
+        return self.own
 
     def all_reduce_max_int(self, values):
         import torch
@@ -280,7 +320,31 @@ class PartitionedAdvectionDiffusionModel(object):
         jl = self.J - 1 - self.j0
         self._last_local = jl if (self._has_rf and 0 <= jl < self.n_local) else -1
         self._theta = theta
+        self._plan = self._make_plan()
         self._ready = theta
+
+    def _make_plan(self):
+        """struct fvm_spike_plan: everything fvm_spike_steps needs to run whole steps in one host call."""
+        pl = _lib.FvmSpikePlan()
+        pl.n_tiles, pl.P, pl.config, pl.lazy = self.nt, self.P, self.config, int(self.lazy)
+        pl.has_first_cell, pl.world, pl.rank = int(self.comm.rank == 0), self.comm.world, self.comm.rank
+        pl.extents[0], pl.extents[1] = self.extents[0], self.extents[1]
+        pl.last_cell_local, pl.theta, pl.w_stride = self._last_local, self._theta, self.w_stride
+        d = lambda t: t.data_ptr()
+        pl.p, pl.q, pl.b, pl.Vt, pl.Wt, pl.sep, pl.bends = (d(self.p), d(self.q), d(self.b), d(self.Vt), d(self.Wt),
+                                                            d(self.sep), d(self.bends))
+        pl.rp, pl.rq, pl.rinv = d(self.rp), d(self.rq), d(self.rinv)
+        pl.rs, pl.rr, pl.g_first = d(self.rs), d(self.rr), d(self.g_first)
+        if self.hier:
+            pl.B, pl.m = self.B, self.nt // self.B
+            pl.Vr, pl.Wr = d(self.Vr), d(self.Wr)
+            pl.tp, pl.tq, pl.tinv, pl.cst = d(self.tp), d(self.tq), d(self.tinv), d(self.top_cst)
+            pl.gr, pl.packet, pl.allp, pl.xs = d(self._gr), d(self.packet), d(self._allp), d(self.xs_ext)
+        elif self.comm.world == 1:
+            pl.B, pl.m, pl.xs = 1, self.nt, d(self.xs)
+        else:
+            return None                 # hierarchical=False across ranks: the Python loop below
+        return pl
 
     def _pick_blocks(self):
         """Blocks per rank of the separator system: as many as keep a block at >= 256 unknowns (one pass of
@@ -443,6 +507,18 @@ class PartitionedAdvectionDiffusionModel(object):
         """``nsteps`` theta steps of the state set by :meth:`set_state` (theta of :meth:`prepare`)."""
         torch = _lib.require_cuda()
         lib, P, nt, cfg, comm = _lib.lib(), self.P, self.nt, self.config, self.comm
+        own = comm.own_nccl(self.device) if comm.world > 1 else None
+        if self._plan is not None and comm.timing is None and (comm.world == 1 or own is not None):
+            # the whole loop in one host call; the all-gather, if any, through our own NCCL communicator
+            with torch.cuda.device(self.device):
+                st = lib.fvm_spike_steps(ctypes.byref(self._plan), _lib.ptr(self._wbuf[0]), _lib.ptr(self._wbuf[1]),
+                                         self._cur, int(self._pending), int(nsteps),
+                                         own.allgather if own else None, own.comm if own else None, _lib.stream_ptr())
+            _lib.check(st, "fvm_spike_steps")
+            if int(nsteps) > 0:
+                self._cur = (self._cur + int(nsteps)) % 2
+                self._pending = self.lazy
+            return
         with torch.cuda.device(self.device):
             for _ in range(int(nsteps)):
                 w_in, w_out = self._wbuf[self._cur], self._wbuf[1 - self._cur]

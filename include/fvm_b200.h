@@ -23,6 +23,7 @@
 #ifndef FVM_B200_H
 #define FVM_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -33,6 +34,7 @@ extern "C" {
 #define FVM_ERR_INVALID_ARG (-1)  /* NULL pointer, J < 3, P < 1, theta outside (0, 1], bad enum */
 #define FVM_ERR_UNSUPPORTED (-2)  /* size outside what this entry point handles               */
 #define FVM_ERR_SCRATCH_LIMIT (-3) /* fvm_spike_local_static: P*n_tiles exceeds the built-in scratch */
+#define FVM_ERR_COLLECTIVE (-4)   /* fvm_spike_steps: the caller's all-gather returned an error    */
 
 /* discretisation of the advective flux [fvm_classes.py:116-128] */
 #define FVM_CENTRAL 0
@@ -303,6 +305,47 @@ int fvm_spike_rank_pack(int64_t P, int64_t B, int64_t m, const double* gr, const
 int fvm_spike_rank_top(int64_t P, int64_t B, int64_t m, int32_t world, int32_t rank, const double* allp,
                        const double* tp, const double* tq, const double* tinv, const double* cst,
                        const double* gr, const double* Vr, const double* Wr, double* xs_ext, void* stream);
+
+/* A whole time loop of variant 3 in ONE host call: nsteps theta steps, each the sequence
+ *   fvm_spike_local(_lazy) -> fvm_spike_reduce_solve (blocks) -> fvm_spike_rank_pack -> all-gather ->
+ *   fvm_spike_rank_top [-> fvm_spike_finalize when lazy == 0]
+ * enqueued on `stream` with nothing allocated and no host synchronisation (without blocks -- B == 1 and
+ * world == 1 -- a step is fvm_spike_local(_lazy) -> fvm_spike_reduce_solve [-> fvm_spike_finalize]).  Replaces
+ * the body of the reference's loop (fvm_classes.py:408-411) for long systems; the per-step host cost of the
+ * separate entry points (five calls) is what bounds meshes of 10^5..10^6 cells, whose step is a few
+ * microseconds of GPU time.
+ * The all-gather across GPUs is the caller's: `allgather` has the signature of ncclAllGather
+ * (sendbuff, recvbuff, sendcount, datatype, comm, stream) and is called with datatype 8 (ncclDouble /
+ * ncclFloat64) -- pass the address of ncclAllGather and an ncclComm_t whose ranks are the slabs in order;
+ * the library itself does not link NCCL.  NULL when world == 1.
+ * The state ping-pongs between w0 and w1: step i reads buffer (cur + i) % 2 and writes the other.
+ * `pending` != 0 says the buffer read first holds an uncorrected state left by a previous lazy call. */
+typedef int (*fvm_allgather_fn)(const void* sendbuff, void* recvbuff, size_t sendcount, int datatype,
+                                void* comm, void* stream);
+
+typedef struct fvm_spike_plan {
+  int64_t n_tiles, P;             /* this rank's tiles, problems                                     */
+  int32_t config, lazy;           /* tile configuration; lazy != 0: correction inside the next solve  */
+  int32_t has_first_cell;         /* as in fvm_spike_local                                            */
+  int32_t world, rank;            /* ranks the cells are split over, this rank                        */
+  int32_t extents[2];             /* spike extents (host values read back from fvm_spike_setup)       */
+  int64_t last_cell_local;        /* as in fvm_spike_local                                            */
+  int64_t B, m;                   /* blocks of the separator system per rank, unknowns per block;
+                                     B == 1 && world == 1: no block level, xs has n_tiles entries     */
+  double theta;
+  int64_t w_stride;
+  const double *p, *q, *b, *Vt, *Wt, *sep, *bends;     /* from fvm_spike_setup                        */
+  const double *rp, *rq, *rinv;   /* factors of the blocks (of the whole separator system without blocks) */
+  const double *Vr, *Wr;          /* block spikes [P][n_tiles]                  (block level only)     */
+  const double *tp, *tq, *tinv, *cst;   /* top system, see fvm_spike_rank_top   (block level only)     */
+  double *rs, *rr, *g_first;      /* work arrays of fvm_spike_local                                    */
+  double *gr, *packet, *allp;     /* [P][n_tiles], [P][B][4], [world][P][B][4]  (block level only)     */
+  double *xs;                     /* separator values: [P][n_tiles+1] with blocks (entry 0 = previous
+                                     rank's last separator), else [P][n_tiles]                         */
+} fvm_spike_plan;
+
+int fvm_spike_steps(const fvm_spike_plan* plan, double* w0, double* w1, int32_t cur, int32_t pending,
+                    int64_t nsteps, fvm_allgather_fn allgather, void* comm, void* stream);
 
 /* Largest P * n_tiles fvm_spike_local_static accepts (32768 tiles, two doubles each = 512 KiB of
  * scratch). */

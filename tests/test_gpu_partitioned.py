@@ -214,3 +214,25 @@ def test_separator_system_in_blocks(blocks):
     bad.set_boundary_conditions(**wl["bc"])
     with pytest.raises(ValueError):
         bad.prepare(1.0)
+
+
+def test_one_call_time_loop_equals_the_step_by_step_host_loop():
+    """fvm_spike_steps (the whole loop in one host call, what step() uses) against the same kernels driven
+    entry point by entry point from Python (the path a gloo group takes): identical bits, with and without
+    the block level, lazy and eager."""
+    wl = W.stiff_reaction(P=2, J=12 * 256 - 7, seed=7)
+    for blocks, lazy in ((1, True), (3, True), (3, False), (1, False)):
+        res = []
+        for host_loop in (False, True):
+            m = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=2,
+                                                   reaction=wl["reaction"], config=1, blocks=blocks, lazy=lazy)
+            m.set_boundary_conditions(**wl["bc"])
+            m.prepare(1.0)
+            m.set_state(wl["w0"])
+            if host_loop:
+                m.comm.timing = []              # a timing request sends step() through the Python loop
+            m.step(3)
+            mid = m.get_state()
+            m.step(4)
+            res.append((mid, m.get_state()))
+        assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1]), (blocks, lazy)

@@ -38,9 +38,18 @@ def test_cfg1_examples_every_step(kind, variant):
         # Thomas arbiter itself sits 2e-11..8e-11 from the reference's SuperLU there (adjacent
         # width ratios up to 657).  Those two meshes get 2e-10; uniform gets 1e-10.
         assert err < (TOL if kind == "uniform" else 2e-10), (kind, scheme, err)
+        # ... and every mesh at the stated 1e-10 against the exact solution (oracle/thomas_arbiter.c, __float128)
+        # of the same fp64 operators: what exceeds 1e-10 on the two wild meshes is the reference's SuperLU
+        asm = O.assemble(f, 1.0, 1e-3, scheme, **bc)
+        A, B = O.theta_operators(asm, 0.01, 0.5)
+        exact = O.theta_run_arbiter(A, B, asm["beta"], w0, 251, np.arange(1, 252))
+        assert step_error(ck[:, 0], exact, np.max(np.abs(w0))) < TOL, (kind, scheme)
         _, ck = run_gpu(f, 1.0, 1e-3, 0.01, scheme, bc, 1.0, w0, 250, 50, variant, P=1)
         err = step_error(ck[:, 0], g["%s_%s_theta1.0" % (kind, scheme)], np.max(np.abs(w0)))
         assert err < (TOL if kind == "uniform" else 2e-10), (kind, scheme, err)
+        A, B = O.theta_operators(asm, 0.01, 1.0)
+        exact = O.theta_run_arbiter(A, B, asm["beta"], w0, 250, np.arange(50, 251, 50))
+        assert step_error(ck[:, 0], exact, np.max(np.abs(w0))) < TOL, (kind, scheme)
 
 
 @pytest.mark.parametrize("variant", VARIANTS)
