@@ -236,3 +236,39 @@ def test_one_call_time_loop_equals_the_step_by_step_host_loop():
             m.step(4)
             res.append((mid, m.get_state()))
         assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1]), (blocks, lazy)
+
+
+@pytest.mark.parametrize("config,J,blocks", [(1, 3000, 3), (2, 9000, None), (0, 20000, None)])
+def test_no_stray_writes_around_the_state_buffers(config, J, blocks):
+    """compute-sanitizer is not available on the GPU pool: guard bands of NaN-free canaries around both state
+    buffers and the per-tile work arrays must survive a time loop (lazy steps, a materialisation, more steps)."""
+    wl = W.stiff_reaction(P=2, J=J, seed=J)
+    m = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=2,
+                                           reaction=wl["reaction"], config=config, blocks=blocks)
+    m.set_boundary_conditions(**wl["bc"])
+    m.prepare(0.5)
+    pad, canary = 4096, -777.25
+    guarded = {}
+
+    def guard(t):
+        big = torch.full((t.numel() + 2 * pad,), canary, dtype=torch.float64, device=t.device)
+        view = big[pad:pad + t.numel()].view(t.shape)
+        view.copy_(t)
+        guarded[id(view)] = big
+        return view
+
+    m._wbuf = [guard(b) for b in m._wbuf]
+    m.rs, m.rr, m.g_first = guard(m.rs), guard(m.rr), guard(m.g_first)
+    if m.hier:
+        m.xs_ext, m._gr, m.packet = guard(m.xs_ext), guard(m._gr), guard(m.packet)
+    else:
+        m.xs = guard(m.xs)
+    m._plan = m._make_plan()
+    m.set_state(wl["w0"])
+    m.step(5)
+    mid = m.get_state()
+    m.step(4)
+    out = m.get_state()
+    assert bool(torch.isfinite(mid).all()) and bool(torch.isfinite(out).all())
+    for big in guarded.values():
+        assert bool((big[:pad] == canary).all()) and bool((big[-pad:] == canary).all())
