@@ -193,7 +193,7 @@ struct FusedExtras {
 // Shared-memory variant (J <= 512, and the RB slow path of J <= 1024).  Same formulation as the
 // tensor-memory kernel below -- no right-hand side, separator rows in yhat, set-up in double-double,
 // spikes of the exact block -- without its twisted factorisation and delayed correction: per step
-//   h_c = g_c + theta*beta_c - l_c h_{c-1};  t_c = h_c kappa_c - c g_c - c s_c g_{c+1};  z_c = t_c - s_c z_{c+1}
+//   h_c = g_c + theta*beta_c - l_c h_{c-1};  u_c = h_c - s"_c u_{c+1};  z_c = kappa_c u_c - c g_c
 //   R yhat_s = xs/theta + beta_s - slo ghat_last - sup ghat_first(next lane),  ghat = z + c g
 //   x'_c = z_c - V_c yhat_s(l-1) - U_c yhat_s(l);   x'_s = yhat_s - c xs
 // l, kappa, V, U in shared memory ([coef][c][lane], lane-consecutive doubles: conflict-free), s in
@@ -234,9 +234,11 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
     }
     Reduced R;
     setup_system<C, RB>(pr, p, lane, dt_run, theta, sl, sk, ss, sv, su, tlo, glo, R);
+    // s" = s kappa_next / kappa: the substitution runs on u = yhat / kappa (see the tensor-memory kernel, 2.)
     double qr[NS];
 #pragma unroll
-    for (int c = 0; c < NS; ++c) qr[c] = (c < N) ? ss[c * 32] : 0.0;
+    for (int c = 0; c < NS; ++c)
+      qr[c] = (c + 1 < N) ? dd_round(dd_div(two_prod(ss[c * 32], sk[(c + 1) * 32]), dd_make(sk[c * 32]))) : 0.0;
     __syncwarp();
 
     double w[C];
@@ -253,20 +255,22 @@ fused_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_
       double rr = fma(xs_old, rth, bsep);
       if (N > 0) {
         const double g0_old = w[0], gl_old = w[N - 1];
+        double hh[NS];
         double h = 0.0;
 #pragma unroll
         for (int c = 0; c < N; ++c) {
-          const double gc = w[c];
-          double r = gc;
+          double r = w[c];
           if (c == 0) r += bfirst;
           if (RB) { if (c == R.rb_c) r += bint; }
           h = (c == 0) ? r : fma(-sl[c * 32], h, r);
-          double t = (MODE == 2) ? h * sk[c * 32] : fma(h, sk[c * 32], -cmul(gc));
-          if (MODE != 2 && c + 1 < N) t = fma(-qr[c], cmul(w[c + 1]), t);
-          w[c] = t;
+          hh[c] = h;
         }
+        double u = 0.0;
 #pragma unroll
-        for (int c = N - 2; c >= 0; --c) w[c] = fma(-qr[c], w[c + 1], w[c]);
+        for (int c = N - 1; c >= 0; --c) {
+          u = (c == N - 1) ? hh[c] : fma(-qr[c], u, hh[c]);
+          w[c] = (MODE == 2) ? sk[c * 32] * u : fma(sk[c * 32], u, -cmul(w[c]));    // z = kappa u - c g
+        }
         // ghat = z + c g: the block solution of yhat with the separators at zero
         const double gh_last = (MODE == 2) ? w[N - 1] : w[N - 1] + cmul(gl_old);
         const double gh_first = (MODE == 2) ? w[0] : w[0] + cmul(g0_old);
