@@ -38,8 +38,8 @@ def _stale(target, srcs):
     return any(os.path.getmtime(s) > t for s in srcs)
 
 
-def _compile(src):
-    obj = os.path.join(BUILD, src.replace(".cu", ".o"))
+def _compile(src, build_dir=None):
+    obj = os.path.join(build_dir or BUILD, src.replace(".cu", ".o"))
     path = os.path.join(CSRC, src)
     if not _stale(obj, [path] + _deps()):
         return obj, ""
@@ -52,8 +52,10 @@ def _compile(src):
     return obj, res.stderr
 
 
-def build_library(force=False, verbose=False):
-    """Compile (if stale) and return the path of libfvm_b200.so."""
+def build_library(force=False, verbose=False, build_dir=None, lib_path=None):
+    """Compile (if stale) and return the path of libfvm_b200.so.  ``build_dir`` / ``lib_path``: build somewhere
+    else than in the tree (tests/test_clean_build.py: a build from nothing but the sources)."""
+    BUILD, LIB = build_dir or globals()["BUILD"], lib_path or globals()["LIB"]
     os.makedirs(BUILD, exist_ok=True)
     if force:
         for f in os.listdir(BUILD):
@@ -61,7 +63,7 @@ def build_library(force=False, verbose=False):
         if os.path.exists(LIB):
             os.remove(LIB)
     with concurrent.futures.ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
-        results = list(ex.map(_compile, SOURCES))
+        results = list(ex.map(lambda src: _compile(src, BUILD), SOURCES))
     objs = [r[0] for r in results]
     if verbose:
         for _, log in results:
