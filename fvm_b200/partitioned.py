@@ -109,8 +109,17 @@ class Comm(object):
         if self.backend != "nccl":
             return None
         if self.own is None:
-            self.own = OwnNccl(self.group, self.rank, self.world, device)
-        return self.own
+            import torch
+            import torch.distributed as dist
+            try:
+                own = OwnNccl(self.group, self.rank, self.world, device)
+            except (OSError, RuntimeError, AttributeError):
+                own = None
+            # every rank or none: a rank that could not make its communicator sends all of them to the host loop
+            ok = torch.tensor([1 if own is not None else 0], dtype=torch.int32, device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=self.group)
+            self.own = own if int(ok.item()) == 1 else False
+        return self.own or None
 
     def all_reduce_max_int(self, values):
         import torch
