@@ -670,7 +670,7 @@ def run_b200(args):
     issue_frac = FP64_INSTR_PER_CELL_UPDATE * cu_s_kernel / (sms * 64.0 * f_clk)   # thread-level DFMAs issued / (64 lanes per clk per SM)
     smem_peak = sms * 128.0 * f_max / 1e9
     onchip = ONCHIP_B_PER_CELL_UPDATE * cu_s_kernel / 1e9
-    roofline = {"kernel": "fused_tmem_pipe_kernel<1, 2> (variant 2, Crank-Nicolson: state in registers, coefficients in TMEM)",
+    roofline = {"kernel": "fused_tmem_pipe_kernel<1, 0> (variant 2, Crank-Nicolson: state in registers, coefficients in TMEM)",
                 "bound": "fp64", "achieved": fp64_ach, "peak": fp64_peak, "unit": "TFLOP/s",
                 "frac": fp64_ach / fp64_peak, "traffic": ncu_traffic(FUSED_SUMMARY),
                 "traffic_note": "DRAM bytes per launch from profiles/%s (ncu --set full, same command); algorithmic "
