@@ -57,6 +57,7 @@ def parse():
                          "cfg5: one mesh of 2^27 cells per GPU split over the ranks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-chunks", type=int, default=None, help="groups run_host cuts the batch into (default: its own)")
     ap.add_argument("--no-long-legs", action="store_true", help="skip the variant-3 legs (cfg 5 / cfg 4) of the default run")
     return ap.parse_args()
 
@@ -595,13 +596,14 @@ def run_b200(args):
         h_out = torch.empty((P, J), dtype=torch.float64).pin_memory()
         h_ck = torch.empty((n_ck, P, J), dtype=torch.float64).pin_memory() if n_ck else None
         h_in.copy_(w0)
+        e2e_kw = {} if args.e2e_chunks is None else {"chunks": args.e2e_chunks}
         for _ in range(2):
-            model.run_host(h_in, 0.5, inner, out=h_out, checkpoint_every=ce, ckpt_out=h_ck)
+            model.run_host(h_in, 0.5, inner, out=h_out, checkpoint_every=ce, ckpt_out=h_ck, **e2e_kw)
         barrier()
         t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
         t0.record()
         for _ in range(K):
-            model.run_host(h_in, 0.5, inner, out=h_out, checkpoint_every=ce, ckpt_out=h_ck)
+            model.run_host(h_in, 0.5, inner, out=h_out, checkpoint_every=ce, ckpt_out=h_ck, **e2e_kw)
         t1.record()
         barrier()
         te = torch.tensor([t0.elapsed_time(t1)], device=dev, dtype=torch.float64)

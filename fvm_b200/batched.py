@@ -537,7 +537,7 @@ class BatchedAdvectionDiffusionModel(object):
                     ckpt[(n + 1) // ce - 1].copy_(dst)
         return bufs[nsteps & 1]
 
-    def run_host(self, w_host, theta, nsteps, out=None, variant="auto", chunks=16, checkpoint_every=0,
+    def run_host(self, w_host, theta, nsteps, out=None, variant="auto", chunks=None, checkpoint_every=0,
                  ckpt_out=None):
         """Host-buffer form of :meth:`run`: ``w_host`` (P, J) lives in host memory (numpy array
         or CPU tensor; pinned memory makes the copies asynchronous and fast).  Copies it to the
@@ -547,7 +547,9 @@ class BatchedAdvectionDiffusionModel(object):
 
         The batch is cut into ``chunks`` groups of problems that travel on three streams, so
         that the upload of one group, the kernel of another and the download of a third overlap
-        (problems are independent: no group waits for another).
+        (problems are independent: no group waits for another).  Default: groups of one wave (8 problems
+        per SM), at most 64 of them -- what nothing overlaps is the first group's upload and the last
+        group's download, so small groups cost least (cfg 3: 56 groups, 1.9 % faster than 14).
 
         ``checkpoint_every`` > 0 (fused variant): the state after every that many steps is
         copied into ``ckpt_out`` (nsteps // checkpoint_every, P, J) in host memory (allocated
@@ -593,7 +595,7 @@ class BatchedAdvectionDiffusionModel(object):
             # groups of whole "waves": the on-chip kernels run 8 problems per SM at a time, so a group
             # that is a multiple of 8 x SMs leaves no SM idle in its last wave
             wave = 8 * torch.cuda.get_device_properties(self.device).multi_processor_count
-            per = -(-self.P // max(1, int(chunks)))
+            per = -(-self.P // (64 if chunks is None else max(1, int(chunks))))
             per = max(wave, -(-per // wave) * wave) if self.P >= 4 * wave else self.P
             bounds = list(range(0, self.P, per)) + [self.P]
             n_chunks = len(bounds) - 1

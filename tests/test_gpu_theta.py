@@ -305,6 +305,8 @@ def test_run_host_pipelined_chunks_equal_device_run():
     out2, ck_host = m.run_host(h_in, 0.5, 30, chunks=3, checkpoint_every=8)
     assert ck_host.shape == (3, 8192, 1024) and ck_host.is_pinned()
     assert torch.equal(ck_host, ck_dev.cpu()) and torch.equal(out2, w_ck.cpu())
+    out3, ck3 = m.run_host(h_in, 0.5, 30, checkpoint_every=8)        # default grouping: one wave per group
+    assert torch.equal(ck3, ck_dev.cpu()) and torch.equal(out3, w_ck.cpu())
     with pytest.raises(ValueError):
         m.run_host(h_in, 0.5, 30, variant="thomas", checkpoint_every=8)
 
