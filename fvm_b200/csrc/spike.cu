@@ -38,7 +38,7 @@
 // a warp's load of its c-th cells is two full 128-byte lines.  With the natural order the same
 // loads touch 32 lines each and the kernel is bound by L1 tag look-ups at 30 % of HBM speed
 // (profiles/r01_spike_launches_natural.csv).  The first and last positions of a tile are its
-// first and last cell in both orders, so ghosts and tile neighbours need no special casing.
+// first and last cell in both orders.
 #include "fvm_device.cuh"
 #include "cta_scan.cuh"
 #include "dd.cuh"
