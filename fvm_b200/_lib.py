@@ -103,6 +103,9 @@ _SIGNATURES = {
     "fvm_spike_rank_top": (ctypes.c_int, [c_i64, c_i64, c_i64, c_i32, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
                                           c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "fvm_spike_static_max_tiles": (c_i64, []),
+    "fvm_spike_graph_create": (ctypes.c_int, [ctypes.POINTER(FvmSpikePlan), c_ptr, c_ptr, c_ptr, ctypes.POINTER(c_ptr)]),
+    "fvm_spike_graph_run": (ctypes.c_int, [c_ptr, c_i64, c_ptr]),
+    "fvm_spike_graph_destroy": (None, [c_ptr]),
     "fvm_spike_steps": (ctypes.c_int, [ctypes.POINTER(FvmSpikePlan), c_ptr, c_ptr, c_i32, c_i32, c_i64, c_ptr, c_ptr,
                                        c_ptr]),
     "fvm_spike_local_static": (ctypes.c_int, [c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_i64,

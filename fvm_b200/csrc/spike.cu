@@ -42,6 +42,7 @@
 #include "fvm_device.cuh"
 #include "cta_scan.cuh"
 #include "dd.cuh"
+#include <new>
 
 namespace fvm {
 
@@ -771,4 +772,50 @@ extern "C" int fvm_spike_steps(const fvm_spike_plan* pl, double* w0, double* w1,
     cur = 1 - cur;
   }
   return FVM_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// fvm_spike_graph_*: two lazy steps of fvm_spike_steps captured once and replayed (see the header).
+struct fvm_spike_graph {
+  cudaGraph_t graph;
+  cudaGraphExec_t exec;
+};
+
+extern "C" int fvm_spike_graph_create(const fvm_spike_plan* pl, double* w0, double* w1, void* stream,
+                                      fvm_spike_graph** out) {
+  if (!pl || !w0 || !w1 || !out || !stream) return FVM_ERR_INVALID_ARG;     // the legacy default stream cannot capture
+  if (pl->world != 1 || !pl->lazy) return FVM_ERR_UNSUPPORTED;
+  *out = nullptr;
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaError_t e = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
+  if (e != cudaSuccess) return (int)e;
+  const int st = fvm_spike_steps(pl, w0, w1, 0, 1, 2, nullptr, nullptr, stream);
+  cudaGraph_t graph = nullptr;
+  e = cudaStreamEndCapture(s, &graph);                   // always end the capture, also after a failed step
+  if (st) { if (graph) cudaGraphDestroy(graph); return st; }
+  if (e != cudaSuccess) return (int)e;
+  cudaGraphExec_t exec = nullptr;
+  e = cudaGraphInstantiate(&exec, graph, 0);
+  if (e != cudaSuccess) { cudaGraphDestroy(graph); return (int)e; }
+  fvm_spike_graph* g = new (std::nothrow) fvm_spike_graph;
+  if (!g) { cudaGraphExecDestroy(exec); cudaGraphDestroy(graph); return (int)cudaErrorMemoryAllocation; }
+  g->graph = graph; g->exec = exec;
+  *out = g;
+  return FVM_OK;
+}
+
+extern "C" int fvm_spike_graph_run(fvm_spike_graph* g, int64_t n_pairs, void* stream) {
+  if (!g || n_pairs < 0) return FVM_ERR_INVALID_ARG;
+  for (int64_t i = 0; i < n_pairs; ++i) {
+    const cudaError_t e = cudaGraphLaunch(g->exec, (cudaStream_t)stream);
+    if (e != cudaSuccess) return (int)e;
+  }
+  return FVM_OK;
+}
+
+extern "C" void fvm_spike_graph_destroy(fvm_spike_graph* g) {
+  if (!g) return;
+  cudaGraphExecDestroy(g->exec);
+  cudaGraphDestroy(g->graph);
+  delete g;
 }

@@ -171,6 +171,8 @@ class PartitionedAdvectionDiffusionModel(object):
         self.discretisation, self.strict_bc, self.spike_tol = discretisation, strict_bc, float(spike_tol)
         self.hierarchical = bool(hierarchical)
         self._blocks_wanted = blocks    # blocks per rank of the separator system (None: chosen from its size)
+        self.use_graph = True           # replay launch-bound time loops as a CUDA graph (see step)
+        self._graph, self._gstream = None, None
         self.lazy = bool(lazy)          # apply the spike correction inside the next step's tile solve
         self._pending = False           # the current buffer holds uncorrected tile solutions
         plan = plan_partition(self.J, self.T, self.comm.world)
@@ -329,8 +331,26 @@ class PartitionedAdvectionDiffusionModel(object):
         jl = self.J - 1 - self.j0
         self._last_local = jl if (self._has_rf and 0 <= jl < self.n_local) else -1
         self._theta = theta
+        self._drop_graph()                  # a graph of an earlier prepare() points at arrays that are gone
         self._plan = self._make_plan()
         self._ready = theta
+
+    def _graph_worthwhile(self, n):
+        """A CUDA graph of the step pays where the step is launch-bound: one GPU, lazy correction, a slab of
+        at most 2^22 cells in all, and enough steps to amortise the capture."""
+        return (self.use_graph and self.comm.world == 1 and self.lazy and n >= 16
+                and self.P * self.n_local <= (1 << 22))
+
+    def _drop_graph(self):
+        if getattr(self, "_graph", None) is not None:
+            _lib.lib().fvm_spike_graph_destroy(self._graph)
+        self._graph = None
+
+    def __del__(self):
+        try:
+            self._drop_graph()
+        except Exception:
+            pass
 
     def _make_plan(self):
         """struct fvm_spike_plan: everything fvm_spike_steps needs to run whole steps in one host call."""
@@ -519,14 +539,41 @@ class PartitionedAdvectionDiffusionModel(object):
         own = comm.own_nccl(self.device) if comm.world > 1 else None
         if self._plan is not None and comm.timing is None and (comm.world == 1 or own is not None):
             # the whole loop in one host call; the all-gather, if any, through our own NCCL communicator
-            with torch.cuda.device(self.device):
+            def steps(n, stream):
+                if n <= 0:
+                    return
                 st = lib.fvm_spike_steps(ctypes.byref(self._plan), _lib.ptr(self._wbuf[0]), _lib.ptr(self._wbuf[1]),
-                                         self._cur, int(self._pending), int(nsteps),
-                                         own.allgather if own else None, own.comm if own else None, _lib.stream_ptr())
-            _lib.check(st, "fvm_spike_steps")
-            if int(nsteps) > 0:
-                self._cur = (self._cur + int(nsteps)) % 2
+                                         self._cur, int(self._pending), int(n),
+                                         own.allgather if own else None, own.comm if own else None, stream)
+                _lib.check(st, "fvm_spike_steps")
+                self._cur = (self._cur + int(n)) % 2
                 self._pending = self.lazy
+
+            n = int(nsteps)
+            with torch.cuda.device(self.device):
+                if self._graph_worthwhile(n):
+                    # launch-bound sizes: two steps captured once in a CUDA graph and replayed, on a stream of
+                    # our own (the legacy default stream cannot capture)
+                    cur_stream = torch.cuda.current_stream()
+                    if self._gstream is None:
+                        self._gstream = torch.cuda.Stream(device=self.device)
+                    self._gstream.wait_stream(cur_stream)
+                    with torch.cuda.stream(self._gstream):
+                        gs = _lib.stream_ptr()
+                        lead = 1 if self._cur == 1 else (0 if self._pending else 2)   # -> pending state in buffer 0
+                        steps(lead, gs)
+                        if self._graph is None:
+                            h = ctypes.c_void_p()
+                            st = lib.fvm_spike_graph_create(ctypes.byref(self._plan), _lib.ptr(self._wbuf[0]),
+                                                            _lib.ptr(self._wbuf[1]), gs, ctypes.byref(h))
+                            _lib.check(st, "fvm_spike_graph_create")
+                            self._graph = h
+                        pairs = (n - lead) // 2
+                        _lib.check(lib.fvm_spike_graph_run(self._graph, pairs, gs), "fvm_spike_graph_run")
+                        steps(n - lead - 2 * pairs, gs)
+                    cur_stream.wait_stream(self._gstream)
+                else:
+                    steps(n, _lib.stream_ptr())
             return
         with torch.cuda.device(self.device):
             for _ in range(int(nsteps)):

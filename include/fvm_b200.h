@@ -8,9 +8,10 @@
  * Conventions
  *  - every pointer is a DEVICE pointer to fp64 data unless stated otherwise;
  *  - the caller owns every buffer; the library allocates nothing, keeps no state
- *    between calls and reads no environment variable (one exception, stated at its
- *    declaration: fvm_spike_local_static works in a fixed device array inside the
- *    library image, whose contents persist from call to call); all work is
+ *    between calls and reads no environment variable (two exceptions, stated at their
+ *    declarations: fvm_spike_local_static works in a fixed device array inside the
+ *    library image, whose contents persist from call to call, and the handle of
+ *    fvm_spike_graph_create owns a CUDA graph until it is destroyed); all work is
  *    enqueued on `stream` (a CUstream / cudaStream_t handle passed as void*;
  *    NULL = the legacy default stream) and no call synchronises the host;
  *  - strided arrays: element (problem p, cell j) of X lives at X[p*X_ps + j*X_cs]
@@ -346,6 +347,20 @@ typedef struct fvm_spike_plan {
 
 int fvm_spike_steps(const fvm_spike_plan* plan, double* w0, double* w1, int32_t cur, int32_t pending,
                     int64_t nsteps, fvm_allgather_fn allgather, void* comm, void* stream);
+
+/* The same loop as a CUDA graph, for meshes whose step is launch-bound (10^5..10^6 cells: a few
+ * microseconds of GPU time in three to five launches).  fvm_spike_graph_create captures TWO consecutive lazy
+ * steps (w0 -> w1 -> w0) of fvm_spike_steps on `stream` -- which must not be the legacy default stream -- and
+ * instantiates them; fvm_spike_graph_run replays the pair n_pairs times.  Requirements: plan->world == 1,
+ * plan->lazy != 0, and w0 must hold a PENDING (uncorrected) state when the graph runs, i.e. at least one
+ * fvm_spike_steps call came first and left the state in w0.  The handle owns host memory and a CUDA graph:
+ * this and fvm_spike_local_static are the two places where the library keeps something between calls;
+ * fvm_spike_graph_destroy releases it.  A plan, its arrays and w0, w1 must outlive the handle unchanged. */
+typedef struct fvm_spike_graph fvm_spike_graph;
+int fvm_spike_graph_create(const fvm_spike_plan* plan, double* w0, double* w1, void* stream,
+                           fvm_spike_graph** out);
+int fvm_spike_graph_run(fvm_spike_graph* graph, int64_t n_pairs, void* stream);
+void fvm_spike_graph_destroy(fvm_spike_graph* graph);
 
 /* Largest P * n_tiles fvm_spike_local_static accepts (32768 tiles, two doubles each = 512 KiB of
  * scratch). */

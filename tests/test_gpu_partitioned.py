@@ -272,3 +272,29 @@ def test_no_stray_writes_around_the_state_buffers(config, J, blocks):
     assert bool(torch.isfinite(mid).all()) and bool(torch.isfinite(out).all())
     for big in guarded.values():
         assert bool((big[:pad] == canary).all()) and bool((big[-pad:] == canary).all())
+
+
+@pytest.mark.parametrize("blocks", [1, 3])
+def test_cuda_graph_time_loop_is_the_same_loop(blocks):
+    """Launch-bound sizes replay two captured steps as a CUDA graph (fvm_spike_graph_*): same bits as the plain
+    one-call loop, from every starting condition (fresh state, pending state, odd and even buffer)."""
+    wl = W.stiff_reaction(P=2, J=12 * 256 - 7, seed=9)
+    res = []
+    for use_graph in (True, False):
+        m = PartitionedAdvectionDiffusionModel(wl["faces"], wl["a"], wl["d"], wl["k"], "exponential", P=2,
+                                               reaction=wl["reaction"], config=1, blocks=blocks)
+        m.use_graph = use_graph
+        m.set_boundary_conditions(**wl["bc"])
+        m.prepare(0.5)
+        m.set_state(wl["w0"])
+        out = []
+        for n in (37, 16, 3, 21):          # fresh -> graph; pending in buffer 1 -> graph; no graph; pending again
+            m.step(n)
+            out.append(m.get_state().clone())
+        m.set_state(out[0])                 # a true state again, graph kept
+        m.step(40)
+        out.append(m.get_state().clone())
+        assert (m._graph is not None) == use_graph
+        res.append(out)
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
