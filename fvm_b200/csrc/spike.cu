@@ -287,18 +287,35 @@ __global__ void __launch_bounds__(256) reduced_rhs_kernel(int64_t n_tiles, const
   if (k == 0) g_first_out[pi] = r2[1];
 }
 
-// Thomas solve of the factored reduced system by ONE CTA per problem, in chunks of TPB*CPT
-// unknowns with the carry handed from chunk to chunk.
-template <int TPB, int CPT>
+// FUSED form of reduced_solve_kernel (fvm_spike_steps): the right-hand side is built while it is loaded
+// (what reduced_rhs_kernel does) and the block's contribution to the gather is written at the end (what
+// rank_pack_kernel does), so a step has two launches fewer.  nt: tiles per problem; B: blocks per problem.
+struct FusedRhs {
+  const double* rs; const double* sep; int64_t nt, B; double* g_first; double* packet;
+};
+
+// Thomas solve of the factored reduced system by ONE CTA per problem (per block of it), in chunks of
+// TPB*CPT unknowns with the carry handed from chunk to chunk.
+template <int TPB, int CPT, bool FUSED>
 __global__ void __launch_bounds__(TPB) reduced_solve_kernel(int64_t n, const double* __restrict__ rp,
                                                             const double* __restrict__ rq,
                                                             const double* __restrict__ rinv,
-                                                            const double* __restrict__ rr, double* __restrict__ xs) {
+                                                            const double* __restrict__ rr, double* __restrict__ xs,
+                                                            FusedRhs fr) {
   constexpr int CH = TPB * CPT;
   __shared__ double sm[66];
   const int64_t pi = blockIdx.x;
   const double* P_ = rp + pi * n; const double* Q_ = rq + pi * n; const double* I_ = rinv + pi * n;
   const double* R_ = rr + pi * n; double* X_ = xs + pi * n;
+  const int64_t prob = FUSED ? pi / fr.B : 0, kt0 = FUSED ? (pi % fr.B) * n : 0;
+  // rr_k = rs_k - up_k g_first(k+1), the term left out at the last tile of the slab (reduced_rhs_kernel)
+  auto rhs = [&](int64_t k) {
+    if (!FUSED) return R_[k];
+    const int64_t t = prob * fr.nt + kt0 + k;
+    double r = fr.rs[2 * t];
+    if (kt0 + k + 1 < fr.nt) r = fma(-fr.sep[t * SEP_STRIDE + SEP_UP], fr.rs[2 * t + 3], r);
+    return r;
+  };
   double carry = 0.0;
   for (int64_t c0 = 0; c0 < n; c0 += CH) {                 // forward: g_k = rr_k*inv_k - p_k g_{k-1}
     double g[CPT], pc[CPT];
@@ -307,7 +324,7 @@ __global__ void __launch_bounds__(TPB) reduced_solve_kernel(int64_t n, const dou
       const int64_t k = c0 + (int64_t)threadIdx.x * CPT + c;
       const bool in = k < n;
       pc[c] = in ? P_[k] : 0.0;
-      g[c] = in ? R_[k] * I_[k] : 0.0;
+      g[c] = in ? rhs(k) * I_[k] : 0.0;
     }
     Affine tot;
     cta_forward<TPB, CPT>(g, [&](int c) { return pc[c]; }, sm, carry, &tot);
@@ -338,6 +355,17 @@ __global__ void __launch_bounds__(TPB) reduced_solve_kernel(int64_t n, const dou
     for (int c = 0; c < CPT; ++c) {
       const int64_t k = c0 + (int64_t)threadIdx.x * CPT + c;
       if (k < n) X_[k] = x[c];
+    }
+  }
+  if (FUSED) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const double gf = fr.rs[2 * prob * fr.nt + 1];
+      if (kt0 == 0) fr.g_first[prob] = gf;
+      if (fr.packet) {
+        double* o = fr.packet + pi * 4;
+        o[0] = X_[0]; o[1] = X_[n - 2]; o[2] = X_[n - 1]; o[3] = gf;
+      }
     }
   }
 }
@@ -458,11 +486,13 @@ static int launch_tile_solve(int64_t n_tiles, int64_t P, const double* p, const 
 #undef FVM_TILE_INST
 }
 
-extern "C" int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
-                               const double* b, const double* sep, const double* bends, int32_t has_first_cell,
-                               int64_t last_cell_local, double theta, const double* w_in, double* w_out,
-                               int64_t w_stride, double* rs,
-                               double* rr, int64_t rr_stride, double* g_first, void* stream) {
+// with_rhs = false: the tile solves only; the caller builds the reduced right-hand side itself (fvm_spike_steps:
+// inside the fused separator solve)
+static int spike_local_impl(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                            const double* b, const double* sep, const double* bends, int32_t has_first_cell,
+                            int64_t last_cell_local, double theta, const double* w_in, double* w_out,
+                            int64_t w_stride, double* rs, double* rr, int64_t rr_stride, double* g_first,
+                            void* stream, bool with_rhs) {
   if (!p || !q || !b || !sep || !bends || !w_in || !w_out || !rs || !rr || !g_first) return FVM_ERR_INVALID_ARG;
   if (n_tiles < 1 || P < 1 || P > 65535 || !(theta > 0.0 && theta <= 1.0)) return FVM_ERR_INVALID_ARG;
   if (config < 0 || config >= kTileCfgs || n_tiles > 0x7fffffffLL) return FVM_ERR_INVALID_ARG;
@@ -473,10 +503,19 @@ extern "C" int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const
                                             w_in, w_out, rs, w_stride, s)
                      : launch_tile_solve<256, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
                                             w_in, w_out, rs, w_stride, s);
-  if (st) return st;
+  if (st || !with_rhs) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
   fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, sep, rs, rr, rr_stride, g_first);
   return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_spike_local(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                               const double* b, const double* sep, const double* bends, int32_t has_first_cell,
+                               int64_t last_cell_local, double theta, const double* w_in, double* w_out,
+                               int64_t w_stride, double* rs,
+                               double* rr, int64_t rr_stride, double* g_first, void* stream) {
+  return spike_local_impl(n_tiles, P, config, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in, w_out,
+                          w_stride, rs, rr, rr_stride, g_first, stream, true);
 }
 
 extern "C" int fvm_spike_reduce_solve(int64_t n_global, int64_t P, const double* rp, const double* rq,
@@ -484,9 +523,9 @@ extern "C" int fvm_spike_reduce_solve(int64_t n_global, int64_t P, const double*
   if (!rp || !rq || !rinv || !rr || !xs || n_global < 1 || P < 1) return FVM_ERR_INVALID_ARG;
   cudaStream_t s = (cudaStream_t)stream;
   if (n_global <= 1024)
-    fvm::reduced_solve_kernel<128, 8><<<(unsigned)P, 128, 0, s>>>(n_global, rp, rq, rinv, rr, xs);
+    fvm::reduced_solve_kernel<128, 8, false><<<(unsigned)P, 128, 0, s>>>(n_global, rp, rq, rinv, rr, xs, fvm::FusedRhs{});
   else
-    fvm::reduced_solve_kernel<1024, 8><<<(unsigned)P, 1024, 0, s>>>(n_global, rp, rq, rinv, rr, xs);
+    fvm::reduced_solve_kernel<1024, 8, false><<<(unsigned)P, 1024, 0, s>>>(n_global, rp, rq, rinv, rr, xs, fvm::FusedRhs{});
   return (int)cudaGetLastError();
 }
 
@@ -523,13 +562,13 @@ extern "C" int fvm_spike_finalize(int64_t n_tiles, int64_t P, int32_t config, co
 // The state buffer then holds the uncorrected z between steps and the separator values of the step
 // that produced it stay in `xs`; fvm_spike_finalize materialises the true state when it is needed
 // (output, checkpoints).
-extern "C" int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
-                                    const double* b, const double* sep, const double* bends,
-                                    int32_t has_first_cell, int64_t last_cell_local, double theta,
-                                    const double* w_in, double* w_out, int64_t w_stride, double* rs, double* rr,
-                                    int64_t rr_stride, double* g_first, const double* Vt, const double* Wt,
-                                    const double* xs, int64_t tile_offset, int64_t n_tiles_global,
-                                    const int32_t* extents_host, void* stream) {
+static int spike_local_lazy_impl(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                                 const double* b, const double* sep, const double* bends,
+                                 int32_t has_first_cell, int64_t last_cell_local, double theta,
+                                 const double* w_in, double* w_out, int64_t w_stride, double* rs, double* rr,
+                                 int64_t rr_stride, double* g_first, const double* Vt, const double* Wt,
+                                 const double* xs, int64_t tile_offset, int64_t n_tiles_global,
+                                 const int32_t* extents_host, void* stream, bool with_rhs) {
   if (!p || !q || !b || !sep || !bends || !w_in || !w_out || !rs || !rr || !g_first || !Vt || !Wt || !xs ||
       !extents_host)
     return FVM_ERR_INVALID_ARG;
@@ -548,10 +587,22 @@ extern "C" int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, 
                                             w_in, w_out, rs, w_stride, s, &lz)
                      : launch_tile_solve<256, 16>(n_tiles, P, p, q, b, sep, bends, has_first_cell, last_cell_local, theta,
                                             w_in, w_out, rs, w_stride, s, &lz);
-  if (st) return st;
+  if (st || !with_rhs) return st;
   dim3 g((unsigned)((n_tiles + 255) / 256), (unsigned)P);
   fvm::reduced_rhs_kernel<<<g, 256, 0, s>>>(n_tiles, sep, rs, rr, rr_stride, g_first);
   return (int)cudaGetLastError();
+}
+
+extern "C" int fvm_spike_local_lazy(int64_t n_tiles, int64_t P, int32_t config, const double* p, const double* q,
+                                    const double* b, const double* sep, const double* bends,
+                                    int32_t has_first_cell, int64_t last_cell_local, double theta,
+                                    const double* w_in, double* w_out, int64_t w_stride, double* rs, double* rr,
+                                    int64_t rr_stride, double* g_first, const double* Vt, const double* Wt,
+                                    const double* xs, int64_t tile_offset, int64_t n_tiles_global,
+                                    const int32_t* extents_host, void* stream) {
+  return spike_local_lazy_impl(n_tiles, P, config, p, q, b, sep, bends, has_first_cell, last_cell_local, theta, w_in,
+                               w_out, w_stride, rs, rr, rr_stride, g_first, Vt, Wt, xs, tile_offset, n_tiles_global,
+                               extents_host, stream, true);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -735,23 +786,33 @@ extern "C" int fvm_spike_steps(const fvm_spike_plan* pl, double* w0, double* w1,
     double* w_out = w[1 - cur];
     int st;
     if (pending)
-      st = fvm_spike_local_lazy(pl->n_tiles, pl->P, pl->config, pl->p, pl->q, pl->b, pl->sep, pl->bends,
-                                pl->has_first_cell, pl->last_cell_local, pl->theta, w_in, w_out, pl->w_stride, pl->rs,
-                                pl->rr, pl->n_tiles, pl->g_first, pl->Vt, pl->Wt, pl->xs, xs_off, xs_n, pl->extents,
-                                stream);
+      st = spike_local_lazy_impl(pl->n_tiles, pl->P, pl->config, pl->p, pl->q, pl->b, pl->sep, pl->bends,
+                                 pl->has_first_cell, pl->last_cell_local, pl->theta, w_in, w_out, pl->w_stride, pl->rs,
+                                 pl->rr, pl->n_tiles, pl->g_first, pl->Vt, pl->Wt, pl->xs, xs_off, xs_n, pl->extents,
+                                 stream, false);
     else
-      st = fvm_spike_local(pl->n_tiles, pl->P, pl->config, pl->p, pl->q, pl->b, pl->sep, pl->bends, pl->has_first_cell,
-                           pl->last_cell_local, pl->theta, w_in, w_out, pl->w_stride, pl->rs, pl->rr, pl->n_tiles,
-                           pl->g_first, stream);
+      st = spike_local_impl(pl->n_tiles, pl->P, pl->config, pl->p, pl->q, pl->b, pl->sep, pl->bends, pl->has_first_cell,
+                            pl->last_cell_local, pl->theta, w_in, w_out, pl->w_stride, pl->rs, pl->rr, pl->n_tiles,
+                            pl->g_first, stream, false);
     if (st) return st;
-    if (!blocks) {
-      st = fvm_spike_reduce_solve(pl->n_tiles, pl->P, pl->rp, pl->rq, pl->rinv, pl->rr, pl->xs, stream);
+    // the separator solve builds its right-hand side while loading it and writes the blocks' packets itself:
+    // reduced_rhs_kernel and rank_pack_kernel, fused (same arithmetic, same bits)
+    {
+      const int64_t n = blocks ? pl->m : pl->n_tiles, nb = blocks ? pl->P * pl->B : pl->P;
+      fvm::FusedRhs fr;
+      fr.rs = pl->rs; fr.sep = pl->sep; fr.nt = pl->n_tiles; fr.B = blocks ? pl->B : 1;
+      fr.g_first = pl->g_first; fr.packet = blocks ? pl->packet : nullptr;
+      double* sol = blocks ? pl->gr : pl->xs;
+      if (n <= 1024)
+        fvm::reduced_solve_kernel<128, 8, true><<<(unsigned)nb, 128, 0, (cudaStream_t)stream>>>(n, pl->rp, pl->rq, pl->rinv,
+                                                                                             pl->rr, sol, fr);
+      else
+        fvm::reduced_solve_kernel<1024, 8, true><<<(unsigned)nb, 1024, 0, (cudaStream_t)stream>>>(n, pl->rp, pl->rq,
+                                                                                               pl->rinv, pl->rr, sol, fr);
+      st = (int)cudaGetLastError();
       if (st) return st;
-    } else {
-      st = fvm_spike_reduce_solve(pl->m, pl->P * pl->B, pl->rp, pl->rq, pl->rinv, pl->rr, pl->gr, stream);
-      if (st) return st;
-      st = fvm_spike_rank_pack(pl->P, pl->B, pl->m, pl->gr, pl->g_first, pl->packet, stream);
-      if (st) return st;
+    }
+    if (blocks) {
       const double* allp = pl->packet;
       if (pl->world > 1) {
         const int rc = allgather(pl->packet, pl->allp, (size_t)(pl->P * pl->B * 4), 8 /* ncclDouble */, comm, stream);
