@@ -46,6 +46,34 @@ def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.FvmProblem) == 8 * 12 + 4 * 5 + 4 + 8 * 2
 
 
+def test_struct_layouts_against_the_c_compiler(tmp_path):
+    """include/fvm_b200.h compiles as plain C, and the ctypes mirrors of its two structs have the sizes and field
+    offsets the C compiler gives them."""
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    fields = {"fvm_problem": [f[0] for f in _lib.FvmProblem._fields_],
+              "fvm_spike_plan": [f[0] for f in _lib.FvmSpikePlan._fields_]}
+    src = ['#include <stdio.h>', '#include <stddef.h>', '#include "fvm_b200.h"', 'int main(void) {']
+    for st, names in fields.items():
+        src.append('  printf("%s %%zu\\n", sizeof(%s));' % (st, st))
+        for n in names:
+            src.append('  printf("%s.%s %%zu\\n", offsetof(%s, %s));' % (st, n, st, n))
+    src += ['  return 0;', '}']
+    c = tmp_path / "layout.c"
+    c.write_text("\n".join(src))
+    exe = tmp_path / "layout"
+    subprocess.run([cc, "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(c), "-o", str(exe)],
+                   check=True)
+    out = dict(ln.split() for ln in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for st, cls in (("fvm_problem", _lib.FvmProblem), ("fvm_spike_plan", _lib.FvmSpikePlan)):
+        assert int(out[st]) == ctypes.sizeof(cls), st
+        for n in fields[st]:
+            assert int(out["%s.%s" % (st, n)]) == getattr(cls, n).offset, (st, n)
+
+
 def test_mesh_and_cellvariable():
     f = np.array([0.0, 0.1, 0.4, 0.5, 1.0])
     m = fvm_b200.Mesh(f)
