@@ -33,6 +33,24 @@ def plan_partition(J, tile_cells, world):
     return dict(tiles_per_rank=per_rank, tiles_global=per_rank * world, ranges=ranges)
 
 
+def pick_blocks(nt, world, wanted=None):
+    """Blocks per rank of the separator system (nt unknowns per rank): as many as keep a block at >= 256
+    unknowns (one pass of the CTA-wide solver), divide the rank's tiles evenly and keep the top system
+    (world * blocks unknowns) within the 1,024 one CTA solves.  ``wanted``: the caller's choice, checked."""
+    nt, cap = int(nt), 1024 // int(world)
+    if wanted is not None:
+        B = int(wanted)
+        if B < 1 or nt % B or nt // B < 2 or B > cap:
+            raise ValueError("blocks=%d does not cut %d tiles per rank into equal blocks of >= 2 (at most %d)"
+                             % (B, nt, cap))
+        return B
+    best = 1
+    for B in range(2, min(nt // 256, cap) + 1):
+        if nt % B == 0:
+            best = B
+    return best
+
+
 class _NcclUniqueId(ctypes.Structure):
     _fields_ = [("internal", ctypes.c_byte * 128)]
 
@@ -376,20 +394,7 @@ class PartitionedAdvectionDiffusionModel(object):
         return pl
 
     def _pick_blocks(self):
-        """Blocks per rank of the separator system: as many as keep a block at >= 256 unknowns (one pass of
-        the CTA-wide solver), divide the rank's tiles evenly and keep the top system within one CTA."""
-        nt, cap = self.nt, 1024 // self.comm.world
-        if self._blocks_wanted is not None:
-            B = int(self._blocks_wanted)
-            if B < 1 or nt % B or nt // B < 2 or B > cap:
-                raise ValueError("blocks=%d does not cut %d tiles per rank into equal blocks of >= 2 (at most %d)"
-                                 % (B, nt, cap))
-            return B
-        best = 1
-        for B in range(2, min(nt // 256, cap) + 1):
-            if nt % B == 0:
-                best = B
-        return best
+        return pick_blocks(self.nt, self.comm.world, self._blocks_wanted)
 
     def _reduced_local_solve(self, rhs, out=None):
         """Solve this rank's blocks of the separator system (m unknowns each, couplings to the neighbouring

@@ -1,3 +1,4 @@
+import pytest
 """Host-side multi-rank plumbing on CPU (gloo, world_size 2): the partition plan and the
 all-gather wrapper the partitioned solver builds its reduced system with."""
 import os
@@ -47,3 +48,17 @@ def test_comm_all_gather_gloo_world2(tmp_path):
     full = W.batched_sweep(8, 16)["k"]
     for r in range(2):
         assert np.array_equal(np.load(tmp_path / ("k%d.npy" % r)), full)
+
+
+def test_blocks_of_the_separator_system():
+    """How the host layer cuts a rank's part of the separator system into blocks (partitioned.pick_blocks)."""
+    from fvm_b200.partitioned import pick_blocks
+    assert pick_blocks(32768, 1) == 128           # cfg 5 on one GPU: 128 blocks of 256 separators
+    assert pick_blocks(32768, 8) == 128           # ... and on eight: 1,024 blocks in all, the top system's limit
+    assert pick_blocks(32768, 16) == 64
+    assert pick_blocks(256, 1) == 1 and pick_blocks(511, 1) == 1 and pick_blocks(512, 1) == 2
+    assert pick_blocks(3 * 257, 1) == 3           # only divisors of the tile count
+    assert pick_blocks(12, 1, wanted=3) == 3 and pick_blocks(4, 2, wanted=2) == 2
+    for nt, world, wanted in ((12, 1, 5), (12, 1, 12), (12, 1, 0), (4096, 8, 256)):
+        with pytest.raises(ValueError):
+            pick_blocks(nt, world, wanted)
