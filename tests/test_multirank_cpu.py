@@ -1,10 +1,10 @@
-import pytest
 """Host-side multi-rank plumbing on CPU (gloo, world_size 2): the partition plan and the
 all-gather wrapper the partitioned solver builds its reduced system with."""
 import os
 import socket
 
 import numpy as np
+import pytest
 import torch
 
 from fvm_b200.partitioned import Comm, plan_partition
