@@ -136,7 +136,7 @@ __device__ __forceinline__ double scan_values(double b_t, const ScanConsts& K, d
 }  // namespace
 
 template <int TPB, int CPT, int MODE>
-__global__ void __launch_bounds__(TPB, (TPB == 256 && CPT == 16) ? 2 : 1)
+__global__ void __launch_bounds__(TPB, CPT == 16 ? (TPB == 256 ? 2 : (TPB == 128 ? 4 : 1)) : 1)
 fused_cta_kernel(fvm_problem pr, const double* __restrict__ dt, double theta, int64_t nsteps,
                  int64_t ckpt_every, double* __restrict__ w_io, double* __restrict__ ckpt) {
   constexpr int T = TPB * CPT;
@@ -366,13 +366,17 @@ static int dispatch_cta(const fvm_problem& pr, const double* dt, double theta, i
 // Called by fvm_theta_run_fused (fused.cu) for 1024 < J <= 8192.
 int run_fused_cta(const fvm_problem& pr, const double* dt, double theta, int64_t nsteps, int64_t ckpt_every,
                   double* w, double* ckpt, cudaStream_t stream) {
-  if (pr.J <= 2048) return dispatch_cta<256, 8>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  // A step is a chain of latencies (two scans, two barriers): with more systems than SMs, CTAs of half the
+  // threads and twice the cells per thread share an SM (four of 128 threads, two of 256) and fill each other's
+  // waits; with fewer systems, the wider CTA finishes a system sooner.
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return (int)cudaGetLastError();
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (pr.J <= 2048) {
+    if (pr.P > sms) return dispatch_cta<128, 16>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+    return dispatch_cta<256, 8>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
+  }
   if (pr.J <= 4096) {
-    // A step is a chain of latencies (two scans, two barriers): with more systems than SMs, two CTAs of half
-    // the threads share an SM and fill each other's waits; with fewer, the wider CTA finishes a system sooner.
-    int dev = 0, sms = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return (int)cudaGetLastError();
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (pr.P > sms) return dispatch_cta<256, 16>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
     return dispatch_cta<512, 8>(pr, dt, theta, nsteps, ckpt_every, w, ckpt, stream);
   }

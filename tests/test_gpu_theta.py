@@ -103,10 +103,10 @@ def test_cta_per_system_sizes(J):
             assert step_error(ck[:, p], want, np.max(np.abs(w0[p]))) < TOL, (J, bc, theta, p)
 
 
-@pytest.mark.parametrize("J", [2100, 4096])
+@pytest.mark.parametrize("J", [1100, 2048, 2100, 4096])
 def test_cta_per_system_more_systems_than_sms(J):
-    """2048 < J <= 4096 with more systems than SMs: the configuration of 256 threads x 16 cells, two CTAs per
-    SM (fused_cta.cu: run_fused_cta).  All BC kinds, three values of theta, a sample against the oracle and
+    """1024 < J <= 4096 with more systems than SMs: the configurations of 16 cells per thread -- 128 threads,
+    four CTAs per SM (J <= 2048) and 256 threads, two CTAs per SM (fused_cta.cu: run_fused_cta).  All BC kinds, three values of theta, a sample against the oracle and
     every system against the one-thread-per-system kernel."""
     P = torch.cuda.get_device_properties(0).multi_processor_count + 13
     rng = np.random.default_rng(J)
