@@ -758,8 +758,9 @@ extern "C" int fvm_spike_rank_top(int64_t P, int64_t B, int64_t m, int32_t world
   if (P < 1 || P > 0x7fffffffLL || B < 1 || m < 2 || world < 1 || rank < 0 || rank >= world)
     return FVM_ERR_INVALID_ARG;
   if ((int64_t)world * B > fvm::kTopTPB * fvm::kTopCPT) return FVM_ERR_UNSUPPORTED;
-  int64_t shares = (B * m + 2047) / 2048;                  // ~2048 separators per CTA
-  if (shares > 64) shares = 64;
+  int64_t shares = (B * m + 511) / 512;                    // ~512 separators per CTA: two passes of its 256 threads
+  if (shares > 256) shares = 256;                          // (the redundant top solve is cheap; the pass over the
+                                                           // separators is a chain of load latencies)
   dim3 grid((unsigned)P, (unsigned)shares);
   fvm::rank_top_kernel<<<grid, fvm::kTopTPB, 0, (cudaStream_t)stream>>>(P, B, m, world, rank, allp, tp, tq, tinv, cst,
                                                                        gr, Vr, Wr, xs_ext);
